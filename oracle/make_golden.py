@@ -1,0 +1,97 @@
+"""TEST INFRASTRUCTURE ONLY -- generate tests/golden/*.pt by running the UNMODIFIED reference modules
+(imported from /root/reference through oracle/ref_shims.py) on seeded synthetic weights and inputs.
+
+Run in the build container only:  python -m oracle.make_golden
+Weights are not stored: they are regenerated from the seed by oracle/weights.py (and loaded into the
+reference modules with strict=True, which also pins the state_dict key layout of SURVEY.md Appendix A).
+Each fixture stores the small inputs and the reference outputs.
+"""
+import os
+import types
+
+import torch
+
+from oracle import ref_shims, weights
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+DEC = dict(channels=[256, 256], dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2,
+           num_heads=2, act_fn="snakebeta")  # configs/model/decoder/default.yaml:1-7
+
+
+def build_cfm(c_in, seed):
+    CFM = ref_shims.load_reference()[0]
+    n_spks, spk = (1, 64) if c_in == 160 else (109, c_in - 160)
+    cfm = CFM(160, 80, types.SimpleNamespace(solver="euler", sigma_min=1e-4), DEC, n_spks=n_spks,
+              spk_emb_dim=spk).eval()
+    cfm.load_state_dict(weights.estimator_state_dict(c_in, seed=seed), strict=True)
+    return cfm
+
+
+def build_generator(seed, weight_norm):
+    _, Generator, AttrDict, v1, _ = ref_shims.load_reference()
+    gen = Generator(AttrDict(v1)).eval()
+    sd = weights.generator_state_dict(seed, weight_norm=weight_norm)
+    if not weight_norm:
+        gen.remove_weight_norm()
+    gen.load_state_dict(sd, strict=True)
+    return gen
+
+
+def estimator_case(name, c_in, lengths, t_pad, seed, n_steps, t_scalar):
+    g = torch.Generator().manual_seed(seed + 1)
+    b = len(lengths)
+    cfm = build_cfm(c_in, seed)
+    mu = torch.randn(b, 80, t_pad, generator=g)
+    z = torch.randn(b, 80, t_pad, generator=g) * 0.667
+    mask = weights.prefix_mask(lengths, t_pad)
+    spks = torch.randn(b, c_in - 160, generator=g) if c_in > 160 else None
+    tb = torch.rand(b, generator=g)
+    with torch.inference_mode():
+        v_scalar = cfm.estimator(z, mask, mu, torch.tensor(t_scalar), spks)
+        v_batched = cfm.estimator(z, mask, mu, tb, spks)
+        dec = cfm.solve_euler(z, torch.linspace(0, 1, n_steps + 1), mu, mask, spks, None)
+    # compute_loss with its two random draws pinned (flow_matching.py:108,110)
+    x1 = torch.randn(b, 80, t_pad, generator=g)
+    t_draw = torch.rand(b, 1, 1, generator=g)
+    z_draw = torch.randn(b, 80, t_pad, generator=g)
+    orig_rand, orig_randn_like = torch.rand, torch.randn_like
+    torch.rand = lambda *a, **k: t_draw.clone()
+    torch.randn_like = lambda *a, **k: z_draw.clone()
+    try:
+        with torch.no_grad():
+            loss, y = cfm.compute_loss(x1, mask, mu, spks)
+    finally:
+        torch.rand, torch.randn_like = orig_rand, orig_randn_like
+    fx = dict(kind="estimator", c_in=c_in, seed=seed, lengths=list(lengths), t_pad=t_pad, n_steps=n_steps,
+              t_scalar=t_scalar, mu=mu, z=z, mask=mask, spks=spks, t_batched=tb, v_scalar=v_scalar.clone(),
+              v_batched=v_batched.clone(), decoded=dec.clone(), x1=x1, t_draw=t_draw, z_draw=z_draw,
+              loss=loss.clone(), y=y.clone())
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "v", float(v_scalar.abs().max()), "dec", float(dec.abs().max()), "loss", float(loss))
+
+
+def generator_case(name, b, t, seed, weight_norm):
+    g = torch.Generator().manual_seed(seed + 2)
+    gen = build_generator(seed, weight_norm)
+    mel = torch.randn(b, 80, t, generator=g) * 2.1 - 5.5  # LJSpeech-like mel statistics
+    with torch.inference_mode():
+        wav = gen(mel)
+    fx = dict(kind="generator", seed=seed, weight_norm=weight_norm, mel=mel, wav=wav.clone())
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "wav", float(wav.abs().max()), float(wav.abs().mean()))
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    torch.manual_seed(0)
+    torch.set_num_threads(8)
+    estimator_case("est_lj_ragged", 160, (24, 17, 9), 24, seed=11, n_steps=3, t_scalar=0.3)
+    estimator_case("est_lj_min", 160, (4, 1), 4, seed=12, n_steps=2, t_scalar=0.0)
+    estimator_case("est_vctk_ragged", 224, (20, 13), 20, seed=13, n_steps=2, t_scalar=0.75)
+    estimator_case("est_lj_t140", 160, (140, 77), 140, seed=14, n_steps=2, t_scalar=0.5)
+    generator_case("gen_plain", 2, 9, seed=21, weight_norm=False)
+    generator_case("gen_weightnorm", 1, 5, seed=22, weight_norm=True)
+
+
+if __name__ == "__main__":
+    main()
