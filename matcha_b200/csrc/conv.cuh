@@ -1,0 +1,245 @@
+// Shared definitions for the conv-as-GEMM kernels (tcgen05 and SIMT): geometry, fused epilogue.
+//
+// Activations are "NTC": [B][T][C] with C contiguous, so a conv tap is the same tile shifted along T and
+// every Conv1d / ConvTranspose1d / Linear on the path becomes   D[t, n] = sum_{tap, c} A[t*? + off_tap, c] * W[n, tap, c].
+// Reference ops covered (citations under /root/reference): Block1D conv (decoder.py:36), res_conv (:54),
+// Downsample1D (:67), Upsample1D ConvTranspose1d (:144), final_proj (:313), attention/FF linears
+// (transformer.py:48,126,196-204), HiFi-GAN conv_pre/ups/ResBlock1 convs (hifigan/models.py:154-177, 18-87).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mb {
+
+constexpr int kMaxTaps = 11;
+constexpr int kMaxPhases = 8;
+
+struct ConvGeom {
+  int B;
+  int T_in;        // rows per batch in each source view
+  int T_out;       // GEMM rows per batch
+  int n_src;       // 1 or 2 (channel concat of two tensors: decoder.py:427)
+  int src_ch[2];   // channels consumed from each source per tap (multiple of the K chunk)
+  int src_ld[2];   // row pitch (elements) of each source view
+  int n_taps, n_phases;
+  int tap_row[kMaxPhases][kMaxTaps];  // source row = t + tap_row
+  int tap_ch[kMaxPhases][kMaxTaps];   // channel base inside the source view (strided conv reads a [T/2][2C] view)
+  int N;           // output channels per phase (padded; weights hold n_phases*N rows)
+  int K_total;     // n_taps * (src_ch[0] + src_ch[1]) = weight row pitch
+};
+
+struct EpiParams {
+  int T_o;                 // output rows per batch (T_out * o_mul)
+  int o_mul;               // output row = t * o_mul + phase * o_phase_step
+  int o_phase_step;
+  int n_valid;             // real output channels (<= N), multiple of 8
+  const float* bias;       // [N] (zero padded) or null
+  // v += mish(groupnorm(raw)) * mask      (Block1D tail fused into the res_conv GEMM: decoder.py:37-43,60)
+  const void* gn_raw;  int gn_ld;  const float* gn_stats;  const float* gn_gamma;  const float* gn_beta;  float gn_inv_count;
+  // v += resid (+ resid2)
+  const void* resid;   int resid_ld;   int resid_f32;
+  const void* resid2;  int resid2_ld;  int resid2_f32;
+  float scale;             // v *= scale (HiFi-GAN xs / num_kernels: hifigan/models.py:192)
+  const float* snake_a;    // SnakeBeta exp(alpha), 1/(exp(beta)+1e-9) (transformer.py:70-78); null = off
+  const float* snake_invb;
+  const float* mask;       // [B][T_o] float 0/1 or null; used by gn_raw and mask_out
+  int mask_out;            // v *= mask
+  float* stats_out;        // GroupNorm partial sums [B][8][2] accumulated from v (32 channels per group)
+  // Euler update fused into final_proj (flow_matching.py:79): x += dt * v ; second output = x * mask
+  float* x_state;  int x_ld;  float dt;
+  void* out0;  int out0_ld;  int out0_f32;  float out0_slope;   // main store; slope != 1 applies LeakyReLU
+  void* out1;  int out1_ld;  float out1_slope;                  // second store (operand dtype), LeakyReLU(slope)
+  // LayerNorm of the finished row (needs the whole row in one tile: N == 256) -> ln_out (operand dtype)
+  void* ln_out;  int ln_ld;  const float* ln_g;  const float* ln_b;
+};
+
+template <typename T> struct Elem;
+template <> struct Elem<float> {
+  static __device__ __forceinline__ float ld(const float* p) { return *p; }
+  static __device__ __forceinline__ void ld8(const float* p, float* v) {
+    float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  static __device__ __forceinline__ void st8(float* p, const float* v) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+};
+template <> struct Elem<__nv_bfloat16> {
+  static __device__ __forceinline__ float ld(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+  static __device__ __forceinline__ void ld8(const __nv_bfloat16* p, float* v) {
+    uint4 u = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+  }
+  static __device__ __forceinline__ void st8(__nv_bfloat16* p, const float* v) {
+    uint4 u; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = u;
+  }
+};
+template <> struct Elem<__half> {
+  static __device__ __forceinline__ float ld(const __half* p) { return __half2float(*p); }
+  static __device__ __forceinline__ void ld8(const __half* p, float* v) {
+    uint4 u = *reinterpret_cast<const uint4*>(p);
+    const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 f = __half22float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+  }
+  static __device__ __forceinline__ void st8(__half* p, const float* v) {
+    uint4 u; __half2* h = reinterpret_cast<__half2*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);  // saturates to +-inf only beyond 65504
+    *reinterpret_cast<uint4*>(p) = u;
+  }
+};
+
+// x * tanh(softplus(x)) with torch's softplus threshold 20 (decoder.py:38).  With n = e^x,
+// tanh(log(1+n)) = (n^2+2n)/(n^2+2n+2): one exp, one divide, no cancellation for x << 0.
+__device__ __forceinline__ float mish_f(float x) {
+  if (x > 20.f) return x;
+  float n = expf(x);
+  float w = n * (n + 2.f);
+  return x * (w / (w + 2.f));
+}
+__device__ __forceinline__ float lrelu_f(float x, float slope) { return x > 0.f ? x : x * slope; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Fused epilogue for one thread's 32-channel slice [n0, n0+32) of output row (b, t, phase).
+// Called by ALL lanes of a warp (GroupNorm partial sums are warp-reduced); `valid` gates memory traffic.
+// v holds the fp32 accumulators on entry and the finished values on exit (what LayerNorm consumes).
+template <typename T>
+__device__ __forceinline__ void epilogue_chunk(const EpiParams& e, int b, int t, int phase, int n0, bool valid,
+                                               bool do_store, float (&v)[32]) {
+  const int to = t * e.o_mul + phase * e.o_phase_step;
+  const long row = static_cast<long>(b) * e.T_o + to;
+  const int nv = min(32, e.n_valid - n0);  // channels of this chunk that exist (multiple of 8, may be <= 0)
+  if (e.bias) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += __ldg(e.bias + n0 + i);
+  }
+  const float m = (e.mask && valid) ? __ldg(e.mask + row) : 1.f;
+  if (e.gn_raw && valid) {
+    const float* st = e.gn_stats + (static_cast<long>(b) * 8 + (n0 >> 5)) * 2;
+    const float mean = st[0] * e.gn_inv_count;
+    const float var = fmaxf(st[1] * e.gn_inv_count - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + 1e-5f);
+    const T* raw = reinterpret_cast<const T*>(e.gn_raw) + row * e.gn_ld + n0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float r[8];
+      Elem<T>::ld8(raw + 8 * j, r);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int n = n0 + 8 * j + i;
+        const float y = (r[i] - mean) * rstd * __ldg(e.gn_gamma + n) + __ldg(e.gn_beta + n);
+        v[8 * j + i] += mish_f(y) * m;
+      }
+    }
+  }
+  if (e.resid && valid) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (8 * j < nv) {
+        float r[8];
+        if (e.resid_f32) Elem<float>::ld8(reinterpret_cast<const float*>(e.resid) + row * e.resid_ld + n0 + 8 * j, r);
+        else Elem<T>::ld8(reinterpret_cast<const T*>(e.resid) + row * e.resid_ld + n0 + 8 * j, r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[8 * j + i] += r[i];
+      }
+    }
+  }
+  if (e.resid2 && valid) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (8 * j < nv) {
+        float r[8];
+        if (e.resid2_f32) Elem<float>::ld8(reinterpret_cast<const float*>(e.resid2) + row * e.resid2_ld + n0 + 8 * j, r);
+        else Elem<T>::ld8(reinterpret_cast<const T*>(e.resid2) + row * e.resid2_ld + n0 + 8 * j, r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[8 * j + i] += r[i];
+      }
+    }
+  }
+  if (e.scale != 1.f) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= e.scale;
+  }
+  if (e.snake_a) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float s = sinf(v[i] * __ldg(e.snake_a + n0 + i));
+      v[i] += __ldg(e.snake_invb + n0 + i) * s * s;
+    }
+  }
+  if (e.mask_out) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= m;
+  }
+  if (e.stats_out) {  // warp-collective: every lane takes part, invalid rows contribute zero
+    float s = 0.f, ss = 0.f;
+    if (valid) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) { s += v[i]; ss += v[i] * v[i]; }
+    }
+    s = warp_sum(s);
+    ss = warp_sum(ss);
+    // all rows of a warp belong to the same batch element b (tiles never straddle batch elements)
+    if ((threadIdx.x & 31) == 0 && do_store) {
+      float* st = e.stats_out + (static_cast<long>(b) * 8 + (n0 >> 5)) * 2;
+      atomicAdd(st, s);
+      atomicAdd(st + 1, ss);
+    }
+  }
+  if (!valid) return;
+  if (e.x_state) {
+    float* xs = e.x_state + row * e.x_ld + n0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (8 * j < nv) {
+        float x[8];
+        Elem<float>::ld8(xs + 8 * j, x);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += e.dt * v[8 * j + i];
+        if (do_store) Elem<float>::st8(xs + 8 * j, x);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[8 * j + i] = x[i] * m;
+      }
+    }
+  }
+  if (!do_store) return;
+  if (e.out0) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (8 * j < nv) {
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = e.out0_slope == 1.f ? v[8 * j + i] : lrelu_f(v[8 * j + i], e.out0_slope);
+        if (e.out0_f32) Elem<float>::st8(reinterpret_cast<float*>(e.out0) + row * e.out0_ld + n0 + 8 * j, o);
+        else Elem<T>::st8(reinterpret_cast<T*>(e.out0) + row * e.out0_ld + n0 + 8 * j, o);
+      }
+    }
+  }
+  if (e.out1) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (8 * j < nv) {
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = e.out1_slope == 1.f ? v[8 * j + i] : lrelu_f(v[8 * j + i], e.out1_slope);
+        Elem<T>::st8(reinterpret_cast<T*>(e.out1) + row * e.out1_ld + n0 + 8 * j, o);
+      }
+    }
+  }
+}
+
+}  // namespace mb

@@ -1,0 +1,306 @@
+// HBM-bound helper kernels of the hot path: GroupNorm-apply + Mish (+ time projection) + mask, LayerNorm (fp32 mode),
+// boundary layout changes (B,C,T) <-> [B][T][C], estimator input packing, timestep embedding, vocoder head.
+// All are one pass, 16-byte vector accesses along the contiguous channel axis.
+#include <math.h>
+
+#include "conv.cuh"
+#include "launch.h"
+
+namespace mb {
+
+// ---------------------------------------------------------------- GroupNorm apply + Mish (+temb) + mask
+// out = (mish(gn(raw)) + tadd) * mask   (decoder.py:37-43 followed by :58 and the next block's x*mask, :41)
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn_mish_kernel(const T* __restrict__ raw, const float* __restrict__ stats, const float* __restrict__ gamma,
+               const float* __restrict__ beta, const float* __restrict__ tadd, int tadd_bstride,
+               const float* __restrict__ mask, T* __restrict__ out, int Tn, long total_vec, float inv_count) {
+  const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;  // one 8-channel vector of a 256-ch row
+  if (i >= total_vec) return;
+  const long row = i >> 5;
+  const int c0 = static_cast<int>(i & 31) * 8;
+  const int b = static_cast<int>(row / Tn);
+  const float m = __ldg(mask + row);
+  float o[8];
+  if (m == 0.f) {  // exact: anything times a zero mask is zero (inputs are finite)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = 0.f;
+  } else {
+    const float* st = stats + (static_cast<long>(b) * 8 + (c0 >> 5)) * 2;
+    const float mean = st[0] * inv_count;
+    const float rstd = rsqrtf(fmaxf(st[1] * inv_count - mean * mean, 0.f) + 1e-5f);
+    float r[8];
+    Elem<T>::ld8(raw + row * 256 + c0, r);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float y = (r[k] - mean) * rstd * __ldg(gamma + c0 + k) + __ldg(beta + c0 + k);
+      float v = mish_f(y);
+      if (tadd) v += __ldg(tadd + static_cast<long>(b) * tadd_bstride + c0 + k);
+      o[k] = v * m;
+    }
+  }
+  Elem<T>::st8(out + row * 256 + c0, o);
+}
+
+template <typename T>
+cudaError_t launch_gn_mish(const T* raw, const float* stats, const float* gamma, const float* beta, const float* tadd,
+                           int tadd_bstride, const float* mask, T* out, int B, int Tn, cudaStream_t st) {
+  const long total = static_cast<long>(B) * Tn * 32;
+  gn_mish_kernel<T><<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
+      raw, stats, gamma, beta, tadd, tadd_bstride, mask, out, Tn, total, 1.f / (32.f * Tn));
+  return cudaGetLastError();
+}
+template cudaError_t launch_gn_mish<float>(const float*, const float*, const float*, const float*, const float*, int,
+                                           const float*, float*, int, int, cudaStream_t);
+template cudaError_t launch_gn_mish<__nv_bfloat16>(const __nv_bfloat16*, const float*, const float*, const float*,
+                                                   const float*, int, const float*, __nv_bfloat16*, int, int, cudaStream_t);
+template cudaError_t launch_gn_mish<__half>(const __half*, const float*, const float*, const float*, const float*, int,
+                                            const float*, __half*, int, int, cudaStream_t);
+
+// ---------------------------------------------------------------- LayerNorm(256), one warp per row, two-pass variance
+template <typename T>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const T* __restrict__ in, const float* __restrict__ g, const float* __restrict__ bta,
+                 T* __restrict__ out, long rows) {
+  const long row = static_cast<long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float v[8];
+  Elem<T>::ld8(in + row * 256 + lane * 8, v);
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += v[k];
+  const float mean = warp_sum(s) * (1.f / 256.f);
+  float ss = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { const float d = v[k] - mean; ss += d * d; }
+  const float rstd = rsqrtf(warp_sum(ss) * (1.f / 256.f) + 1e-5f);
+  float o[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) o[k] = (v[k] - mean) * rstd * __ldg(g + lane * 8 + k) + __ldg(bta + lane * 8 + k);
+  Elem<T>::st8(out + row * 256 + lane * 8, o);
+}
+template <typename T>
+cudaError_t launch_layernorm(const T* in, const float* g, const float* b, T* out, long rows, cudaStream_t st) {
+  layernorm_kernel<T><<<static_cast<unsigned>((rows + 7) / 8), 256, 0, st>>>(in, g, b, out, rows);
+  return cudaGetLastError();
+}
+template cudaError_t launch_layernorm<float>(const float*, const float*, const float*, float*, long, cudaStream_t);
+template cudaError_t launch_layernorm<__nv_bfloat16>(const __nv_bfloat16*, const float*, const float*, __nv_bfloat16*,
+                                                     long, cudaStream_t);
+template cudaError_t launch_layernorm<__half>(const __half*, const float*, const float*, __half*, long, cudaStream_t);
+
+// ---------------------------------------------------------------- (B,C,T) <-> [B][T][C] fp32, 32x32 shared-memory tiles
+__global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ in, float* __restrict__ out, int R, int C) {
+  // in: [batch][R][C] -> out: [batch][C][R]
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const float* src = in + static_cast<long>(b) * R * C;
+  float* dst = out + static_cast<long>(b) * R * C;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (r < R && c < C) ? src[static_cast<long>(r) * C + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (r < R && c < C) dst[static_cast<long>(c) * R + r] = tile[threadIdx.x][i];
+  }
+}
+cudaError_t launch_bct_to_btc(const float* in, float* out, int B, int C, int Tn, cudaStream_t st) {
+  dim3 grid((Tn + 31) / 32, (C + 31) / 32, B);
+  transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(in, out, C, Tn);
+  return cudaGetLastError();
+}
+cudaError_t launch_btc_to_bct(const float* in, float* out, int B, int C, int Tn, cudaStream_t st) {
+  dim3 grid((C + 31) / 32, (Tn + 31) / 32, B);
+  transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(in, out, Tn, C);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- estimator input [x | mu | spk | 0] * mask  (decoder.py:384-388, :41)
+template <typename T>
+__global__ void __launch_bounds__(256)
+pack_xin_kernel(const float* __restrict__ x, const float* __restrict__ mu, const float* __restrict__ spk, int spk_dim,
+                const float* __restrict__ mask, T* __restrict__ xin, int ld, int Tn, long total_vec) {
+  const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total_vec) return;
+  const int vpr = ld / 8;
+  const long row = i / vpr;
+  const int c0 = static_cast<int>(i % vpr) * 8;
+  const int b = static_cast<int>(row / Tn);
+  const float m = __ldg(mask + row);
+  float o[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = c0 + k;
+    float v = 0.f;
+    if (c < 80) v = x[row * 80 + c];
+    else if (c < 160) v = mu[row * 80 + c - 80];
+    else if (c < 160 + spk_dim) v = spk[static_cast<long>(b) * spk_dim + c - 160];
+    o[k] = v * m;
+  }
+  Elem<T>::st8(xin + row * ld + c0, o);
+}
+template <typename T>
+cudaError_t launch_pack_xin(const float* x_ntc, const float* mu_ntc, const float* spk, int spk_dim, const float* mask,
+                            T* xin, int ld, int B, int Tn, cudaStream_t st) {
+  const long total = static_cast<long>(B) * Tn * (ld / 8);
+  pack_xin_kernel<T><<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(x_ntc, mu_ntc, spk, spk_dim, mask, xin,
+                                                                                 ld, Tn, total);
+  return cudaGetLastError();
+}
+template cudaError_t launch_pack_xin<float>(const float*, const float*, const float*, int, const float*, float*, int, int,
+                                            int, cudaStream_t);
+template cudaError_t launch_pack_xin<__nv_bfloat16>(const float*, const float*, const float*, int, const float*,
+                                                    __nv_bfloat16*, int, int, int, cudaStream_t);
+template cudaError_t launch_pack_xin<__half>(const float*, const float*, const float*, int, const float*, __half*, int,
+                                             int, int, cudaStream_t);
+
+// mask pyramid: mask[:, :, ::2] (decoder.py:407)
+__global__ void mask_half_kernel(const float* __restrict__ mask, float* __restrict__ mh, int Tn, long total) {
+  const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int th = Tn / 2;
+  const long b = i / th, t = i % th;
+  mh[i] = mask[b * Tn + 2 * t];
+}
+cudaError_t launch_mask_half(const float* mask, float* mask_h, int B, int Tn, cudaStream_t st) {
+  const long total = static_cast<long>(B) * (Tn / 2);
+  mask_half_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(mask, mask_h, Tn, total);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- timestep embedding
+// SinusoidalPosEmb (decoder.py:20-29): emb = cat(sin(e), cos(e)), e = (1000 t) * exp(j * -(ln 1e4 / (half-1))).
+// exp/sin/cos are evaluated in double and rounded once, i.e. correctly rounded fp32 functions of fp32 arguments.
+__global__ void sinusoidal_kernel(const float* __restrict__ t_vals, int c_in, int ld, float* __restrict__ emb) {
+  const int half = c_in / 2;
+  const int j = threadIdx.x;
+  const float t = t_vals[blockIdx.x];
+  if (j < half) {
+    const float step = static_cast<float>(-(log(10000.0) / (half - 1)));
+    const float w = static_cast<float>(exp(static_cast<double>(static_cast<float>(j) * step)));
+    const float e = (1000.f * t) * w;
+    emb[static_cast<long>(blockIdx.x) * ld + j] = static_cast<float>(sin(static_cast<double>(e)));
+    emb[static_cast<long>(blockIdx.x) * ld + half + j] = static_cast<float>(cos(static_cast<double>(e)));
+  }
+}
+cudaError_t launch_sinusoidal(const float* t_vals, int n_t, int c_in, int ld, float* emb, cudaStream_t st) {
+  sinusoidal_kernel<<<n_t, 128, 0, st>>>(t_vals, c_in, ld, emb);
+  return cudaGetLastError();
+}
+
+// y[t][n] = act(x[t] . w[n] + b[n]): one warp per output, fp32 (TimestepEmbedding decoder.py:105-117; mlp decoder.py:49)
+__global__ void __launch_bounds__(256)
+small_linear_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                    float* __restrict__ y, int K, int N, int act) {
+  const int n = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int t = blockIdx.y;
+  if (n >= N) return;
+  const int lane = threadIdx.x & 31;
+  const float* xr = x + static_cast<long>(t) * K;
+  const float* wr = w + static_cast<long>(n) * K;
+  float s = 0.f;
+  for (int k = lane; k < K; k += 32) s = fmaf(xr[k], wr[k], s);
+  s = warp_sum(s);
+  if (lane == 0) {
+    s += b[n];
+    if (act == 1) s = s / (1.f + expf(-s));
+    else if (act == 2) s = mish_f(s);
+    y[static_cast<long>(t) * N + n] = s;
+  }
+}
+cudaError_t launch_small_linear(const float* x, const float* w, const float* b, float* y, int n_t, int K, int N, int act,
+                                cudaStream_t st) {
+  dim3 grid((N + 7) / 8, n_t);
+  small_linear_kernel<<<grid, 256, 0, st>>>(x, w, b, y, K, N, act);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- vocoder boundary
+template <typename T>
+__global__ void __launch_bounds__(256)
+pack_mel_kernel(const float* __restrict__ mel, int Tsrc, float scale, float shift, T* __restrict__ out, int ld, int L,
+                long total) {
+  const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int vpr = ld / 8;
+  const int t = static_cast<int>(i % L);           // t fastest: coalesced reads of the (B,C,T) source
+  const int cg = static_cast<int>((i / L) % vpr);
+  const long b = i / (static_cast<long>(L) * vpr);
+  float o[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cg * 8 + k;
+    o[k] = c < 80 ? mel[(b * 80 + c) * Tsrc + t] * scale + shift : 0.f;
+  }
+  Elem<T>::st8(out + (b * L + t) * ld + cg * 8, o);
+}
+template <typename T>
+cudaError_t launch_pack_mel(const float* mel_bct, int Tsrc, float scale, float shift, T* out, int ld, int B, int L,
+                            cudaStream_t st) {
+  const long total = static_cast<long>(B) * L * (ld / 8);
+  pack_mel_kernel<T><<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(mel_bct, Tsrc, scale, shift, out, ld, L,
+                                                                                 total);
+  return cudaGetLastError();
+}
+template cudaError_t launch_pack_mel<float>(const float*, int, float, float, float*, int, int, int, cudaStream_t);
+template cudaError_t launch_pack_mel<__nv_bfloat16>(const float*, int, float, float, __nv_bfloat16*, int, int, int,
+                                                    cudaStream_t);
+template cudaError_t launch_pack_mel<__half>(const float*, int, float, float, __half*, int, int, int, cudaStream_t);
+
+__global__ void affine_crop_kernel(const float* __restrict__ in, int Tsrc, float scale, float shift,
+                                   float* __restrict__ out, int L, long total) {
+  const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const long bc = i / L;
+  const int t = static_cast<int>(i % L);
+  out[i] = in[bc * Tsrc + t] * scale + shift;
+}
+cudaError_t launch_affine_crop(const float* in, int Tsrc, float scale, float shift, float* out, int B, int C, int L,
+                               cudaStream_t st) {
+  const long total = static_cast<long>(B) * C * L;
+  affine_crop_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(in, Tsrc, scale, shift, out, L, total);
+  return cudaGetLastError();
+}
+
+// conv_post Conv1d(32,1,7,pad 3) + tanh (hifigan/models.py:177,194-195); the input already carries leaky_relu(0.01).
+template <typename T>
+__global__ void __launch_bounds__(256)
+conv_post_kernel(const T* __restrict__ in, const float* __restrict__ w, float bias, float* __restrict__ wav, long L) {
+  __shared__ float ws[7 * 32];
+  for (int i = threadIdx.x; i < 7 * 32; i += blockDim.x) ws[i] = w[i];
+  __syncthreads();
+  const long t = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long b = blockIdx.y;
+  if (t >= L) return;
+  float acc = bias;
+#pragma unroll
+  for (int j = 0; j < 7; ++j) {
+    const long s = t + j - 3;
+    if (s < 0 || s >= L) continue;
+    const T* p = in + (b * L + s) * 32;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float v[8];
+      Elem<T>::ld8(p + 8 * q, v);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc = fmaf(v[k], ws[j * 32 + 8 * q + k], acc);
+    }
+  }
+  wav[b * L + t] = tanhf(acc);
+}
+template <typename T>
+cudaError_t launch_conv_post(const T* in, const float* w, float bias, float* wav, int B, long L, cudaStream_t st) {
+  dim3 grid(static_cast<unsigned>((L + 255) / 256), B);
+  conv_post_kernel<T><<<grid, 256, 0, st>>>(in, w, bias, wav, L);
+  return cudaGetLastError();
+}
+template cudaError_t launch_conv_post<float>(const float*, const float*, float, float*, int, long, cudaStream_t);
+template cudaError_t launch_conv_post<__nv_bfloat16>(const __nv_bfloat16*, const float*, float, float*, int, long,
+                                                     cudaStream_t);
+template cudaError_t launch_conv_post<__half>(const __half*, const float*, float, float*, int, long, cudaStream_t);
+
+}  // namespace mb

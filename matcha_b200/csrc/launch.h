@@ -1,0 +1,54 @@
+// Host-visible launch interface of the kernels (internal; the public boundary is include/matcha_b200.h).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include "conv.cuh"
+
+namespace mb {
+
+struct ConvLaunch {
+  ConvGeom g;
+  EpiParams e;
+  const void* a[2];   // sources (SIMT path)
+  const void* w;      // packed weights [n_phases*N][K_total]
+  CUtensorMap tmA[2]; // TMA views (tcgen05 path)
+  CUtensorMap tmW;
+  int ntile, kc;      // tcgen05 tile: N per CTA, K chunk (channels per TMA box)
+};
+
+template <typename T> cudaError_t launch_conv_umma(const ConvLaunch& L, cudaStream_t st);
+template <typename T> cudaError_t launch_conv_simt(const ConvLaunch& L, cudaStream_t st);
+
+// ---- elementwise / small kernels (elementwise.cu)
+template <typename T>
+cudaError_t launch_gn_mish(const T* raw, const float* stats, const float* gamma, const float* beta, const float* tadd,
+                           int tadd_bstride, const float* mask, T* out, int B, int Tn, cudaStream_t st);
+template <typename T>
+cudaError_t launch_layernorm(const T* in, const float* g, const float* b, T* out, long rows, cudaStream_t st);
+cudaError_t launch_bct_to_btc(const float* in, float* out, int B, int C, int Tn, cudaStream_t st);
+cudaError_t launch_btc_to_bct(const float* in, float* out, int B, int C, int Tn, cudaStream_t st);
+template <typename T>
+cudaError_t launch_pack_xin(const float* x_ntc, const float* mu_ntc, const float* spk, int spk_dim, const float* mask,
+                            T* xin, int ld, int B, int Tn, cudaStream_t st);
+cudaError_t launch_mask_half(const float* mask, float* mask_h, int B, int Tn, cudaStream_t st);
+// sinusoidal embedding + time MLP + the six per-ResNet projections (decoder.py:20-29, 105-117, 49)
+cudaError_t launch_sinusoidal(const float* t_vals, int n_t, int c_in, int ld, float* emb, cudaStream_t st);
+// small dense layer y[t][n] = act(sum_k x[t][k] w[n][k] + b[n]); act: 0 none, 1 SiLU, 2 Mish
+cudaError_t launch_small_linear(const float* x, const float* w, const float* b, float* y, int n_t, int K, int N, int act,
+                                cudaStream_t st);
+// mel (B,80,Tsrc) fp32, first L frames -> operand [B][L][ld] = value*scale+shift, channels >= 80 zero
+template <typename T>
+cudaError_t launch_pack_mel(const float* mel_bct, int Tsrc, float scale, float shift, T* out, int ld, int B, int L,
+                            cudaStream_t st);
+// out (B,C,L) = in (B,C,Tsrc)[:, :, :L] * scale + shift   (crop + denormalize: matcha_tts.py:136,145)
+cudaError_t launch_affine_crop(const float* in, int Tsrc, float scale, float shift, float* out, int B, int C, int L,
+                               cudaStream_t st);
+template <typename T>
+cudaError_t launch_conv_post(const T* in, const float* w /*[7][32]*/, float bias, float* wav, int B, long L, cudaStream_t st);
+
+// ---- attention (attention.cu): qkv [B][L][384] (q | k | v, 2 heads x 64), additive key mask, out [B][L][128]
+template <typename T>
+cudaError_t launch_attention_simt(const T* qkv, const float* mask, T* out, int B, int L, cudaStream_t st);
+
+}  // namespace mb
