@@ -1,0 +1,94 @@
+/* matcha_b200 -- C ABI of the B200-native Matcha-TTS synthesis hot path.
+ *
+ * The reference (Mocifiel/Matcha, a pure-PyTorch project) has no FFI layer; its boundary for this path is the Python
+ * class API.  Each entry point below names the reference interface it stands behind (path:line under the reference
+ * tree).  All tensor arguments are plain pointers in the REFERENCE layouts: (B, C, T) contiguous fp32; any internal
+ * relayout ([B][T][C], bf16/f16 operands) is private.  Unless stated otherwise pointers are DEVICE pointers and work is
+ * enqueued on `stream` (a cudaStream_t passed as void*).  Every function returns 0 on success; otherwise
+ * mb200_last_error() describes the failure (thread-local string).  There is no CPU fallback.
+ */
+#ifndef MATCHA_B200_H_
+#define MATCHA_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mb200_plan mb200_plan;
+
+enum { MB200_F32 = 0, MB200_BF16 = 1, MB200_F16 = 2 };
+
+typedef struct {
+  int dtype;       /* MB200_F32: FFMA kernels, fp32 everywhere.  MB200_BF16 / MB200_F16: tcgen05 tensor-core kernels,
+                      bf16 / f16 operands and activations, fp32 accumulation and statistics. */
+  int c_in;        /* estimator input channels: 160 (LJSpeech) or 224 (VCTK: + 64 speaker dims), flow_matching.py:130 */
+  int force_simt;  /* debugging: run the half-precision modes on the FFMA kernels instead of tcgen05 */
+  int use_graph;   /* capture decode / vocoder launches into a CUDA graph per (B, T, n_steps) shape */
+} mb200_cfg;
+
+/* One parameter tensor of a reference state_dict: HOST fp32, contiguous. */
+typedef struct {
+  const char* name;
+  const float* data;
+  int ndim;
+  long long shape[4];
+} mb200_tensor;
+
+const char* mb200_last_error(void);
+const char* mb200_version(void);
+
+int mb200_plan_create(const mb200_cfg* cfg, mb200_plan** out);
+void mb200_plan_destroy(mb200_plan* plan);
+
+/* Decoder.__init__ parameter tree (matcha/models/components/decoder.py:201-316); `prefix` is stripped from names
+ * (e.g. "estimator." or "decoder.estimator.").  Repacks to the kernels' operand layouts and uploads. */
+int mb200_load_estimator(mb200_plan* plan, const mb200_tensor* tensors, int n, const char* prefix);
+/* HiFi-GAN Generator parameters (matcha/hifigan/models.py:149-179), either weight_g/weight_v (checkpoint layout,
+ * matcha/cli.py:87) or plain weight (after remove_weight_norm, models.py:199-206). */
+int mb200_load_generator(mb200_plan* plan, const mb200_tensor* tensors, int n);
+
+/* The (t, dt) pairs BASECFM.solve_euler uses (matcha/models/components/flow_matching.py:52,70-83), fp32. Host only. */
+int mb200_euler_schedule(int n_steps, float* t_out, float* dt_out);
+
+/* Decoder.forward(x, mask, mu, t, spks) -> velocity (B,80,T)   (decoder.py:363-443).
+ * t: device fp32, 1 value (t_is_batched = 0) or B values (t_is_batched = 1, the compute_loss case). spks: (B, c_in-160) or NULL. */
+int mb200_estimator_forward(mb200_plan* plan, const float* x, const float* mask, const float* mu, const float* t,
+                            int t_is_batched, const float* spks, int B, int T, float* out, void* stream);
+
+/* BASECFM.solve_euler(x=z, t_span=linspace(0,1,n_steps+1), mu, mask, spks) -> (B,80,T)   (flow_matching.py:55-85).
+ * z is the already temperature-scaled noise (flow_matching.py:51). */
+int mb200_cfm_decode(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
+                     int T, int n_steps, float* out, void* stream);
+
+/* Generator.forward(mel (B,80,L)) -> wav (B,1,256*L)   (matcha/hifigan/models.py:181-197). */
+int mb200_hifigan_forward(mb200_plan* plan, const float* mel, int B, int L, float* wav, void* stream);
+
+/* The whole hot path of MatchaTTS.synthesise + cli.to_waveform: decode, crop to L frames, denormalise
+ * (matcha_tts.py:135-145, utils/model.py:71-90), vocode, clamp (cli.py:117-118).
+ * dec_out (B,80,T), mel_out (B,80,L), wav_out (B,1,256*L); any of the three may be NULL except wav_out. */
+int mb200_synthesise(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
+                     int T, int n_steps, int L, float mel_mean, float mel_std, float* dec_out, float* mel_out,
+                     float* wav_out, void* stream);
+
+/* Same, with HOST buffers (pinned or pageable): copies inputs in, runs, copies mel_out / wav_out back and synchronises.
+ * This is the end-to-end call the benchmark's `e2e` figure times. */
+int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
+                          int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out);
+
+/* Bookkeeping for the benchmark: kernels launched (or replayed inside graphs) by this plan since creation. */
+long long mb200_launch_count(const mb200_plan* plan);
+/* Device-memory footprint of the plan's workspaces and weights, bytes. */
+long long mb200_workspace_bytes(const mb200_plan* plan);
+
+/* Unit-test hook: one Conv1d / ConvTranspose1d (+ bias) through the conv-GEMM kernel of the plan's mode.
+ * x (B,Cin,T) fp32 device, w reference layout HOST fp32 ((Cout,Cin,K) or (Cin,Cout,K) when transposed), bias HOST (Cout)
+ * or NULL, y (B,Cout,T_out) fp32 device.  stride applies to Conv1d (1|2) or ConvTranspose1d (K == 2*stride). */
+int mb200_test_conv1d(mb200_plan* plan, const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T,
+                      int K, int dilation, int stride, int transposed, float* y, void* stream);
+/* Unit-test hook: masked-additive self-attention, qkv (B,T,384) fp32 device (q pre-scaled), mask (B,T) -> out (B,T,128). */
+int mb200_test_attention(mb200_plan* plan, const float* qkv, const float* mask, int B, int T, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MATCHA_B200_H_ */

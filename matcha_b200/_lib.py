@@ -1,0 +1,244 @@
+"""ctypes binding of libmatcha_b200.so (the C ABI declared in include/matcha_b200.h).
+
+There is no CPU or PyTorch fallback: if the library is missing or a call fails, an exception is raised.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmatcha_b200.so")
+
+F32, BF16, F16 = 0, 1, 2
+DTYPES = {"fp32": F32, "float32": F32, "bf16": BF16, "bfloat16": BF16, "fp16": F16, "float16": F16, "half": F16}
+
+EXPORTS = [
+    "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
+    "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
+    "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
+    "mb200_workspace_bytes", "mb200_test_conv1d", "mb200_test_attention",
+]
+
+
+class Cfg(ctypes.Structure):
+    _fields_ = [("dtype", ctypes.c_int), ("c_in", ctypes.c_int), ("force_simt", ctypes.c_int),
+                ("use_graph", ctypes.c_int)]
+
+
+class Tensor(ctypes.Structure):
+    _fields_ = [("name", ctypes.c_char_p), ("data", ctypes.c_void_p), ("ndim", ctypes.c_int),
+                ("shape", ctypes.c_longlong * 4)]
+
+
+_lib = None
+_lock = threading.Lock()
+
+
+def load():
+    """Loads the shared library (once).  Raises if it has not been built: the product path has no fallback."""
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m matcha_b200.build` (nvcc, sm_100a). "
+                "matcha_b200 has no CPU / PyTorch fallback.")
+        lib = ctypes.CDLL(LIB_PATH)
+        vp, i, f = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+        lib.mb200_last_error.restype = ctypes.c_char_p
+        lib.mb200_version.restype = ctypes.c_char_p
+        lib.mb200_plan_create.argtypes = [ctypes.POINTER(Cfg), ctypes.POINTER(vp)]
+        lib.mb200_plan_destroy.argtypes = [vp]
+        lib.mb200_plan_destroy.restype = None
+        lib.mb200_load_estimator.argtypes = [vp, ctypes.POINTER(Tensor), i, ctypes.c_char_p]
+        lib.mb200_load_generator.argtypes = [vp, ctypes.POINTER(Tensor), i]
+        lib.mb200_euler_schedule.argtypes = [i, ctypes.POINTER(f), ctypes.POINTER(f)]
+        lib.mb200_estimator_forward.argtypes = [vp, vp, vp, vp, vp, i, vp, i, i, vp, vp]
+        lib.mb200_cfm_decode.argtypes = [vp, vp, vp, vp, vp, i, i, i, vp, vp]
+        lib.mb200_hifigan_forward.argtypes = [vp, vp, i, i, vp, vp]
+        lib.mb200_synthesise.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp, vp, vp]
+        lib.mb200_synthesise_host.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp]
+        lib.mb200_launch_count.argtypes = [vp]
+        lib.mb200_launch_count.restype = ctypes.c_longlong
+        lib.mb200_workspace_bytes.argtypes = [vp]
+        lib.mb200_workspace_bytes.restype = ctypes.c_longlong
+        lib.mb200_test_conv1d.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, i, i, vp, vp]
+        lib.mb200_test_attention.argtypes = [vp, vp, vp, i, i, vp, vp]
+        _lib = lib
+        return lib
+
+
+def check(rc):
+    if rc != 0:
+        raise RuntimeError("matcha_b200: " + load().mb200_last_error().decode("utf-8", "replace"))
+
+
+def euler_schedule(n_steps):
+    """(t, dt) per step exactly as the CUDA path uses them (host-only call; no GPU needed)."""
+    lib = load()
+    ts = (ctypes.c_float * n_steps)()
+    dts = (ctypes.c_float * n_steps)()
+    check(lib.mb200_euler_schedule(n_steps, ts, dts))
+    return list(ts), list(dts)
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _dev_f32(t, device):
+    if t is None:
+        return None
+    return t.detach().to(device=device, dtype=torch.float32).contiguous()
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Plan:
+    """Owns one mb200_plan: packed weights, workspaces, CUDA graphs.  One per (precision, c_in, device)."""
+
+    def __init__(self, precision="fp16", c_in=160, force_simt=False, use_graph=True, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("matcha_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = load()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.precision = precision
+        self.c_in = c_in
+        cfg = Cfg(DTYPES[precision], c_in, int(force_simt), int(use_graph))
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_plan_create(ctypes.byref(cfg), ctypes.byref(handle)))
+        self.handle = handle
+        self._keep = []
+
+    def __del__(self):
+        h, self.handle = getattr(self, "handle", None), None
+        if h:
+            try:
+                self.lib.mb200_plan_destroy(h)
+            except Exception:
+                pass
+
+    # ---- weights
+    def _tensor_array(self, state_dict):
+        items = [(k, v.detach().to("cpu", torch.float32).contiguous()) for k, v in state_dict.items()
+                 if torch.is_tensor(v)]
+        arr = (Tensor * len(items))()
+        keep = []
+        for j, (k, v) in enumerate(items):
+            name = k.encode()
+            keep.append((name, v))
+            arr[j].name = name
+            arr[j].data = v.data_ptr()
+            arr[j].ndim = v.ndim
+            for d in range(v.ndim):
+                arr[j].shape[d] = v.shape[d]
+        return arr, len(items), keep
+
+    def load_estimator(self, state_dict, prefix="estimator."):
+        arr, n, keep = self._tensor_array(state_dict)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_load_estimator(self.handle, arr, n, prefix.encode()))
+        del keep
+
+    def load_generator(self, state_dict):
+        arr, n, keep = self._tensor_array(state_dict)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_load_generator(self.handle, arr, n))
+        del keep
+
+    # ---- compute
+    def estimator_forward(self, x, mask, mu, t, spks=None):
+        b, c, tt = x.shape
+        x, mask, mu, spks = (_dev_f32(v, self.device) for v in (x, mask, mu, spks))
+        t = _dev_f32(torch.as_tensor(t), self.device).reshape(-1)
+        batched = t.numel() > 1
+        if batched and t.numel() != b:
+            raise ValueError("t must be a scalar or have one value per batch element")
+        out = torch.empty(b, 80, tt, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_estimator_forward(self.handle, _ptr(x), _ptr(mask), _ptr(mu), _ptr(t), int(batched),
+                                                   _ptr(spks), b, tt, _ptr(out), _stream()))
+        return out
+
+    def cfm_decode(self, mu, mask, z, n_steps, spks=None):
+        b, c, tt = mu.shape
+        mu, mask, z, spks = (_dev_f32(v, self.device) for v in (mu, mask, z, spks))
+        out = torch.empty(b, 80, tt, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_cfm_decode(self.handle, _ptr(mu), _ptr(mask), _ptr(z), _ptr(spks), b, tt, int(n_steps),
+                                            _ptr(out), _stream()))
+        return out
+
+    def hifigan_forward(self, mel):
+        b, c, l = mel.shape
+        if c != 80:
+            raise ValueError("HiFi-GAN v1 expects 80 mel channels")
+        mel = _dev_f32(mel, self.device)
+        wav = torch.empty(b, 1, 256 * l, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_hifigan_forward(self.handle, _ptr(mel), b, l, _ptr(wav), _stream()))
+        return wav
+
+    def synthesise(self, mu, mask, z, n_steps, length, mel_mean, mel_std, spks=None):
+        """decode -> crop to `length` frames -> denormalise -> vocode.  Returns (decoded, mel, wav)."""
+        b, c, tt = mu.shape
+        mu, mask, z, spks = (_dev_f32(v, self.device) for v in (mu, mask, z, spks))
+        dec = torch.empty(b, 80, tt, device=self.device, dtype=torch.float32)
+        mel = torch.empty(b, 80, length, device=self.device, dtype=torch.float32)
+        wav = torch.empty(b, 1, 256 * length, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_synthesise(self.handle, _ptr(mu), _ptr(mask), _ptr(z), _ptr(spks), b, tt, int(n_steps),
+                                            int(length), float(mel_mean), float(mel_std), _ptr(dec), _ptr(mel),
+                                            _ptr(wav), _stream()))
+        return dec, mel, wav
+
+    def synthesise_host(self, mu, mask, z, n_steps, length, mel_mean, mel_std, spks=None, mel_out=None, wav_out=None):
+        """Host-buffer end-to-end call (H2D, hot path, D2H, sync).  Inputs are CPU fp32 tensors (ideally pinned)."""
+        b, c, tt = mu.shape
+        for v in (mu, mask, z, spks):
+            if v is not None and (v.is_cuda or v.dtype != torch.float32 or not v.is_contiguous()):
+                raise ValueError("synthesise_host takes contiguous fp32 CPU tensors")
+        if mel_out is None:
+            mel_out = torch.empty(b, 80, length, dtype=torch.float32).pin_memory()
+        if wav_out is None:
+            wav_out = torch.empty(b, 1, 256 * length, dtype=torch.float32).pin_memory()
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_synthesise_host(self.handle, _ptr(mu), _ptr(mask), _ptr(z), _ptr(spks), b, tt,
+                                                 int(n_steps), int(length), float(mel_mean), float(mel_std),
+                                                 _ptr(mel_out), _ptr(wav_out)))
+        return mel_out, wav_out
+
+    def launch_count(self):
+        return int(self.lib.mb200_launch_count(self.handle))
+
+    def workspace_bytes(self):
+        return int(self.lib.mb200_workspace_bytes(self.handle))
+
+    # ---- unit-test hooks
+    def test_conv1d(self, x, w, bias, dilation=1, stride=1, transposed=False):
+        b, cin, t = x.shape
+        k = w.shape[2]
+        cout = w.shape[1] if transposed else w.shape[0]
+        t_out = t * stride if transposed else t // stride
+        x = _dev_f32(x, self.device)
+        w = w.detach().to("cpu", torch.float32).contiguous()
+        bias = None if bias is None else bias.detach().to("cpu", torch.float32).contiguous()
+        y = torch.empty(b, cout, t_out, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_test_conv1d(self.handle, _ptr(x), _ptr(w), _ptr(bias), b, cin, cout, t, k, dilation,
+                                             stride, int(transposed), _ptr(y), _stream()))
+        return y
+
+    def test_attention(self, qkv, mask):
+        b, t, _ = qkv.shape
+        qkv, mask = _dev_f32(qkv, self.device), _dev_f32(mask, self.device)
+        out = torch.empty(b, t, 128, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_test_attention(self.handle, _ptr(qkv), _ptr(mask), b, t, _ptr(out), _stream()))
+        return out

@@ -1,0 +1,186 @@
+// extern "C" boundary (include/matcha_b200.h) and the unit-test hooks.
+#include <cstring>
+
+#include "plan.h"
+
+namespace mb {
+const char* last_error_cstr();
+void euler_schedule_host(int n_steps, float* ts, float* dts);
+
+void Plan::test_conv1d(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T, int K, int dil,
+                       int stride, bool transposed, float* y, cudaStream_t st) {
+  std::lock_guard<std::recursive_mutex> lk(mu_);
+  const int dtype = cfg.dtype;
+  const size_t es = esize(dtype);
+  const int cpad = Cin % 64 == 0 ? Cin : (Cin == 32 ? 32 : (Cin + 63) / 64 * 64);
+  PackedW W;
+  int T_out = T, T_o = T, view_rows = T, view_ld = cpad;
+  if (transposed) {
+    HostTensor wt{w, {Cin, Cout, K}};
+    W = pack_convT(wt, bias, stride);
+    T_o = T * stride;
+  } else if (stride == 2) {
+    if (K != 3 || T % 2 || cpad != Cin) throw Error("test_conv1d: stride 2 needs K == 3, even T and Cin % 64 == 0");
+    HostTensor wt{w, {Cout, Cin, K}};
+    W = pack_conv_stride2(wt, bias, Cin);
+    T_out = T / 2; T_o = T / 2; view_rows = T / 2; view_ld = 2 * Cin;
+  } else {
+    HostTensor wt{w, {Cout, Cin, K}};
+    W = pack_conv1d(wt, bias, dil, {{Cin, cpad}});
+  }
+  // stage: x (B,Cin,T) fp32 -> [B][T][cpad] operand dtype, zero padded channels
+  float* x_ntc = static_cast<float*>(dalloc(static_cast<size_t>(B) * T * Cin * 4));
+  void* xa = dalloc(static_cast<size_t>(B) * T * cpad * es);
+  float* y_ntc = static_cast<float*>(dalloc(static_cast<size_t>(B) * T_o * W.N * 4));
+  MB_CUDA(launch_bct_to_btc(x, x_ntc, B, Cin, T, st));
+  {
+    // reuse pack_mel's "first C channels, zero pad" only fits C == 80; do a generic strided convert instead
+    std::vector<float> tmp(static_cast<size_t>(B) * T * Cin);
+    MB_CUDA(cudaStreamSynchronize(st));
+    MB_CUDA(cudaMemcpy(tmp.data(), x_ntc, tmp.size() * 4, cudaMemcpyDeviceToHost));
+    std::vector<float> padded(static_cast<size_t>(B) * T * cpad, 0.f);
+    for (size_t r = 0; r < static_cast<size_t>(B) * T; ++r)
+      for (int c = 0; c < Cin; ++c) padded[r * cpad + c] = tmp[r * Cin + c];
+    void* up = upload_operand(padded);
+    MB_CUDA(cudaMemcpy(xa, up, padded.size() * es, cudaMemcpyDeviceToDevice));
+  }
+  EpiParams e{};
+  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f;
+  e.out0 = y_ntc; e.out0_ld = W.N; e.out0_f32 = 1;
+  Launch op = conv_op(W, Src{xa, view_ld, transposed || stride == 1 ? cpad : Cin, view_rows}, nullptr, B, T_out, e);
+  MB_CUDA(op(st));
+  // [B][T_o][N] -> (B, Cout, T_o): transpose all N channels, then copy the first Cout rows per batch element
+  float* y_full = static_cast<float*>(dalloc(static_cast<size_t>(B) * T_o * W.N * 4));
+  MB_CUDA(launch_btc_to_bct(y_ntc, y_full, B, W.N, T_o, st));
+  for (int b = 0; b < B; ++b)
+    MB_CUDA(cudaMemcpyAsync(y + static_cast<size_t>(b) * Cout * T_o, y_full + static_cast<size_t>(b) * W.N * T_o,
+                            static_cast<size_t>(Cout) * T_o * 4, cudaMemcpyDeviceToDevice, st));
+  MB_CUDA(cudaStreamSynchronize(st));
+  launches += 3;
+}
+
+void Plan::test_attention(const float* qkv, const float* mask, int B, int T, float* out, cudaStream_t st) {
+  std::lock_guard<std::recursive_mutex> lk(mu_);
+  const int dtype = cfg.dtype;
+  const size_t n_in = static_cast<size_t>(B) * T * 384, n_out = static_cast<size_t>(B) * T * 128;
+  std::vector<float> h(n_in);
+  MB_CUDA(cudaStreamSynchronize(st));
+  MB_CUDA(cudaMemcpy(h.data(), qkv, n_in * 4, cudaMemcpyDeviceToHost));
+  void* q = upload_operand(h);
+  void* o = dalloc(n_out * esize(dtype));
+  if (dtype == MB200_F32) MB_CUDA(launch_attention_simt<float>((const float*)q, mask, (float*)o, B, T, st));
+  else if (dtype == MB200_BF16) MB_CUDA(launch_attention_simt<__nv_bfloat16>((const __nv_bfloat16*)q, mask, (__nv_bfloat16*)o, B, T, st));
+  else MB_CUDA(launch_attention_simt<__half>((const __half*)q, mask, (__half*)o, B, T, st));
+  MB_CUDA(cudaStreamSynchronize(st));
+  if (dtype == MB200_F32) {
+    MB_CUDA(cudaMemcpy(out, o, n_out * 4, cudaMemcpyDeviceToDevice));
+  } else {
+    std::vector<uint16_t> raw(n_out);
+    MB_CUDA(cudaMemcpy(raw.data(), o, n_out * 2, cudaMemcpyDeviceToHost));
+    std::vector<float> f(n_out);
+    for (size_t i = 0; i < n_out; ++i) {
+      if (dtype == MB200_BF16) { __nv_bfloat16 v; std::memcpy(&v, &raw[i], 2); f[i] = __bfloat162float(v); }
+      else { __half v; std::memcpy(&v, &raw[i], 2); f[i] = __half2float(v); }
+    }
+    MB_CUDA(cudaMemcpy(out, f.data(), n_out * 4, cudaMemcpyHostToDevice));
+  }
+  launches += 1;
+}
+}  // namespace mb
+
+using mb::Plan;
+
+namespace {
+template <typename F>
+int guarded(F&& f) {
+  try {
+    f();
+    return 0;
+  } catch (const std::exception& e) {
+    mb::set_last_error(e.what());
+    return 1;
+  } catch (...) {
+    mb::set_last_error("unknown error");
+    return 1;
+  }
+}
+mb::StateDict to_state_dict(const mb200_tensor* t, int n, const char* prefix) {
+  mb::StateDict sd;
+  const std::string pre = prefix ? prefix : "";
+  for (int i = 0; i < n; ++i) {
+    std::string name = t[i].name;
+    if (!pre.empty()) {
+      if (name.compare(0, pre.size(), pre) != 0) continue;
+      name = name.substr(pre.size());
+    }
+    mb::HostTensor h{t[i].data, {}};
+    for (int d = 0; d < t[i].ndim; ++d) h.shape.push_back(t[i].shape[d]);
+    sd.emplace(name, std::move(h));
+  }
+  return sd;
+}
+Plan* P(mb200_plan* p) {
+  if (!p) throw mb::Error("null plan");
+  return reinterpret_cast<Plan*>(p);
+}
+}  // namespace
+
+extern "C" {
+
+const char* mb200_last_error(void) { return mb::last_error_cstr(); }
+const char* mb200_version(void) { return "matcha_b200 0.1 (sm_100a)"; }
+
+int mb200_plan_create(const mb200_cfg* cfg, mb200_plan** out) {
+  return guarded([&] {
+    if (!cfg || !out) throw mb::Error("null argument");
+    *out = reinterpret_cast<mb200_plan*>(new Plan(*cfg));
+  });
+}
+void mb200_plan_destroy(mb200_plan* plan) { delete reinterpret_cast<Plan*>(plan); }
+
+int mb200_load_estimator(mb200_plan* plan, const mb200_tensor* tensors, int n, const char* prefix) {
+  return guarded([&] { P(plan)->load_estimator(to_state_dict(tensors, n, prefix)); });
+}
+int mb200_load_generator(mb200_plan* plan, const mb200_tensor* tensors, int n) {
+  return guarded([&] { P(plan)->load_generator(to_state_dict(tensors, n, nullptr)); });
+}
+int mb200_euler_schedule(int n_steps, float* t_out, float* dt_out) {
+  return guarded([&] {
+    if (n_steps < 1 || !t_out || !dt_out) throw mb::Error("bad arguments");
+    mb::euler_schedule_host(n_steps, t_out, dt_out);
+  });
+}
+int mb200_estimator_forward(mb200_plan* plan, const float* x, const float* mask, const float* mu, const float* t,
+                            int t_is_batched, const float* spks, int B, int T, float* out, void* stream) {
+  return guarded([&] { P(plan)->estimator_forward(x, mask, mu, t, t_is_batched != 0, spks, B, T, out, static_cast<cudaStream_t>(stream)); });
+}
+int mb200_cfm_decode(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B, int T,
+                     int n_steps, float* out, void* stream) {
+  return guarded([&] { P(plan)->cfm_decode(mu, mask, z, spks, B, T, n_steps, out, static_cast<cudaStream_t>(stream)); });
+}
+int mb200_hifigan_forward(mb200_plan* plan, const float* mel, int B, int L, float* wav, void* stream) {
+  return guarded([&] { P(plan)->hifigan_forward(mel, L, 1.f, 0.f, B, L, wav, static_cast<cudaStream_t>(stream)); });
+}
+int mb200_synthesise(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B, int T,
+                     int n_steps, int L, float mel_mean, float mel_std, float* dec_out, float* mel_out, float* wav_out,
+                     void* stream) {
+  return guarded([&] {
+    P(plan)->synthesise(mu, mask, z, spks, B, T, n_steps, L, mel_mean, mel_std, dec_out, mel_out, wav_out, static_cast<cudaStream_t>(stream));
+  });
+}
+int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
+                          int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out) {
+  return guarded([&] { P(plan)->synthesise_host(mu, mask, z, spks, B, T, n_steps, L, mel_mean, mel_std, mel_out, wav_out); });
+}
+long long mb200_launch_count(const mb200_plan* plan) { return plan ? reinterpret_cast<const Plan*>(plan)->launches : 0; }
+long long mb200_workspace_bytes(const mb200_plan* plan) { return plan ? reinterpret_cast<const Plan*>(plan)->bytes_allocated : 0; }
+
+int mb200_test_conv1d(mb200_plan* plan, const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T,
+                      int K, int dilation, int stride, int transposed, float* y, void* stream) {
+  return guarded([&] { P(plan)->test_conv1d(x, w, bias, B, Cin, Cout, T, K, dilation, stride, transposed != 0, y, static_cast<cudaStream_t>(stream)); });
+}
+int mb200_test_attention(mb200_plan* plan, const float* qkv, const float* mask, int B, int T, float* out, void* stream) {
+  return guarded([&] { P(plan)->test_attention(qkv, mask, B, T, out, static_cast<cudaStream_t>(stream)); });
+}
+
+}  // extern "C"

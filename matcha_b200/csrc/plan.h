@@ -1,0 +1,165 @@
+// Host-side plan: packed weights, workspaces, TMA descriptors, launch programs and their CUDA graphs.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <functional>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/matcha_b200.h"
+#include "launch.h"
+
+namespace mb {
+
+struct Error : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+void set_last_error(const std::string& s);
+
+#define MB_CUDA(expr)                                                                                       \
+  do {                                                                                                      \
+    cudaError_t _e = (expr);                                                                                \
+    if (_e != cudaSuccess)                                                                                  \
+      throw ::mb::Error(std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" __FILE__ ":" + std::to_string(__LINE__) + ")"); \
+  } while (0)
+
+inline size_t esize(int dtype) { return dtype == MB200_F32 ? 4 : 2; }
+
+// Device allocation owned by the plan (freed with it).
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+// A reference state_dict tensor on the host.
+struct HostTensor {
+  const float* data;
+  std::vector<long long> shape;
+  long long numel() const { long long n = 1; for (auto s : shape) n *= s; return n; }
+};
+using StateDict = std::map<std::string, HostTensor>;
+
+// One conv / linear repacked as the GEMM B operand: [n_phases * N][K_total] in the plan dtype, K ordered
+// (tap, source, channel) with every source's channel count padded to the K chunk.
+struct PackedW {
+  void* w = nullptr;
+  float* bias = nullptr;     // [N] zero padded, may be null
+  int N = 0, n_valid = 0, K_total = 0, n_taps = 0, n_phases = 1;
+  int ntile = 0, kc = 0;
+  CUtensorMap tm{};          // valid in tensor-core modes
+  // tap table (source row offset, channel base in the source view) per phase
+  int tap_row[kMaxPhases][kMaxTaps] = {};
+  int tap_ch[kMaxPhases][kMaxTaps] = {};
+  int o_mul = 1;             // output rows per GEMM row (ConvTranspose stride)
+};
+
+struct Src {
+  const void* p;
+  int ld;       // row pitch of the view, elements
+  int ch;       // channels consumed (padded)
+  int rows;     // rows per batch element of the view
+};
+
+using Launch = std::function<cudaError_t(cudaStream_t)>;
+struct Program {
+  std::vector<Launch> ops;
+  cudaGraphExec_t graph = nullptr;
+  long long kernels = 0;  // kernel launches per run (memsets not counted)
+  std::vector<float> host_f32;  // small per-program host constants (Euler t schedule)
+};
+
+struct ResnetW {
+  PackedW conv1, conv2, res;
+  float *gn1_g, *gn1_b, *gn2_g, *gn2_b;
+};
+struct TransformerW {
+  PackedW qkv, out, ff1, ff2;
+  float *ln1_g, *ln1_b, *ln3_g, *ln3_b, *snake_a, *snake_invb;
+};
+struct EstimatorW {
+  bool loaded = false;
+  float *t_w1, *t_b1, *t_w2, *t_b2;   // time MLP fp32
+  float *t_wp, *t_bp;                 // six mlp.1 projections stacked [6*256][1024], [6*256]
+  ResnetW res[6];                     // down0, down1, mid0, mid1, up0, up1
+  TransformerW tr[6];
+  PackedW down0, down1, up0, up1, final_conv, final_proj;
+  float *fgn_g, *fgn_b;
+};
+struct GeneratorW {
+  bool loaded = false;
+  PackedW conv_pre, ups[4], c1[12][3], c2[12][3];
+  float* post_w = nullptr;  // [7][32] fp32
+  float post_b = 0.f;
+};
+
+class Plan {
+ public:
+  explicit Plan(const mb200_cfg& cfg);
+  ~Plan();
+  void load_estimator(const StateDict& sd);
+  void load_generator(const StateDict& sd);
+
+  void estimator_forward(const float* x, const float* mask, const float* mu, const float* t, bool batched,
+                         const float* spks, int B, int T, float* out, cudaStream_t st);
+  void cfm_decode(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
+                  float* out, cudaStream_t st);
+  void hifigan_forward(const float* mel, int Tsrc, float scale, float shift, int B, int L, float* wav, cudaStream_t st);
+  void synthesise(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps, int L,
+                  float mel_mean, float mel_std, float* dec_out, float* mel_out, float* wav_out, cudaStream_t st);
+  void synthesise_host(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
+                       int L, float mel_mean, float mel_std, float* mel_out, float* wav_out);
+  void test_conv1d(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T, int K, int dil,
+                   int stride, bool transposed, float* y, cudaStream_t st);
+  void test_attention(const float* qkv, const float* mask, int B, int T, float* out, cudaStream_t st);
+
+  long long launches = 0;
+  long long bytes_allocated = 0;
+  mb200_cfg cfg;
+
+  // ---- helpers shared by the translation units
+  bool tensor_core() const { return cfg.dtype != MB200_F32 && !cfg.force_simt; }
+  void* dalloc(size_t bytes);                       // plan-owned, zero-initialised
+  float* upload_f32(const float* host, size_t n);   // plan-owned
+  void* ensure(DevBuf& b, size_t bytes);            // grow-only workspace
+  void* upload_operand(const std::vector<float>& host);  // fp32 host -> plan dtype device
+  CUtensorMap tmap_act(const void* p, int ld, int rows, int B, int kc) const;
+  CUtensorMap tmap_w(const void* p, int K_total, int rows, int kc, int ntile) const;
+  // Generic weight repack. weight(n, c, j) with c the concatenated real input channel; segs = (real, padded) channels of
+  // each source; taps_j[phase][tap] = kernel index j.
+  PackedW pack_conv(const std::function<float(int, int, int)>& weight, const float* bias, int n_real, int n_pad,
+                    const std::vector<std::pair<int, int>>& segs, const std::vector<std::vector<int>>& taps_j);
+  PackedW pack_conv1d(const HostTensor& w, const float* bias, int dil, const std::vector<std::pair<int, int>>& segs,
+                      int n_pad = 0, float row_scale_first = 1.f, int scaled_rows = 0);
+  PackedW pack_conv_stride2(const HostTensor& w, const float* bias, int C);
+  PackedW pack_convT(const HostTensor& w, const float* bias, int stride);
+  Launch conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, EpiParams e);
+  void run(Program& prog, cudaStream_t st);
+
+ private:
+  std::vector<void*> owned_;
+  std::recursive_mutex mu_;
+  EstimatorW est_;
+  GeneratorW gen_;
+  // workspaces
+  DevBuf ws_est_[24];
+  DevBuf ws_voc_[8];
+  DevBuf ws_io_[8];
+  std::map<std::tuple<int, int, int, int, long long>, std::unique_ptr<Program>> decode_cache_;   // (B,T,steps,spk,ptr-key)
+  std::map<std::tuple<int, int>, std::unique_ptr<Program>> vocoder_cache_;
+
+  void build_estimator_step(Program& prog, int B, int T, const float* tproj, int tproj_bstride, bool euler, float dt,
+                            float* v_out_ntc);
+  void build_time_embed(Program& prog, const float* t_dev, int n_t);
+  void build_vocoder(Program& prog, int B, int L, float* wav);
+  void estimator_buffers(int B, int T);
+  void vocoder_buffers(int B, int L);
+  friend struct PlanAccess;
+};
+
+}  // namespace mb

@@ -1,0 +1,280 @@
+// Plan infrastructure: allocation, TMA descriptor encoding, weight repacking, conv op construction, program
+// execution / CUDA-graph capture.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cudaTypedefs.h>
+
+#include <cstring>
+
+#include "plan.h"
+
+namespace mb {
+
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& s) { g_last_error = s; }
+const char* last_error_cstr() { return g_last_error.c_str(); }
+
+static PFN_cuTensorMapEncodeTiled get_encode() {
+  static PFN_cuTensorMapEncodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !p)
+      throw Error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
+  }
+  return fn;
+}
+
+Plan::Plan(const mb200_cfg& c) : cfg(c) {
+  if (cfg.dtype != MB200_F32 && cfg.dtype != MB200_BF16 && cfg.dtype != MB200_F16) throw Error("unknown dtype");
+  if (cfg.c_in != 160 && cfg.c_in != 224) throw Error("c_in must be 160 (LJSpeech) or 224 (VCTK, 64-dim speaker embedding)");
+  int dev = 0, major = 0;
+  MB_CUDA(cudaGetDevice(&dev));
+  MB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
+}
+
+Plan::~Plan() {
+  for (auto& kv : decode_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
+  for (auto& kv : vocoder_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
+  for (void* p : owned_) cudaFree(p);
+  for (auto* arr : {ws_est_, ws_voc_, ws_io_}) (void)arr;
+  for (auto& b : ws_est_) if (b.p) cudaFree(b.p);
+  for (auto& b : ws_voc_) if (b.p) cudaFree(b.p);
+  for (auto& b : ws_io_) if (b.p) cudaFree(b.p);
+}
+
+void* Plan::dalloc(size_t bytes) {
+  void* p = nullptr;
+  bytes = (bytes + 255) & ~size_t(255);
+  MB_CUDA(cudaMalloc(&p, bytes));
+  MB_CUDA(cudaMemset(p, 0, bytes));
+  owned_.push_back(p);
+  bytes_allocated += static_cast<long long>(bytes);
+  return p;
+}
+
+float* Plan::upload_f32(const float* host, size_t n) {
+  float* d = static_cast<float*>(dalloc(n * sizeof(float)));
+  MB_CUDA(cudaMemcpy(d, host, n * sizeof(float), cudaMemcpyHostToDevice));
+  return d;
+}
+
+void* Plan::ensure(DevBuf& b, size_t bytes) {
+  if (b.bytes >= bytes) return b.p;
+  // workspaces are referenced by cached programs: growing one invalidates them
+  for (auto& kv : decode_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
+  for (auto& kv : vocoder_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
+  decode_cache_.clear();
+  vocoder_cache_.clear();
+  if (b.p) { MB_CUDA(cudaDeviceSynchronize()); cudaFree(b.p); bytes_allocated -= static_cast<long long>(b.bytes); }
+  bytes = (bytes + 1023) & ~size_t(1023);
+  MB_CUDA(cudaMalloc(&b.p, bytes));
+  MB_CUDA(cudaMemset(b.p, 0, bytes));
+  b.bytes = bytes;
+  bytes_allocated += static_cast<long long>(bytes);
+  return b.p;
+}
+
+void* Plan::upload_operand(const std::vector<float>& host) {
+  const size_t n = host.size();
+  if (cfg.dtype == MB200_F32) return upload_f32(host.data(), n);
+  std::vector<uint16_t> tmp(n);
+  if (cfg.dtype == MB200_BF16) {
+    for (size_t i = 0; i < n; ++i) { __nv_bfloat16 h = __float2bfloat16_rn(host[i]); std::memcpy(&tmp[i], &h, 2); }
+  } else {
+    for (size_t i = 0; i < n; ++i) { __half h = __float2half_rn(host[i]); std::memcpy(&tmp[i], &h, 2); }
+  }
+  void* d = dalloc(n * 2);
+  MB_CUDA(cudaMemcpy(d, tmp.data(), n * 2, cudaMemcpyHostToDevice));
+  return d;
+}
+
+// Activation view [B][rows][ld] (channels contiguous): 3-D map, box = kc channels x 128 rows x 1 batch element.
+// Rows outside [0, rows) are zero-filled by TMA: that IS the conv's zero padding at the utterance edges.
+CUtensorMap Plan::tmap_act(const void* p, int ld, int rows, int B, int kc) const {
+  CUtensorMap m;
+  const CUtensorMapDataType dt = cfg.dtype == MB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(ld), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(B)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 2, static_cast<cuuint64_t>(ld) * 2 * rows};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(kc), 128, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = get_encode()(&m, dt, 3, const_cast<void*>(p), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                            kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled(activation) failed: " + std::to_string(static_cast<int>(r)));
+  return m;
+}
+
+CUtensorMap Plan::tmap_w(const void* p, int K_total, int rows, int kc, int ntile) const {
+  CUtensorMap m;
+  const CUtensorMapDataType dt = cfg.dtype == MB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(K_total), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(K_total) * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kc), static_cast<cuuint32_t>(ntile)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = get_encode()(&m, dt, 2, const_cast<void*>(p), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                            kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled(weights) failed: " + std::to_string(static_cast<int>(r)));
+  return m;
+}
+
+PackedW Plan::pack_conv(const std::function<float(int, int, int)>& weight, const float* bias, int n_real, int n_pad,
+                        const std::vector<std::pair<int, int>>& segs, const std::vector<std::vector<int>>& taps_j) {
+  PackedW W;
+  W.n_phases = static_cast<int>(taps_j.size());
+  W.n_taps = static_cast<int>(taps_j[0].size());
+  if (W.n_taps > kMaxTaps || W.n_phases > kMaxPhases) throw Error("pack_conv: too many taps/phases");
+  int pad_total = 0;
+  bool all64 = true;
+  for (auto& s : segs) { pad_total += s.second; if (s.second % 64) all64 = false; if (s.second % 32) throw Error("pack_conv: channel padding must be a multiple of 32"); }
+  W.kc = all64 ? 64 : 32;
+  W.N = n_pad;
+  W.n_valid = n_real;
+  W.K_total = W.n_taps * pad_total;
+  W.ntile = (n_pad % 256 == 0) ? 256 : (n_pad % 128 == 0) ? 128 : (n_pad % 64 == 0) ? 64 : 32;
+  if (n_pad % 32) throw Error("pack_conv: N must be a multiple of 32");
+  if (W.kc == 32 && W.ntile != 32) throw Error("pack_conv: 32-channel K chunks are only built for N tile 32");
+  std::vector<float> host(static_cast<size_t>(W.n_phases) * n_pad * W.K_total, 0.f);
+  for (int ph = 0; ph < W.n_phases; ++ph)
+    for (int n = 0; n < n_real; ++n) {
+      float* row = host.data() + (static_cast<size_t>(ph) * n_pad + n) * W.K_total;
+      for (int tp = 0; tp < W.n_taps; ++tp) {
+        int koff = tp * pad_total, cglob = 0;
+        for (auto& s : segs) {
+          for (int c = 0; c < s.first; ++c) row[koff + c] = weight(n, cglob + c, taps_j[ph][tp]);
+          koff += s.second;
+          cglob += s.first;
+        }
+      }
+    }
+  W.w = upload_operand(host);
+  if (bias) {
+    std::vector<float> bp(n_pad, 0.f);
+    for (int n = 0; n < n_real; ++n) bp[n] = bias[n];
+    W.bias = upload_f32(bp.data(), n_pad);
+  }
+  if (tensor_core()) W.tm = tmap_w(W.w, W.K_total, W.n_phases * n_pad, W.kc, W.ntile);
+  return W;
+}
+
+// Conv1d weight (Cout, Cin, K), "same" padding, dilation dil.  Optionally scales the first `scaled_rows` output rows
+// (used to fold the 1/sqrt(head_dim) attention scale into W_q).
+PackedW Plan::pack_conv1d(const HostTensor& w, const float* bias, int dil, const std::vector<std::pair<int, int>>& segs,
+                          int n_pad, float row_scale_first, int scaled_rows) {
+  const int Cout = static_cast<int>(w.shape[0]), Cin = static_cast<int>(w.shape[1]);
+  const int K = w.shape.size() > 2 ? static_cast<int>(w.shape[2]) : 1;
+  int real = 0;
+  for (auto& s : segs) real += s.first;
+  if (real != Cin) throw Error("pack_conv1d: channel segments do not add up to Cin");
+  if (!n_pad) n_pad = (Cout + 31) / 32 * 32;
+  std::vector<std::vector<int>> taps(1);
+  for (int j = 0; j < K; ++j) taps[0].push_back(j);
+  const float* d = w.data;
+  PackedW W = pack_conv(
+      [&](int n, int c, int j) { return d[(static_cast<size_t>(n) * Cin + c) * K + j] * (n < scaled_rows ? row_scale_first : 1.f); },
+      bias, Cout, n_pad, segs, taps);
+  for (int j = 0; j < K; ++j) { W.tap_row[0][j] = (j - (K - 1) / 2) * dil; W.tap_ch[0][j] = 0; }
+  return W;
+}
+
+// Conv1d(C, Cout, 3, stride 2, padding 1) (decoder.py:67) on the [T/2][2C] view of the input:
+// out[t] = w0 x[2t-1] + w1 x[2t] + w2 x[2t+1]  ->  taps (row -1, ch C), (row 0, ch 0), (row 0, ch C).
+PackedW Plan::pack_conv_stride2(const HostTensor& w, const float* bias, int C) {
+  PackedW W = pack_conv1d(w, bias, 1, {{C, C}});
+  W.tap_row[0][0] = -1; W.tap_ch[0][0] = C;
+  W.tap_row[0][1] = 0;  W.tap_ch[0][1] = 0;
+  W.tap_row[0][2] = 0;  W.tap_ch[0][2] = C;
+  return W;
+}
+
+// ConvTranspose1d weight (Cin, Cout, K) with K == 2*stride, padding (K-stride)/2 (decoder.py:144; hifigan/models.py:158-169).
+// Output phase ph (t = stride*m + ph) is a 2-tap conv: j = ph + p + stride*delta reads input row m - delta.
+PackedW Plan::pack_convT(const HostTensor& w, const float* bias, int stride) {
+  const int Cin = static_cast<int>(w.shape[0]), Cout = static_cast<int>(w.shape[1]), K = static_cast<int>(w.shape[2]);
+  if (K != 2 * stride) throw Error("pack_convT: only kernel == 2*stride is supported");
+  const int p = (K - stride) / 2;
+  std::vector<std::vector<int>> taps(stride);
+  int rows[kMaxPhases][2];
+  for (int ph = 0; ph < stride; ++ph) {
+    const int d0 = (ph + p < stride) ? 0 : -1;
+    for (int q = 0; q < 2; ++q) {
+      const int delta = d0 + q;
+      taps[ph].push_back(ph + p + stride * delta);
+      rows[ph][q] = -delta;
+    }
+  }
+  const float* d = w.data;
+  const int cpad = (Cin + 63) / 64 * 64;
+  PackedW W = pack_conv([&](int n, int c, int j) { return d[(static_cast<size_t>(c) * Cout + n) * K + j]; }, bias, Cout,
+                        (Cout + 31) / 32 * 32, {{Cin, cpad}}, taps);
+  for (int ph = 0; ph < stride; ++ph)
+    for (int q = 0; q < 2; ++q) { W.tap_row[ph][q] = rows[ph][q]; W.tap_ch[ph][q] = 0; }
+  W.o_mul = stride;
+  return W;
+}
+
+Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, EpiParams e) {
+  ConvLaunch L{};
+  ConvGeom& g = L.g;
+  g.B = B; g.T_in = s0.rows; g.T_out = T_out;
+  g.n_src = s1 ? 2 : 1;
+  g.src_ch[0] = s0.ch; g.src_ld[0] = s0.ld;
+  g.src_ch[1] = s1 ? s1->ch : 0; g.src_ld[1] = s1 ? s1->ld : 0;
+  g.n_taps = W.n_taps; g.n_phases = W.n_phases;
+  std::memcpy(g.tap_row, W.tap_row, sizeof(g.tap_row));
+  std::memcpy(g.tap_ch, W.tap_ch, sizeof(g.tap_ch));
+  g.N = W.N; g.K_total = W.K_total;
+  if (W.n_taps * (g.src_ch[0] + g.src_ch[1]) != W.K_total) throw Error("conv_op: sources do not match the packed weight K");
+  if (s1 && s1->rows != s0.rows) throw Error("conv_op: concat sources differ in length");
+  e.o_mul = W.o_mul; e.o_phase_step = 1; e.T_o = T_out * W.o_mul; e.n_valid = W.n_valid; e.bias = W.bias;
+  L.e = e;
+  L.a[0] = s0.p; L.a[1] = s1 ? s1->p : s0.p;
+  L.w = W.w; L.ntile = W.ntile; L.kc = W.kc;
+  if (e.ln_out && (W.N != 256 || !tensor_core())) throw Error("conv_op: fused LayerNorm needs the tensor-core kernel and N == 256");
+  if (tensor_core()) {
+    L.tmA[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc);
+    L.tmA[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc) : L.tmA[0];
+    L.tmW = W.tm;
+  }
+  const int dtype = cfg.dtype;
+  const bool tc = tensor_core();
+  return [L, dtype, tc](cudaStream_t st) -> cudaError_t {
+    if (dtype == MB200_F32) return launch_conv_simt<float>(L, st);
+    if (dtype == MB200_BF16) return tc ? launch_conv_umma<__nv_bfloat16>(L, st) : launch_conv_simt<__nv_bfloat16>(L, st);
+    return tc ? launch_conv_umma<__half>(L, st) : launch_conv_simt<__half>(L, st);
+  };
+}
+
+void Plan::run(Program& prog, cudaStream_t st) {
+  if (prog.graph) {
+    MB_CUDA(cudaGraphLaunch(prog.graph, st));
+    launches += prog.kernels;
+    return;
+  }
+  for (auto& op : prog.ops) MB_CUDA(op(st));
+  launches += prog.kernels;
+  if (cfg.use_graph) {
+    // The eager pass above already produced this call's result (and configured every kernel); record the same
+    // launches into a graph for the following calls.  Capture happens on a private stream: the caller's may be
+    // the legacy default stream, which cannot be captured.
+    cudaStream_t cs;
+    MB_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    cudaGraph_t graph = nullptr;
+    cudaError_t err = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+    if (err == cudaSuccess) {
+      for (auto& op : prog.ops) { err = op(cs); if (err != cudaSuccess) break; }
+      cudaError_t e2 = cudaStreamEndCapture(cs, &graph);
+      if (err == cudaSuccess) err = e2;
+    }
+    if (err == cudaSuccess) err = cudaGraphInstantiate(&prog.graph, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    cudaStreamDestroy(cs);
+    if (err != cudaSuccess) { prog.graph = nullptr; throw Error(std::string("CUDA graph capture failed: ") + cudaGetErrorString(err)); }
+  }
+}
+
+}  // namespace mb

@@ -53,7 +53,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // Bounded wait: a pipeline bug must surface as a trapped launch (an error code at the C ABI),
 // never as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+  for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
     if (mbar_try_wait(bar, parity)) return;
   }
   __trap();

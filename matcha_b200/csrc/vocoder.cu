@@ -1,0 +1,210 @@
+// HiFi-GAN v1 generator (matcha/hifigan/models.py:149-197) as a launch program: every Conv1d / ConvTranspose1d is
+// a conv-GEMM launch; LeakyReLU, residual adds, the 3-branch mean and the stage hand-over live in the epilogues.
+#include <cmath>
+
+#include "plan.h"
+
+namespace mb {
+
+namespace {
+enum VocBuf { V_MEL, V_A, V_X, V_XL, V_R, V_RL, V_C1, V_SUM };
+const int kRates[4] = {8, 8, 2, 2};
+const int kKernels[3] = {3, 7, 11};
+const int kDils[3] = {1, 3, 5};
+
+const HostTensor& need(const StateDict& sd, const std::string& k) {
+  auto it = sd.find(k);
+  if (it == sd.end()) throw Error("generator state_dict is missing '" + k + "'");
+  return it->second;
+}
+// Effective weight for either key layout: plain `weight`, or weight_norm's g * v / ||v|| with the norm over all dims
+// but 0 (old-style torch.nn.utils.weight_norm, dim=0; matcha/hifigan/models.py:20-87,154-177,199-206).
+HostTensor effective_weight(const StateDict& sd, const std::string& name, std::vector<std::vector<float>>& keep) {
+  auto it = sd.find(name + ".weight");
+  if (it != sd.end()) return it->second;
+  const HostTensor& g = need(sd, name + ".weight_g");
+  const HostTensor& v = need(sd, name + ".weight_v");
+  const long long d0 = v.shape[0], inner = v.numel() / d0;
+  if (g.numel() != d0) throw Error("weight_g of '" + name + "' does not match weight_v");
+  keep.emplace_back(static_cast<size_t>(v.numel()));
+  std::vector<float>& w = keep.back();
+  for (long long i = 0; i < d0; ++i) {
+    double ss = 0.0;
+    for (long long j = 0; j < inner; ++j) { const double x = v.data[i * inner + j]; ss += x * x; }
+    const float nrm = static_cast<float>(std::sqrt(ss));
+    const float s = g.data[i] / nrm;
+    for (long long j = 0; j < inner; ++j) w[i * inner + j] = v.data[i * inner + j] * s;
+  }
+  return HostTensor{w.data(), v.shape};
+}
+EpiParams epi() {
+  EpiParams e{};
+  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f; e.o_mul = 1;
+  return e;
+}
+}  // namespace
+
+void Plan::load_generator(const StateDict& sd) {
+  std::lock_guard<std::recursive_mutex> lk(mu_);
+  std::vector<std::vector<float>> keep;
+  GeneratorW& G = gen_;
+  {
+    HostTensor w = effective_weight(sd, "conv_pre", keep);
+    if (w.shape != std::vector<long long>{512, 80, 7}) throw Error("conv_pre.weight must be (512,80,7): only HiFi-GAN v1 is supported");
+    G.conv_pre = pack_conv1d(w, need(sd, "conv_pre.bias").data, 1, {{80, 128}});
+  }
+  int ch = 512;
+  for (int i = 0; i < 4; ++i) {
+    HostTensor w = effective_weight(sd, "ups." + std::to_string(i), keep);
+    if (w.shape != std::vector<long long>{ch, ch / 2, 2 * kRates[i]}) throw Error("ups." + std::to_string(i) + " has an unexpected shape");
+    G.ups[i] = pack_convT(w, need(sd, "ups." + std::to_string(i) + ".bias").data, kRates[i]);
+    ch /= 2;
+    for (int j = 0; j < 3; ++j)
+      for (int m = 0; m < 3; ++m) {
+        const std::string p = "resblocks." + std::to_string(3 * i + j) + ".";
+        HostTensor w1 = effective_weight(sd, p + "convs1." + std::to_string(m), keep);
+        HostTensor w2 = effective_weight(sd, p + "convs2." + std::to_string(m), keep);
+        if (w1.shape != std::vector<long long>{ch, ch, kKernels[j]}) throw Error(p + "convs1 has an unexpected shape");
+        G.c1[3 * i + j][m] = pack_conv1d(w1, need(sd, p + "convs1." + std::to_string(m) + ".bias").data, kDils[m], {{ch, ch}});
+        G.c2[3 * i + j][m] = pack_conv1d(w2, need(sd, p + "convs2." + std::to_string(m) + ".bias").data, 1, {{ch, ch}});
+      }
+  }
+  {
+    HostTensor w = effective_weight(sd, "conv_post", keep);   // (1, 32, 7) -> [7][32]
+    std::vector<float> pw(7 * 32);
+    for (int c = 0; c < 32; ++c)
+      for (int j = 0; j < 7; ++j) pw[j * 32 + c] = w.data[c * 7 + j];
+    G.post_w = upload_f32(pw.data(), pw.size());
+    G.post_b = need(sd, "conv_post.bias").data[0];
+  }
+  G.loaded = true;
+  vocoder_cache_.clear();
+}
+
+void Plan::vocoder_buffers(int B, int L) {
+  const size_t es = esize(cfg.dtype);
+  const size_t bl = static_cast<size_t>(B) * L;
+  ensure(ws_voc_[V_MEL], bl * 128 * es);
+  for (int b : {V_A, V_X, V_XL, V_R, V_RL, V_C1, V_SUM}) ensure(ws_voc_[b], bl * 8192 * es);
+}
+
+// Everything between the packed mel and the conv_post input; conv_post itself writes to the caller's buffer and is
+// launched outside the cached program.
+void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
+  const int f32 = cfg.dtype == MB200_F32;
+  auto buf = [&](int i) { return ws_voc_[i].p; };
+  auto add = [&](Launch l) { prog.ops.push_back(std::move(l)); prog.kernels++; };
+  const GeneratorW& G = gen_;
+  {  // conv_pre, then the first stage's leaky_relu(0.1) (models.py:182,184)
+    EpiParams e = epi();
+    e.out0 = buf(V_A); e.out0_ld = 512; e.out0_f32 = f32; e.out0_slope = 0.1f;
+    add(conv_op(G.conv_pre, Src{buf(V_MEL), 128, 128, L}, nullptr, B, L, e));
+  }
+  int ch = 512, len = L;
+  for (int i = 0; i < 4; ++i) {
+    const int C = ch / 2;
+    {  // ups[i]: x and leaky_relu(x) for the three ResBlocks (models.py:185, :92)
+      EpiParams e = epi();
+      e.out0 = buf(V_X); e.out0_ld = C; e.out0_f32 = f32;
+      e.out1 = buf(V_XL); e.out1_ld = C; e.out1_slope = 0.1f;
+      add(conv_op(G.ups[i], Src{buf(V_A), ch, ch, len}, nullptr, B, len, e));
+    }
+    len *= kRates[i];
+    ch = C;
+    for (int j = 0; j < 3; ++j) {
+      for (int m = 0; m < 3; ++m) {
+        const PackedW& W1 = G.c1[3 * i + j][m];
+        const PackedW& W2 = G.c2[3 * i + j][m];
+        {  // xt = lrelu(c1(lrelu(r)))   (models.py:92-94)
+          EpiParams e = epi();
+          e.out0 = buf(V_C1); e.out0_ld = C; e.out0_f32 = f32; e.out0_slope = 0.1f;
+          add(conv_op(W1, Src{m == 0 ? buf(V_XL) : buf(V_RL), C, C, len}, nullptr, B, len, e));
+        }
+        EpiParams e = epi();  // r = c2(xt) + r   (models.py:95-96)
+        e.resid = m == 0 ? buf(V_X) : buf(V_R); e.resid_ld = C; e.resid_f32 = f32;
+        if (m < 2) {
+          e.out0 = buf(V_R); e.out0_ld = C; e.out0_f32 = f32;
+          e.out1 = buf(V_RL); e.out1_ld = C; e.out1_slope = 0.1f;
+        } else if (j == 0) {
+          e.out0 = buf(V_SUM); e.out0_ld = C; e.out0_f32 = f32;
+        } else if (j == 1) {
+          e.resid2 = buf(V_SUM); e.resid2_ld = C; e.resid2_f32 = f32;
+          e.out0 = buf(V_SUM); e.out0_ld = C; e.out0_f32 = f32;
+        } else {  // x = xs / 3, then the next consumer's leaky_relu: 0.1 inside the loop, 0.01 before conv_post (:192-193)
+          e.resid2 = buf(V_SUM); e.resid2_ld = C; e.resid2_f32 = f32;
+          e.scale = 1.f / 3.f;
+          e.out0 = buf(V_A); e.out0_ld = C; e.out0_f32 = f32; e.out0_slope = i == 3 ? 0.01f : 0.1f;
+        }
+        add(conv_op(W2, Src{buf(V_C1), C, C, len}, nullptr, B, len, e));
+      }
+    }
+  }
+}
+
+}  // namespace mb
+
+namespace mb {
+
+void Plan::hifigan_forward(const float* mel, int Tsrc, float scale, float shift, int B, int L, float* wav, cudaStream_t st) {
+  std::lock_guard<std::recursive_mutex> lk(mu_);
+  if (!gen_.loaded) throw Error("generator weights are not loaded");
+  if (B < 1 || L < 1) throw Error("empty vocoder input");
+  vocoder_buffers(B, L);
+  const int dtype = cfg.dtype;
+  void* melp = ws_voc_[V_MEL].p;
+  if (dtype == MB200_F32) MB_CUDA(launch_pack_mel<float>(mel, Tsrc, scale, shift, (float*)melp, 128, B, L, st));
+  else if (dtype == MB200_BF16) MB_CUDA(launch_pack_mel<__nv_bfloat16>(mel, Tsrc, scale, shift, (__nv_bfloat16*)melp, 128, B, L, st));
+  else MB_CUDA(launch_pack_mel<__half>(mel, Tsrc, scale, shift, (__half*)melp, 128, B, L, st));
+  auto key = std::make_tuple(B, L);
+  auto it = vocoder_cache_.find(key);
+  if (it == vocoder_cache_.end()) {
+    auto prog = std::make_unique<Program>();
+    build_vocoder(*prog, B, L, nullptr);
+    it = vocoder_cache_.emplace(key, std::move(prog)).first;
+  }
+  run(*it->second, st);
+  const long Lw = static_cast<long>(L) * 256;
+  const void* a = ws_voc_[V_A].p;
+  if (dtype == MB200_F32) MB_CUDA(launch_conv_post<float>((const float*)a, gen_.post_w, gen_.post_b, wav, B, Lw, st));
+  else if (dtype == MB200_BF16) MB_CUDA(launch_conv_post<__nv_bfloat16>((const __nv_bfloat16*)a, gen_.post_w, gen_.post_b, wav, B, Lw, st));
+  else MB_CUDA(launch_conv_post<__half>((const __half*)a, gen_.post_w, gen_.post_b, wav, B, Lw, st));
+  launches += 2;
+}
+
+void Plan::synthesise(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
+                      int L, float mel_mean, float mel_std, float* dec_out, float* mel_out, float* wav_out, cudaStream_t st) {
+  std::lock_guard<std::recursive_mutex> lk(mu_);
+  if (L < 1 || L > T) throw Error("vocoder length L must be in [1, T]");
+  if (!wav_out) throw Error("wav_out must not be NULL");
+  float* dec = dec_out;
+  if (!dec) dec = static_cast<float*>(ensure(ws_io_[1], static_cast<size_t>(B) * 80 * T * 4));
+  cfm_decode(mu, mask, z, spks, B, T, n_steps, dec, st);
+  if (mel_out) { MB_CUDA(launch_affine_crop(dec, T, mel_std, mel_mean, mel_out, B, 80, L, st)); launches += 1; }
+  // tanh already bounds the waveform to [-1, 1]: cli.py:118's clamp is the identity here
+  hifigan_forward(dec, T, mel_std, mel_mean, B, L, wav_out, st);
+}
+
+void Plan::synthesise_host(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
+                           int L, float mel_mean, float mel_std, float* mel_out, float* wav_out) {
+  std::lock_guard<std::recursive_mutex> lk(mu_);
+  const size_t n_mel = static_cast<size_t>(B) * 80 * T, n_mask = static_cast<size_t>(B) * T;
+  const size_t n_spk = spks ? static_cast<size_t>(B) * (cfg.c_in - 160) : 0;
+  const size_t n_out_mel = static_cast<size_t>(B) * 80 * L, n_wav = static_cast<size_t>(B) * 256 * L;
+  float* d_mu = static_cast<float*>(ensure(ws_io_[2], n_mel * 4));
+  float* d_z = static_cast<float*>(ensure(ws_io_[3], n_mel * 4));
+  float* d_mask = static_cast<float*>(ensure(ws_io_[4], n_mask * 4));
+  float* d_spk = spks ? static_cast<float*>(ensure(ws_io_[5], n_spk * 4)) : nullptr;
+  float* d_melo = static_cast<float*>(ensure(ws_io_[6], n_out_mel * 4));
+  float* d_wav = static_cast<float*>(ensure(ws_io_[7], n_wav * 4));
+  cudaStream_t st = nullptr;  // legacy default stream: ordered against everything else in the process
+  MB_CUDA(cudaMemcpyAsync(d_mu, mu, n_mel * 4, cudaMemcpyHostToDevice, st));
+  MB_CUDA(cudaMemcpyAsync(d_z, z, n_mel * 4, cudaMemcpyHostToDevice, st));
+  MB_CUDA(cudaMemcpyAsync(d_mask, mask, n_mask * 4, cudaMemcpyHostToDevice, st));
+  if (spks) MB_CUDA(cudaMemcpyAsync(d_spk, spks, n_spk * 4, cudaMemcpyHostToDevice, st));
+  synthesise(d_mu, d_mask, d_z, d_spk, B, T, n_steps, L, mel_mean, mel_std, nullptr, mel_out ? d_melo : nullptr, d_wav, st);
+  if (mel_out) MB_CUDA(cudaMemcpyAsync(mel_out, d_melo, n_out_mel * 4, cudaMemcpyDeviceToHost, st));
+  MB_CUDA(cudaMemcpyAsync(wav_out, d_wav, n_wav * 4, cudaMemcpyDeviceToHost, st));
+  MB_CUDA(cudaStreamSynchronize(st));
+}
+
+}  // namespace mb
