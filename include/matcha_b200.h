@@ -80,6 +80,13 @@ long long mb200_launch_count(const mb200_plan* plan);
 /* Device-memory footprint of the plan's workspaces and weights, bytes. */
 long long mb200_workspace_bytes(const mb200_plan* plan);
 
+/* Built-in profiler.  While on, launch programs run eagerly (no CUDA graph) with a CUDA-event pair around every
+ * operation on the launching stream.  mb200_get_profile fills out[6][4][3]: [region][kind] = {launches, milliseconds,
+ * algorithmic FLOPs}; region 0 = estimator, 1..4 = vocoder stages (conv_pre in 1), 5 = other; kind 0 = conv-GEMM,
+ * 1 = attention, 2 = elementwise / small kernels, 3 = memset / memcpy.  Turning it on or off zeroes the counters. */
+int mb200_set_profiling(mb200_plan* plan, int on);
+int mb200_get_profile(const mb200_plan* plan, double* out);
+
 /* Unit-test hook: one Conv1d / ConvTranspose1d (+ bias) through the conv-GEMM kernel of the plan's mode.
  * x (B,Cin,T) fp32 device, w reference layout HOST fp32 ((Cout,Cin,K) or (Cin,Cout,K) when transposed), bias HOST (Cout)
  * or NULL, y (B,Cout,T_out) fp32 device.  stride applies to Conv1d (1|2) or ConvTranspose1d (K == 2*stride). */

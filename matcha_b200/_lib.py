@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_test_conv1d", "mb200_test_attention",
+    "mb200_workspace_bytes", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention",
 ]
 
 
@@ -65,6 +65,8 @@ def load():
         lib.mb200_launch_count.restype = ctypes.c_longlong
         lib.mb200_workspace_bytes.argtypes = [vp]
         lib.mb200_workspace_bytes.restype = ctypes.c_longlong
+        lib.mb200_set_profiling.argtypes = [vp, i]
+        lib.mb200_get_profile.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
         lib.mb200_test_conv1d.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, i, i, vp, vp]
         lib.mb200_test_attention.argtypes = [vp, vp, vp, i, i, vp, vp]
         _lib = lib
@@ -213,6 +215,21 @@ class Plan:
                                                  int(n_steps), int(length), float(mel_mean), float(mel_std),
                                                  _ptr(mel_out), _ptr(wav_out)))
         return mel_out, wav_out
+
+    def set_profiling(self, on):
+        check(self.lib.mb200_set_profiling(self.handle, int(on)))
+
+    def get_profile(self):
+        """{(region, kind): (launches, ms, flops)} for the non-empty slots; see include/matcha_b200.h."""
+        buf = (ctypes.c_double * (6 * 4 * 3))()
+        check(self.lib.mb200_get_profile(self.handle, buf))
+        out = {}
+        for r in range(6):
+            for k in range(4):
+                n, ms, fl = buf[(r * 4 + k) * 3:(r * 4 + k) * 3 + 3]
+                if n:
+                    out[(r, k)] = (int(n), ms, fl)
+        return out
 
     def launch_count(self):
         return int(self.lib.mb200_launch_count(self.handle))

@@ -173,6 +173,19 @@ int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, 
   return guarded([&] { P(plan)->synthesise_host(mu, mask, z, spks, B, T, n_steps, L, mel_mean, mel_std, mel_out, wav_out); });
 }
 long long mb200_launch_count(const mb200_plan* plan) { return plan ? reinterpret_cast<const Plan*>(plan)->launches : 0; }
+int mb200_set_profiling(mb200_plan* plan, int on) {
+  return guarded([&] {
+    Plan* p = P(plan);
+    p->profiling = on != 0;
+    std::memset(p->prof, 0, sizeof(p->prof));
+  });
+}
+int mb200_get_profile(const mb200_plan* plan, double* out) {
+  return guarded([&] {
+    if (!plan || !out) throw mb::Error("null argument");
+    std::memcpy(out, reinterpret_cast<const Plan*>(plan)->prof, sizeof(double) * mb::kProfRegions * mb::kProfKinds * 3);
+  });
+}
 long long mb200_workspace_bytes(const mb200_plan* plan) { return plan ? reinterpret_cast<const Plan*>(plan)->bytes_allocated : 0; }
 
 int mb200_test_conv1d(mb200_plan* plan, const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T,

@@ -136,7 +136,9 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   {
     float* sb = stats_base;
     const size_t bytes = static_cast<size_t>(13) * B * 16 * 4;
-    ops.push_back([sb, bytes](cudaStream_t st) { return cudaMemsetAsync(sb, 0, bytes, st); });
+    Launch ms([sb, bytes](cudaStream_t st) { return cudaMemsetAsync(sb, 0, bytes, st); });
+    ms.kind = 3;
+    ops.push_back(std::move(ms));
   }
 
   auto gn_mish = [&](const void* raw, const float* st, const float* g, const float* bta, const float* tadd, int tbs,
@@ -155,11 +157,14 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     });
   };
   auto attention = [&](const void* qkv, const float* mask, void* out, int L) {
-    add([=](cudaStream_t s) -> cudaError_t {
+    Launch at([=](cudaStream_t s) -> cudaError_t {
       if (dtype == MB200_F32) return launch_attention_simt<float>((const float*)qkv, mask, (float*)out, B, L, s);
       if (dtype == MB200_BF16) return launch_attention_simt<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s);
       return launch_attention_simt<__half>((const __half*)qkv, mask, (__half*)out, B, L, s);
     });
+    at.kind = 1;
+    at.flops = 4.0 * B * 2 * static_cast<double>(L) * L * 64;   // QK^T + PV, dense over all L keys as the reference computes it
+    add(std::move(at));
   };
 
   // ResnetBlock1D (decoder.py:46-61): in (1 or 2 sources, already masked) -> RES (unmasked), LN1(RES) -> LN

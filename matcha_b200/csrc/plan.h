@@ -50,7 +50,7 @@ using StateDict = std::map<std::string, HostTensor>;
 struct PackedW {
   void* w = nullptr;
   float* bias = nullptr;     // [N] zero padded, may be null
-  int N = 0, n_valid = 0, K_total = 0, n_taps = 0, n_phases = 1;
+  int N = 0, n_valid = 0, K_total = 0, k_real = 0, n_taps = 0, n_phases = 1;
   int ntile = 0, kc = 0;
   CUtensorMap tm{};          // valid in tensor-core modes
   // tap table (source row offset, channel base in the source view) per phase
@@ -66,7 +66,18 @@ struct Src {
   int rows;     // rows per batch element of the view
 };
 
-using Launch = std::function<cudaError_t(cudaStream_t)>;
+// One enqueued operation of a program plus the bookkeeping the built-in profiler needs.
+struct Launch {
+  std::function<cudaError_t(cudaStream_t)> fn;
+  int kind = 2;     // 0 conv-GEMM, 1 attention, 2 elementwise / small kernels, 3 memset / memcpy (not a kernel)
+  int region = 0;   // 0 estimator, 1..4 vocoder stage (conv_pre counted in 1), 5 boundary
+  double flops = 0; // algorithmic FLOPs (2 per MAC, real channels only)
+  Launch() = default;
+  template <typename F, typename = std::enable_if_t<!std::is_same<std::decay_t<F>, Launch>::value>>
+  Launch(F&& f) : fn(std::forward<F>(f)) {}
+  cudaError_t operator()(cudaStream_t s) const { return fn(s); }
+};
+constexpr int kProfRegions = 6, kProfKinds = 4;
 struct Program {
   std::vector<Launch> ops;
   cudaGraphExec_t graph = nullptr;
@@ -120,6 +131,9 @@ class Plan {
 
   long long launches = 0;
   long long bytes_allocated = 0;
+  // built-in profiler: when on, programs run eagerly with an event pair around every op
+  bool profiling = false;
+  double prof[kProfRegions][kProfKinds][3] = {};   // [region][kind] = {launches, milliseconds, flops}
   mb200_cfg cfg;
 
   // ---- helpers shared by the translation units

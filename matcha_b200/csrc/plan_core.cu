@@ -135,6 +135,7 @@ PackedW Plan::pack_conv(const std::function<float(int, int, int)>& weight, const
   W.N = n_pad;
   W.n_valid = n_real;
   W.K_total = W.n_taps * pad_total;
+  for (auto& sgm : segs) W.k_real += W.n_taps * sgm.first;
   W.ntile = (n_pad % 256 == 0) ? 256 : (n_pad % 128 == 0) ? 128 : (n_pad % 64 == 0) ? 64 : 32;
   if (n_pad % 32) throw Error("pack_conv: N must be a multiple of 32");
   if (W.kc == 32 && W.ntile != 32) throw Error("pack_conv: 32-channel K chunks are only built for N tile 32");
@@ -242,14 +243,37 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
   }
   const int dtype = cfg.dtype;
   const bool tc = tensor_core();
-  return [L, dtype, tc](cudaStream_t st) -> cudaError_t {
+  Launch op([L, dtype, tc](cudaStream_t st) -> cudaError_t {
     if (dtype == MB200_F32) return launch_conv_simt<float>(L, st);
     if (dtype == MB200_BF16) return tc ? launch_conv_umma<__nv_bfloat16>(L, st) : launch_conv_simt<__nv_bfloat16>(L, st);
     return tc ? launch_conv_umma<__half>(L, st) : launch_conv_simt<__half>(L, st);
-  };
+  });
+  op.kind = 0;
+  op.flops = 2.0 * B * T_out * W.n_phases * static_cast<double>(W.n_valid) * W.k_real;
+  return op;
 }
 
 void Plan::run(Program& prog, cudaStream_t st) {
+  if (profiling) {
+    std::vector<cudaEvent_t> ev(prog.ops.size() + 1);
+    for (auto& e : ev) MB_CUDA(cudaEventCreate(&e));
+    MB_CUDA(cudaEventRecord(ev[0], st));
+    for (size_t i = 0; i < prog.ops.size(); ++i) {
+      MB_CUDA(prog.ops[i](st));
+      MB_CUDA(cudaEventRecord(ev[i + 1], st));
+    }
+    MB_CUDA(cudaStreamSynchronize(st));
+    for (size_t i = 0; i < prog.ops.size(); ++i) {
+      float ms = 0.f;
+      MB_CUDA(cudaEventElapsedTime(&ms, ev[i], ev[i + 1]));
+      const Launch& l = prog.ops[i];
+      double* slot = prof[l.region < kProfRegions ? l.region : kProfRegions - 1][l.kind < kProfKinds ? l.kind : kProfKinds - 1];
+      slot[0] += 1; slot[1] += ms; slot[2] += l.flops;
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    launches += prog.kernels;
+    return;
+  }
   if (prog.graph) {
     MB_CUDA(cudaGraphLaunch(prog.graph, st));
     launches += prog.kernels;

@@ -93,7 +93,8 @@ void Plan::vocoder_buffers(int B, int L) {
 void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
   const int f32 = cfg.dtype == MB200_F32;
   auto buf = [&](int i) { return ws_voc_[i].p; };
-  auto add = [&](Launch l) { prog.ops.push_back(std::move(l)); prog.kernels++; };
+  int region = 1;
+  auto add = [&](Launch l) { l.region = region; prog.ops.push_back(std::move(l)); prog.kernels++; };
   const GeneratorW& G = gen_;
   {  // conv_pre, then the first stage's leaky_relu(0.1) (models.py:182,184)
     EpiParams e = epi();
@@ -103,6 +104,7 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
   int ch = 512, len = L;
   for (int i = 0; i < 4; ++i) {
     const int C = ch / 2;
+    region = i + 1;
     {  // ups[i]: x and leaky_relu(x) for the three ResBlocks (models.py:185, :92)
       EpiParams e = epi();
       e.out0 = buf(V_X); e.out0_ld = C; e.out0_f32 = f32;

@@ -1,0 +1,246 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle / the reference-generated golden vectors.
+
+Tolerances (BASELINE.json north_star): fp32 mode max-abs <= 1e-3; half-precision modes relative L2 <= 1e-2.
+Everything here needs a B200 (-m gpu)."""
+import os
+import types
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+import matcha_b200 as mb
+from matcha_b200._lib import Plan
+from oracle import matcha_oracle as mo
+from oracle import weights
+
+pytestmark = pytest.mark.gpu
+
+FP32_MAXABS = 1e-3
+HALF_REL_L2 = 1e-2
+DEC = dict(channels=[256, 256], dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=2,
+           act_fn="snakebeta")
+CFM_PARAMS = types.SimpleNamespace(solver="euler", sigma_min=1e-4)
+EST_CASES = ["est_lj_ragged", "est_lj_min", "est_vctk_ragged", "est_lj_t140"]
+
+
+def rel_l2(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm())
+
+
+def maxabs(a, b):
+    return float((a - b).abs().max())
+
+
+def _quant(x, prec):
+    return x if prec == "fp32" else x.to(torch.bfloat16 if prec == "bf16" else torch.float16).float()
+
+
+def _load(golden_dir, name):
+    return torch.load(os.path.join(golden_dir, name + ".pt"), weights_only=False)
+
+
+def check(got, want, prec):
+    got = got.cpu()
+    assert torch.isfinite(got).all()
+    if prec == "fp32":
+        assert maxabs(got, want) <= FP32_MAXABS, (maxabs(got, want), rel_l2(got, want))
+    else:
+        assert rel_l2(got, want) <= HALF_REL_L2, rel_l2(got, want)
+
+
+# ------------------------------------------------------------------------------------------ conv-GEMM kernel
+CONV_CASES = [  # (B, Cin, Cout, T, K, dilation, stride, transposed)
+    (2, 256, 256, 140, 3, 1, 1, False), (1, 64, 64, 300, 7, 3, 1, False), (2, 32, 32, 513, 11, 5, 1, False),
+    (2, 256, 256, 24, 3, 1, 2, False), (2, 256, 256, 70, 4, 1, 2, True), (1, 512, 256, 9, 16, 1, 8, True),
+    (1, 64, 32, 130, 4, 1, 2, True), (3, 160, 256, 24, 3, 1, 1, False), (2, 256, 1024, 130, 1, 1, 1, False),
+    (2, 1024, 256, 130, 1, 1, 1, False), (2, 256, 384, 4, 1, 1, 1, False), (2, 80, 512, 37, 7, 1, 1, False),
+    (2, 256, 80, 140, 1, 1, 1, False), (1, 128, 128, 1000, 11, 5, 1, False), (1, 256, 256, 1, 3, 1, 1, False),
+]
+
+
+@pytest.mark.parametrize("prec,simt", [("fp32", False), ("bf16", False), ("fp16", False), ("bf16", True)])
+def test_conv_gemm_matches_torch(prec, simt):
+    """Every Conv1d / ConvTranspose1d / Linear shape class on the path, against torch in fp64 on the same
+    (operand-rounded) inputs: the kernels accumulate in fp32, so agreement is ~1e-6 in every mode."""
+    plan = Plan(prec, 160, force_simt=simt, use_graph=False)
+    g = torch.Generator().manual_seed(0)
+    for (b, cin, cout, t, k, dil, stride, tr) in CONV_CASES:
+        x = torch.randn(b, cin, t, generator=g)
+        w = (torch.randn(cin, cout, k, generator=g) if tr else torch.randn(cout, cin, k, generator=g)) / (cin * k) ** 0.5
+        bias = torch.randn(cout, generator=g)
+        xq, wq = _quant(x, prec).double(), _quant(w, prec).double()
+        if tr:
+            ref = F.conv_transpose1d(xq, wq, bias.double(), stride=stride, padding=(k - stride) // 2)
+        else:
+            ref = F.conv1d(xq, wq, bias.double(), stride=stride, dilation=dil, padding=dil * (k - 1) // 2)
+        y = plan.test_conv1d(x, w, bias, dilation=dil, stride=stride, transposed=tr).cpu().double()
+        assert y.shape == ref.shape
+        assert float((y - ref).abs().max()) < 5e-5, (prec, simt, b, cin, cout, t, k, dil, stride, tr)
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
+def test_attention_adds_the_float_mask(prec):
+    """softmax(q k^T + mask[key]) v over ALL padded keys, incl. L = 1 and ragged L."""
+    plan = Plan(prec, 160, use_graph=False)
+    g = torch.Generator().manual_seed(1)
+    for (b, t, lens) in [(2, 24, [24, 9]), (2, 140, [140, 77]), (1, 452, [400]), (1, 1, [1]), (2, 33, [33, 1])]:
+        qkv = torch.randn(b, t, 384, generator=g)
+        qkv[:, :, :128] *= 0.3
+        mask = (torch.arange(t)[None] < torch.tensor(lens)[:, None]).float()
+        x = _quant(qkv, prec).double()
+        q, k, v = (x[:, :, i * 128:(i + 1) * 128].reshape(b, t, 2, 64).transpose(1, 2) for i in range(3))
+        ref = (torch.softmax(q @ k.transpose(-1, -2) + mask[:, None, None, :].double(), -1) @ v)
+        ref = ref.transpose(1, 2).reshape(b, t, 128)
+        y = plan.test_attention(qkv, mask).cpu().double()
+        tol = 2e-5 if prec == "fp32" else (2e-3 if prec == "fp16" else 1.6e-2)  # output rounding of the half types
+        assert float((y - ref).abs().max()) < tol, (prec, b, t)
+
+
+# ------------------------------------------------------------------------------------------ golden vectors
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
+@pytest.mark.parametrize("name", EST_CASES)
+def test_estimator_and_decode_match_reference_golden(golden_dir, name, prec):
+    fx = _load(golden_dir, name)
+    plan = Plan(prec, fx["c_in"])
+    plan.load_estimator(weights.estimator_state_dict(fx["c_in"], seed=fx["seed"]))
+    v = plan.estimator_forward(fx["z"], fx["mask"], fx["mu"], fx["t_scalar"], fx["spks"])
+    vb = plan.estimator_forward(fx["z"], fx["mask"], fx["mu"], fx["t_batched"], fx["spks"])
+    dec = plan.cfm_decode(fx["mu"], fx["mask"], fx["z"], fx["n_steps"], fx["spks"])
+    replay = plan.cfm_decode(fx["mu"], fx["mask"], fx["z"], fx["n_steps"], fx["spks"])  # CUDA-graph replay
+    if prec == "bf16":  # a single velocity evaluation is the noisiest quantity in bf16 (precision)
+        assert rel_l2(v.cpu(), fx["v_scalar"]) < 2.5e-2 and rel_l2(vb.cpu(), fx["v_batched"]) < 2.5e-2
+    else:
+        check(v, fx["v_scalar"], prec)
+        check(vb, fx["v_batched"], prec)
+    check(dec, fx["decoded"], prec)
+    check(replay, fx["decoded"], prec)
+    pad = fx["mask"].expand_as(fx["z"]) == 0
+    assert (v.cpu()[pad] == 0).all()                      # velocity is masked (decoder.py:443)
+    assert torch.equal(dec.cpu()[pad], fx["z"][pad])      # so padded frames keep their noise through the Euler loop
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
+@pytest.mark.parametrize("name", ["gen_plain", "gen_weightnorm"])
+def test_generator_matches_reference_golden(golden_dir, name, prec):
+    fx = _load(golden_dir, name)
+    plan = Plan(prec, 160)
+    plan.load_generator(weights.generator_state_dict(fx["seed"], weight_norm=fx["weight_norm"]))
+    wav = plan.hifigan_forward(fx["mel"])
+    assert wav.shape == fx["wav"].shape
+    check(wav, fx["wav"], prec)
+    check(plan.hifigan_forward(fx["mel"]), fx["wav"], prec)  # graph replay
+
+
+# ------------------------------------------------------------------------------------------ oracle, seeded inputs
+@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+@pytest.mark.parametrize("c_in", [160, 224])
+def test_hot_path_matches_oracle(prec, c_in):
+    """decode (10 steps) -> crop -> denormalise -> vocoder against the CPU oracle, ragged batch, odd vocoder length."""
+    g = torch.Generator().manual_seed(7)
+    b, t_pad, lens, n_steps = 3, 60, [57, 60, 31], 10
+    length = max(lens)  # matcha_tts.py:136: the vocoder sees y_max_length, here 60; also try an odd crop below
+    est_sd, gen_sd = weights.estimator_state_dict(c_in, seed=101), weights.generator_state_dict(102)
+    mu = torch.randn(b, 80, t_pad, generator=g)
+    z = torch.randn(b, 80, t_pad, generator=g) * 0.667
+    spks = torch.randn(b, 64, generator=g) if c_in == 224 else None
+    mask = weights.prefix_mask(lens, t_pad)
+    mean, std = -5.536622, 2.116101
+    with torch.inference_mode():
+        o_dec = mo.solve_euler(est_sd, z, mu, mask, n_steps, spks)
+        o_mel = o_dec[:, :, :57] * std + mean
+        o_wav = mo.hifigan_forward(gen_sd, o_mel).clamp(-1, 1)
+    plan = Plan(prec, c_in)
+    plan.load_estimator(est_sd)
+    plan.load_generator(gen_sd)
+    dec, mel, wav = plan.synthesise(mu, mask, z, n_steps, 57, mean, std, spks)
+    check(dec, o_dec, prec)
+    check(mel, o_mel, prec)
+    assert wav.shape == o_wav.shape == (b, 1, 57 * 256)
+    if prec == "fp32":
+        check(wav, o_wav, prec)
+    else:
+        assert rel_l2(wav.cpu(), o_wav) <= HALF_REL_L2
+    # host-buffer entry point gives the same answer
+    mel_h, wav_h = plan.synthesise_host(mu, mask.contiguous(), z, n_steps, 57, mean, std, spks)
+    assert rel_l2(wav_h, o_wav) <= (1e-4 if prec == "fp32" else HALF_REL_L2)
+    assert length == 60
+
+
+def test_module_api_is_drop_in(golden_dir):
+    """The nn.Module surface: CFM.forward / solve_euler / estimator / compute_loss and Generator.forward."""
+    fx = _load(golden_dir, "est_lj_ragged")
+    cfm = mb.CFM(160, 80, CFM_PARAMS, DEC, precision="fp32")
+    cfm.load_state_dict(weights.estimator_state_dict(160, seed=fx["seed"]), strict=True)
+    cfm = cfm.cuda().eval()
+    dev = lambda v: None if v is None else v.cuda()  # noqa: E731
+    v = cfm.estimator(dev(fx["z"]), dev(fx["mask"]), dev(fx["mu"]), torch.tensor(fx["t_scalar"]).cuda(), None)
+    check(v, fx["v_scalar"], "fp32")
+    dec = cfm.solve_euler(dev(fx["z"]), torch.linspace(0, 1, fx["n_steps"] + 1).cuda(), dev(fx["mu"]), dev(fx["mask"]), None, None)
+    check(dec, fx["decoded"], "fp32")
+    # non-uniform grid goes through the per-step path and must agree with the oracle's recurrence on that grid
+    span = torch.tensor([0.0, 0.2, 0.7, 1.0])
+    dec2 = cfm.solve_euler(dev(fx["z"]), span.cuda(), dev(fx["mu"]), dev(fx["mask"]), None, None).cpu()
+    sd = weights.estimator_state_dict(160, seed=fx["seed"])
+    x, t = fx["z"], span[0]
+    for i in range(3):
+        x = x + (span[i + 1] - t) * mo.estimator_forward(sd, x, fx["mask"], fx["mu"], t)
+        t = span[i + 1]
+    assert maxabs(dec2, x) <= FP32_MAXABS
+    # compute_loss with pinned draws (flow_matching.py:108,110)
+    t_draw, z_draw = fx["t_draw"].cuda(), fx["z_draw"].cuda()
+    orig_rand, orig_randn_like = torch.rand, torch.randn_like
+    torch.rand = lambda *a, **k: t_draw.clone()
+    torch.randn_like = lambda *a, **k: z_draw.clone()
+    try:
+        loss, y = cfm.compute_loss(dev(fx["x1"]), dev(fx["mask"]), dev(fx["mu"]))
+    finally:
+        torch.rand, torch.randn_like = orig_rand, orig_randn_like
+    assert abs(float(loss) - float(fx["loss"])) < 1e-4 * abs(float(fx["loss"]))
+    assert maxabs(y.cpu(), fx["y"]) < 1e-6
+    # forward() draws its own noise: shape/finite/mask only
+    out = cfm(dev(fx["mu"]), dev(fx["mask"]), 4, temperature=0.667)
+    assert out.shape == fx["mu"].shape and torch.isfinite(out).all()
+    gfx = _load(golden_dir, "gen_weightnorm")
+    gen = mb.Generator(mb.AttrDict(mb.HIFIGAN_V1), precision="fp32")
+    gen.load_state_dict(weights.generator_state_dict(gfx["seed"], weight_norm=True), strict=True)
+    gen = gen.cuda().eval()
+    check(gen(gfx["mel"].cuda()), gfx["wav"], "fp32")
+    gen.remove_weight_norm()   # cli.py:84-90 order: load with weight-norm keys, then remove
+    check(gen(gfx["mel"].cuda()), gfx["wav"], "fp32")
+
+
+# ------------------------------------------------------------------------------------------ full size (BASELINE cfg2)
+def test_full_size_properties_cfg2():
+    """B=64, T=452, 10 Euler steps + vocoder: too large for the CPU oracle, so check size-independent properties:
+    the tensor-core path agrees with the independent FFMA fp32 path, padded frames keep their noise, masked velocity,
+    waveform bounded, batch-order equivariance."""
+    g = torch.Generator().manual_seed(1234)
+    b, t_pad, n_steps = 64, 452, 10
+    lens = [451] * 48 + [int(v) for v in torch.randint(60, 451, (16,), generator=g)]
+    est_sd, gen_sd = weights.estimator_state_dict(160, seed=1234), weights.generator_state_dict(1234)
+    mu = torch.randn(b, 80, t_pad, generator=g).cuda()
+    z = (torch.randn(b, 80, t_pad, generator=g) * 0.667).cuda()
+    mask = weights.prefix_mask(lens, t_pad).cuda()
+    mean, std = -5.536622, 2.116101
+    out = {}
+    for prec in ("fp16", "fp32"):
+        plan = Plan(prec, 160)
+        plan.load_estimator(est_sd)
+        plan.load_generator(gen_sd)
+        out[prec] = plan.synthesise(mu, mask, z, n_steps, 451, mean, std)
+        if prec == "fp16":
+            perm = torch.randperm(b, generator=g).cuda()
+            dec_p, _, wav_p = plan.synthesise(mu[perm], mask[perm], z[perm], n_steps, 451, mean, std)
+            assert rel_l2(dec_p.cpu(), out[prec][0][perm].cpu()) < 5e-3   # utterances are independent (atomics order only)
+            assert rel_l2(wav_p.cpu(), out[prec][2][perm].cpu()) < 5e-3
+        del plan
+        torch.cuda.empty_cache()
+    dec16, mel16, wav16 = out["fp16"]
+    dec32, mel32, wav32 = out["fp32"]
+    assert rel_l2(dec16.cpu(), dec32.cpu()) <= HALF_REL_L2
+    assert rel_l2(wav16.cpu(), wav32.cpu()) <= HALF_REL_L2
+    pad = (mask.expand_as(z) == 0)
+    assert torch.equal(dec16[pad], z[pad]) and torch.equal(dec32[pad], z[pad])
+    assert float(wav16.abs().max()) <= 1.0 and torch.isfinite(wav16).all()
+    assert wav16.shape == (b, 1, 451 * 256)
