@@ -159,8 +159,10 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   auto attention = [&](const void* qkv, const float* mask, void* out, int L) {
     Launch at([=](cudaStream_t s) -> cudaError_t {
       if (dtype == MB200_F32) return launch_attention_simt<float>((const float*)qkv, mask, (float*)out, B, L, s);
-      if (dtype == MB200_BF16) return launch_attention_simt<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s);
-      return launch_attention_simt<__half>((const __half*)qkv, mask, (__half*)out, B, L, s);
+      if (dtype == MB200_BF16) return tc ? launch_attention_mma<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s)
+                                         : launch_attention_simt<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s);
+      return tc ? launch_attention_mma<__half>((const __half*)qkv, mask, (__half*)out, B, L, s)
+                : launch_attention_simt<__half>((const __half*)qkv, mask, (__half*)out, B, L, s);
     });
     at.kind = 1;
     at.flops = 4.0 * B * 2 * static_cast<double>(L) * L * 64;   // QK^T + PV, dense over all L keys as the reference computes it

@@ -50,5 +50,7 @@ cudaError_t launch_conv_post(const T* in, const float* w /*[7][32]*/, float bias
 // ---- attention (attention.cu): qkv [B][L][384] (q | k | v, 2 heads x 64), additive key mask, out [B][L][128]
 template <typename T>
 cudaError_t launch_attention_simt(const T* qkv, const float* mask, T* out, int B, int L, cudaStream_t st);
+template <typename T>   // mma.sync tensor-core version (attention_mma.cu), half types only
+cudaError_t launch_attention_mma(const T* qkv, const float* mask, T* out, int B, int L, cudaStream_t st);
 
 }  // namespace mb
