@@ -30,6 +30,24 @@ struct ConvGeom {
   int K_total;     // n_taps * (src_ch[0] + src_ch[1]) = weight row pitch
 };
 
+// Geometry of the persistent kernel (conv_gemm2.cu).  The K loop is organised in A-load GROUPS: one group = one source
+// view and channel base; for each K chunk of a group the A tile is loaded ONCE with a halo (128 + 8*extra rows) and
+// every tap of the group reuses it through a row-shifted shared-memory descriptor.
+constexpr int kMaxGroups = 4;
+struct ConvGeom2 {
+  int B, T_in, T_out, N, n_phases, K_total;
+  int n_groups;
+  int g_src[kMaxGroups], g_ch[kMaxGroups], g_chunks[kMaxGroups], g_ntaps[kMaxGroups];
+  int g_rowmin[kMaxPhases][kMaxGroups];            // first halo row relative to the tile's first output row
+  int g_extra[kMaxPhases][kMaxGroups];             // extra 8-row boxes after the first 128 rows
+  int g_shift[kMaxPhases][kMaxGroups][kMaxTaps];   // row shift of each tap inside the halo tile
+  int g_wk[kMaxGroups][kMaxTaps];                  // K coordinate of the tap's weight slice for chunk 0
+  int w_resident;                                  // all weight tiles stay in shared memory for the CTA's lifetime
+  int a_stages, w_stages;                          // ring depths (w_stages unused when resident)
+  int m_tiles, n_tiles, total_tiles;
+  int base_off_mode;                               // descriptor base_offset policy for shifted A tiles (bring-up knob)
+};
+
 struct EpiParams {
   int T_o;                 // output rows per batch (T_out * o_mul)
   int o_mul;               // output row = t * o_mul + phase * o_phase_step

@@ -15,10 +15,15 @@ struct ConvLaunch {
   CUtensorMap tmA[2]; // TMA views (tcgen05 path)
   CUtensorMap tmW;
   int ntile, kc;      // tcgen05 tile: N per CTA, K chunk (channels per TMA box)
+  // persistent kernel (conv_gemm2.cu)
+  ConvGeom2 g2;
+  CUtensorMap tmA8[2];  // same views, 8-row boxes (halo rows beyond the first 128)
+  int smem_bytes, grid;
 };
 
 template <typename T> cudaError_t launch_conv_umma(const ConvLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_conv_simt(const ConvLaunch& L, cudaStream_t st);
+template <typename T> cudaError_t launch_conv_umma2(const ConvLaunch& L, cudaStream_t st);
 
 // ---- elementwise / small kernels (elementwise.cu)
 template <typename T>

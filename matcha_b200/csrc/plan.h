@@ -132,6 +132,9 @@ class Plan {
   long long launches = 0;
   long long bytes_allocated = 0;
   // built-in profiler: when on, programs run eagerly with an event pair around every op
+  int kernel_version = 2;   // 2 = persistent conv_gemm2.cu (default), 1 = first non-persistent kernel (MB200_KERNEL=1)
+  int base_off_mode = 0;    // row-shifted A descriptors need no base_offset: the swizzle is a function of absolute smem address bits (measured; MB200_BASEOFF=1 to test the other policy)
+  int num_sms = 148;
   bool profiling = false;
   double prof[kProfRegions][kProfKinds][3] = {};   // [region][kind] = {launches, milliseconds, flops}
   mb200_cfg cfg;
@@ -142,7 +145,7 @@ class Plan {
   float* upload_f32(const float* host, size_t n);   // plan-owned
   void* ensure(DevBuf& b, size_t bytes);            // grow-only workspace
   void* upload_operand(const std::vector<float>& host);  // fp32 host -> plan dtype device
-  CUtensorMap tmap_act(const void* p, int ld, int rows, int B, int kc) const;
+  CUtensorMap tmap_act(const void* p, int ld, int rows, int B, int kc, int box_rows = 128) const;
   CUtensorMap tmap_w(const void* p, int K_total, int rows, int kc, int ntile) const;
   // Generic weight repack. weight(n, c, j) with c the concatenated real input channel; segs = (real, padded) channels of
   // each source; taps_j[phase][tap] = kernel index j.

@@ -4,6 +4,8 @@
 #include <cuda_fp16.h>
 #include <cudaTypedefs.h>
 
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "plan.h"
@@ -33,6 +35,9 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   int dev = 0, major = 0;
   MB_CUDA(cudaGetDevice(&dev));
   MB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  MB_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  if (const char* v = std::getenv("MB200_KERNEL")) kernel_version = std::atoi(v);
+  if (const char* v = std::getenv("MB200_BASEOFF")) base_off_mode = std::atoi(v);
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -94,12 +99,12 @@ void* Plan::upload_operand(const std::vector<float>& host) {
 
 // Activation view [B][rows][ld] (channels contiguous): 3-D map, box = kc channels x 128 rows x 1 batch element.
 // Rows outside [0, rows) are zero-filled by TMA: that IS the conv's zero padding at the utterance edges.
-CUtensorMap Plan::tmap_act(const void* p, int ld, int rows, int B, int kc) const {
+CUtensorMap Plan::tmap_act(const void* p, int ld, int rows, int B, int kc, int box_rows) const {
   CUtensorMap m;
   const CUtensorMapDataType dt = cfg.dtype == MB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   cuuint64_t dims[3] = {static_cast<cuuint64_t>(ld), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(B)};
   cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 2, static_cast<cuuint64_t>(ld) * 2 * rows};
-  cuuint32_t box[3] = {static_cast<cuuint32_t>(kc), 128, 1};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(kc), static_cast<cuuint32_t>(box_rows), 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = get_encode()(&m, dt, 3, const_cast<void*>(p), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                             kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
@@ -240,13 +245,67 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     L.tmA[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc);
     L.tmA[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc) : L.tmA[0];
     L.tmW = W.tm;
+    // ---- persistent kernel geometry: A-load groups = (source, channel base); taps of a group share one halo tile
+    ConvGeom2& g2 = L.g2;
+    g2.B = B; g2.T_in = s0.rows; g2.T_out = T_out; g2.N = W.N; g2.n_phases = W.n_phases; g2.K_total = W.K_total;
+    const int per_tap = g.src_ch[0] + g.src_ch[1];
+    int ng = 0;
+    for (int s = 0; s < g.n_src; ++s) {
+      std::vector<int> bases;
+      for (int tp = 0; tp < W.n_taps; ++tp)
+        if (std::find(bases.begin(), bases.end(), W.tap_ch[0][tp]) == bases.end()) bases.push_back(W.tap_ch[0][tp]);
+      for (int cb : bases) {
+        if (ng >= kMaxGroups) throw Error("conv_op: too many A-load groups");
+        g2.g_src[ng] = s; g2.g_ch[ng] = cb; g2.g_chunks[ng] = g.src_ch[s] / W.kc;
+        int nt = 0;
+        for (int tp = 0; tp < W.n_taps; ++tp)
+          if (W.tap_ch[0][tp] == cb) g2.g_wk[ng][nt++] = tp * per_tap + (s ? g.src_ch[0] : 0);
+        g2.g_ntaps[ng] = nt;
+        for (int ph = 0; ph < W.n_phases; ++ph) {
+          int rmin = 1 << 30, rmax = -(1 << 30);
+          for (int tp = 0; tp < W.n_taps; ++tp)
+            if (W.tap_ch[0][tp] == cb) { rmin = std::min(rmin, W.tap_row[ph][tp]); rmax = std::max(rmax, W.tap_row[ph][tp]); }
+          g2.g_rowmin[ph][ng] = rmin;
+          g2.g_extra[ph][ng] = (rmax - rmin + 7) / 8;
+          if (g2.g_extra[ph][ng] > 8) throw Error("conv_op: tap span exceeds the halo capacity");
+          int k = 0;
+          for (int tp = 0; tp < W.n_taps; ++tp)
+            if (W.tap_ch[0][tp] == cb) g2.g_shift[ph][ng][k++] = W.tap_row[ph][tp] - rmin;
+        }
+        ++ng;
+      }
+    }
+    g2.n_groups = ng;
+    g2.m_tiles = (T_out + 127) / 128;
+    g2.n_tiles = W.N / W.ntile;
+    g2.total_tiles = B * g2.m_tiles * g2.n_tiles * W.n_phases;
+    g2.base_off_mode = base_off_mode;
+    const int a_bytes = 192 * W.kc * 2, w_tile = W.ntile * W.kc * 2, budget = 220 * 1024;
+    const long w_total = static_cast<long>(W.n_phases) * W.N * W.K_total * 2;
+    if (w_total <= 120 * 1024) {
+      g2.w_resident = 1;
+      g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
+      g2.w_stages = 0;
+      L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + 2048;
+    } else {
+      g2.w_resident = 0;
+      g2.a_stages = 3;
+      g2.w_stages = std::min(8, (budget - g2.a_stages * a_bytes) / w_tile);
+      L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * w_tile + 2048;
+    }
+    L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8);
+    L.tmA8[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 8) : L.tmA8[0];
+    L.grid = std::min(g2.total_tiles, num_sms);
   }
   const int dtype = cfg.dtype;
   const bool tc = tensor_core();
-  Launch op([L, dtype, tc](cudaStream_t st) -> cudaError_t {
+  const bool v2 = kernel_version >= 2;
+  Launch op([L, dtype, tc, v2](cudaStream_t st) -> cudaError_t {
     if (dtype == MB200_F32) return launch_conv_simt<float>(L, st);
-    if (dtype == MB200_BF16) return tc ? launch_conv_umma<__nv_bfloat16>(L, st) : launch_conv_simt<__nv_bfloat16>(L, st);
-    return tc ? launch_conv_umma<__half>(L, st) : launch_conv_simt<__half>(L, st);
+    if (dtype == MB200_BF16)
+      return tc ? (v2 ? launch_conv_umma2<__nv_bfloat16>(L, st) : launch_conv_umma<__nv_bfloat16>(L, st))
+                : launch_conv_simt<__nv_bfloat16>(L, st);
+    return tc ? (v2 ? launch_conv_umma2<__half>(L, st) : launch_conv_umma<__half>(L, st)) : launch_conv_simt<__half>(L, st);
   });
   op.kind = 0;
   op.flops = 2.0 * B * T_out * W.n_phases * static_cast<double>(W.n_valid) * W.k_real;
