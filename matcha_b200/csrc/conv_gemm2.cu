@@ -9,6 +9,7 @@
 //   warps 2-5, 6-9   two epilogue groups that drain alternate tiles (tcgen05.ld -> fused epilogue -> global), so the
 //               epilogue of tile i overlaps the loads and MMAs of tiles i+1, i+2.
 #include "conv.cuh"
+#include "epilogue2.cuh"
 #include "launch.h"
 #include "ptx.cuh"
 
@@ -91,6 +92,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   uint64_t* t_empty = t_full + 4;
   uint64_t* wres = t_empty + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres + 1);
+  uint8_t* stage_base = reinterpret_cast<uint8_t*>(wres + 3);   // 8 warp-private epilogue staging tiles (16-byte aligned)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int np = g.n_tiles * g.n_phases;
@@ -213,8 +215,12 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       mbar_wait(&t_full[slot], (it / NACC) & 1);
       tc_fence_after();
       const int t = t0 + lane_grp * 32 + lane;
-      epilogue_tile<NTILE, T>(e, b, t, t < g.T_out, phase, n_tile * NTILE,
-                              tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * NTILE);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * NTILE;
+      if (epi2_supported(e))
+        epilogue_tile2<NTILE, T>(e, b, t0 + lane_grp * 32, g.T_out, phase, n_tile * NTILE, taddr,
+                                 stage_base + (warp - 2) * kStageBytes, lane);
+      else
+        epilogue_tile<NTILE, T>(e, b, t, t < g.T_out, phase, n_tile * NTILE, taddr);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&t_empty[slot]);

@@ -280,18 +280,18 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     g2.n_tiles = W.N / W.ntile;
     g2.total_tiles = B * g2.m_tiles * g2.n_tiles * W.n_phases;
     g2.base_off_mode = base_off_mode;
-    const int a_bytes = 192 * W.kc * 2, w_tile = W.ntile * W.kc * 2, budget = 220 * 1024;
+    const int a_bytes = 192 * W.kc * 2, w_tile = W.ntile * W.kc * 2, budget = 182 * 1024;   // 227 KB minus barriers, alignment slack and 8 x 4.5 KB epilogue staging
     const long w_total = static_cast<long>(W.n_phases) * W.N * W.K_total * 2;
-    if (w_total <= 120 * 1024) {
+    if (w_total <= 100 * 1024) {
       g2.w_resident = 1;
       g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
       g2.w_stages = 0;
-      L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + 2048;
+      L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + 2048 + 8 * 4608;
     } else {
       g2.w_resident = 0;
-      g2.a_stages = 3;
+      g2.a_stages = W.ntile == 256 ? 2 : 3;
       g2.w_stages = std::min(8, (budget - g2.a_stages * a_bytes) / w_tile);
-      L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * w_tile + 2048;
+      L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * w_tile + 2048 + 8 * 4608;
     }
     L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8);
     L.tmA8[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 8) : L.tmA8[0];
