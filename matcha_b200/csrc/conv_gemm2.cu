@@ -92,7 +92,8 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   uint64_t* t_empty = t_full + 4;
   uint64_t* wres = t_empty + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres + 1);
-  uint8_t* stage_base = reinterpret_cast<uint8_t*>(wres + 3);   // 8 warp-private epilogue staging tiles (16-byte aligned)
+  // 8 warp-private epilogue staging tiles, 16-byte aligned
+  uint8_t* stage_base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(wres + 2) + 15) & ~uintptr_t(15));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int np = g.n_tiles * g.n_phases;
