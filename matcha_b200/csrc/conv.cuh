@@ -45,6 +45,8 @@ struct ConvGeom2 {
   int w_resident;                                  // all weight tiles stay in shared memory for the CTA's lifetime
   int a_stages, w_stages;                          // ring depths (w_stages unused when resident)
   int m_tiles, n_tiles, total_tiles;
+  int mb;                                          // 128-row blocks per tile (1, 2 or 4): narrow-N layers amortise per-tile costs
+  int a_bytes;                                     // bytes of one A ring stage: (128*mb + 64) rows
   int base_off_mode;                               // descriptor base_offset policy for shifted A tiles (bring-up knob)
 };
 

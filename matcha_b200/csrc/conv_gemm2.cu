@@ -71,10 +71,12 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
                        const __grid_constant__ CUtensorMap tmW, const __grid_constant__ ConvGeom2 g,
                        const __grid_constant__ EpiParams e) {
   constexpr int ROWB = KC * 2;
-  constexpr int A_BYTES = kARows * ROWB;
   constexpr int W_TILE = NTILE * ROWB;
-  constexpr int NACC = (512 / NTILE) < 4 ? (512 / NTILE) : 4;
-  constexpr int TMEM_COLS = NACC * NTILE;
+  constexpr int TMEM_COLS = 512;   // one CTA per SM: take all of TMEM
+  const int A_BYTES = g.a_bytes;
+  const int SLOT_COLS = g.mb * NTILE;
+  const int NACC = (512 / SLOT_COLS) < 4 ? (512 / SLOT_COLS) : 4;
+  const int TROWS = 128 * g.mb;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
@@ -126,7 +128,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
         const int nn = tile % np, mm = tile / np;
         const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
-        const int t0 = (mm % g.m_tiles) * 128, b = mm / g.m_tiles;
+        const int t0 = (mm % g.m_tiles) * TROWS, b = mm / g.m_tiles;
         for (int q = 0; q < g.n_groups; ++q) {
           const CUtensorMap* m128 = g.g_src[q] ? &tmA1 : &tmA0;
           const CUtensorMap* m8 = g.g_src[q] ? &tmA1x : &tmA0x;
@@ -134,10 +136,10 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
           for (int c = 0; c < g.g_chunks[q]; ++c) {
             mbar_wait(&a_empty[as], aph ^ 1);
             uint8_t* dst = a_ring + as * A_BYTES;
-            mbar_expect_tx(&a_full[as], (128 + 8 * extra) * ROWB);
+            mbar_expect_tx(&a_full[as], (TROWS + 8 * extra) * ROWB);
             const int ch = g.g_ch[q] + c * KC;
-            tma_load_3d(dst, m128, &a_full[as], ch, row0, b);
-            for (int x = 0; x < extra; ++x) tma_load_3d(dst + (128 + 8 * x) * ROWB, m8, &a_full[as], ch, row0 + 128 + 8 * x, b);
+            for (int i = 0; i < g.mb; ++i) tma_load_3d(dst + i * 128 * ROWB, m128, &a_full[as], ch, row0 + 128 * i, b);
+            for (int x = 0; x < extra; ++x) tma_load_3d(dst + (TROWS + 8 * x) * ROWB, m8, &a_full[as], ch, row0 + TROWS + 8 * x, b);
             if (++as == g.a_stages) { as = 0; aph ^= 1; }
             if (!g.w_resident) {
               for (int tp = 0; tp < g.g_ntaps[q]; ++tp) {
@@ -163,7 +165,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       const int slot = it % NACC;
       mbar_wait(&t_empty[slot], (((it / NACC) & 1) ^ 1));
       tc_fence_after();
-      const uint32_t dtm = tmem_base + slot * NTILE;
+      const uint32_t dtm = tmem_base + slot * SLOT_COLS;
       uint32_t first = 1;
       for (int q = 0; q < g.n_groups; ++q) {
         for (int c = 0; c < g.g_chunks[q]; ++c) {
@@ -180,14 +182,14 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
               w_addr = smem_u32(w_base + ws * W_TILE);
             }
             if (lane == 0) {
-              const uint32_t sa = a_addr + g.g_shift[phase][q][tp] * ROWB;
-              uint64_t adesc = umma_smem_desc<ROWB>(sa);
-              if (g.base_off_mode) adesc |= static_cast<uint64_t>((sa >> 7) & 7) << 49;
               const uint64_t bdesc = umma_smem_desc<ROWB>(w_addr);
+              for (int i = 0; i < g.mb; ++i) {   // the weight tile is reused by every 128-row block of the tile
+                const uint32_t sa = a_addr + (g.g_shift[phase][q][tp] + 128 * i) * ROWB;
+                uint64_t adesc = umma_smem_desc<ROWB>(sa);
+                if (g.base_off_mode) adesc |= static_cast<uint64_t>((sa >> 7) & 7) << 49;
 #pragma unroll
-              for (int k = 0; k < KC / 16; ++k) {
-                umma_f16(dtm, adesc + 2 * k, bdesc + 2 * k, idesc, first ? 0u : 1u);
-                first = 0;
+                for (int k = 0; k < KC / 16; ++k)
+                  umma_f16(dtm + i * NTILE, adesc + 2 * k, bdesc + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
               }
               if (!g.w_resident) umma_commit(&w_empty[ws]);
             }
@@ -211,17 +213,19 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     for (int tile = blockIdx.x + grp * gridDim.x; tile < g.total_tiles; tile += 2 * gridDim.x, it += 2) {
       const int nn = tile % np, mm = tile / np;
       const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
-      const int t0 = (mm % g.m_tiles) * 128, b = mm / g.m_tiles;
+      const int t0 = (mm % g.m_tiles) * TROWS, b = mm / g.m_tiles;
       const int slot = it % NACC;
       mbar_wait(&t_full[slot], (it / NACC) & 1);
       tc_fence_after();
-      const int t = t0 + lane_grp * 32 + lane;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * NTILE;
-      if (epi2_supported(e))
-        epilogue_tile2<NTILE, T>(e, b, t0 + lane_grp * 32, g.T_out, phase, n_tile * NTILE, taddr,
-                                 stage_base + (warp - 2) * kStageBytes, lane);
-      else
-        epilogue_tile<NTILE, T>(e, b, t, t < g.T_out, phase, n_tile * NTILE, taddr);
+      for (int i = 0; i < g.mb; ++i) {
+        const int tw = t0 + 128 * i + lane_grp * 32;
+        if (tw >= g.T_out) break;   // warp-uniform: nothing of this block exists
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * SLOT_COLS + i * NTILE;
+        if (epi2_supported(e))
+          epilogue_tile2<NTILE, T>(e, b, tw, g.T_out, phase, n_tile * NTILE, taddr, stage_base + (warp - 2) * kStageBytes, lane);
+        else
+          epilogue_tile<NTILE, T>(e, b, tw + lane, tw + lane < g.T_out, phase, n_tile * NTILE, taddr);
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&t_empty[slot]);

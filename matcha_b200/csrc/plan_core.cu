@@ -276,12 +276,16 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
       }
     }
     g2.n_groups = ng;
-    g2.m_tiles = (T_out + 127) / 128;
+    // narrow-N layers (HiFi-GAN stages 2-4) process 2-4 blocks of 128 rows per tile to amortise per-tile latencies
+    g2.mb = 1;
+    if (T_out >= 2048) g2.mb = W.ntile == 32 ? 4 : (W.ntile <= 128 ? 2 : 1);
+    g2.m_tiles = (T_out + 128 * g2.mb - 1) / (128 * g2.mb);
     g2.n_tiles = W.N / W.ntile;
     g2.total_tiles = B * g2.m_tiles * g2.n_tiles * W.n_phases;
     g2.base_off_mode = base_off_mode;
-    const int a_bytes = 192 * W.kc * 2, w_tile = W.ntile * W.kc * 2, budget = 182 * 1024;   // 227 KB minus barriers, alignment slack and 8 x 4.5 KB epilogue staging
+    const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = W.ntile * W.kc * 2, budget = 182 * 1024;   // 227 KB minus barriers, alignment slack and 8 x 4.5 KB epilogue staging
     const long w_total = static_cast<long>(W.n_phases) * W.N * W.K_total * 2;
+    g2.a_bytes = a_bytes;
     if (w_total <= 100 * 1024) {
       g2.w_resident = 1;
       g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
@@ -289,7 +293,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
       L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + 2048 + 8 * 4608;
     } else {
       g2.w_resident = 0;
-      g2.a_stages = W.ntile == 256 ? 2 : 3;
+      g2.a_stages = (W.ntile == 256 || g2.mb > 1) ? 2 : 3;
       g2.w_stages = std::min(8, (budget - g2.a_stages * a_bytes) / w_tile);
       L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * w_tile + 2048 + 8 * 4608;
     }

@@ -56,6 +56,9 @@ CONV_CASES = [  # (B, Cin, Cout, T, K, dilation, stride, transposed)
     (1, 64, 32, 130, 4, 1, 2, True), (3, 160, 256, 24, 3, 1, 1, False), (2, 256, 1024, 130, 1, 1, 1, False),
     (2, 1024, 256, 130, 1, 1, 1, False), (2, 256, 384, 4, 1, 1, 1, False), (2, 80, 512, 37, 7, 1, 1, False),
     (2, 256, 80, 140, 1, 1, 1, False), (1, 128, 128, 1000, 11, 5, 1, False), (1, 256, 256, 1, 3, 1, 1, False),
+    # long sequences: the persistent kernel switches to 2/4 blocks of 128 rows per tile (T_out >= 2048)
+    (1, 32, 32, 2500, 11, 5, 1, False), (2, 64, 64, 2200, 7, 3, 1, False), (1, 128, 128, 2100, 3, 1, 1, False),
+    (1, 128, 128, 2304, 11, 1, 1, False), (1, 64, 32, 1100, 4, 1, 2, True),
 ]
 
 

@@ -36,7 +36,8 @@ def group_conv(prec, simt):
         (1, 128, 64, 200, 4, 1, 2, True), (1, 64, 32, 130, 4, 1, 2, True), (3, 160, 256, 24, 3, 1, 1, False),
         (2, 256, 1024, 130, 1, 1, 1, False), (2, 1024, 256, 130, 1, 1, 1, False), (2, 256, 384, 4, 1, 1, 1, False),
         (2, 128, 256, 129, 1, 1, 1, False), (2, 80, 512, 37, 7, 1, 1, False), (2, 256, 80, 140, 1, 1, 1, False),
-        (1, 128, 128, 1000, 11, 5, 1, False),
+        (1, 128, 128, 1000, 11, 5, 1, False), (1, 32, 32, 2500, 11, 5, 1, False), (2, 64, 64, 2200, 7, 3, 1, False),
+        (1, 128, 128, 2100, 3, 1, 1, False), (1, 128, 128, 2304, 11, 1, 1, False), (1, 64, 32, 1100, 4, 1, 2, True),
     ]
     for (b, cin, cout, t, k, dil, stride, tr) in cases:
         x = torch.randn(b, cin, t, generator=g)
