@@ -1,4 +1,7 @@
 // extern "C" boundary (include/matcha_b200.h) and the unit-test hooks.
+#include <cstdio>
+#include <cstdlib>
+#include <algorithm>
 #include <cstring>
 
 #include "plan.h"
@@ -47,8 +50,39 @@ void Plan::test_conv1d(const float* x, const float* w, const float* bias, int B,
   EpiParams e{};
   e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f;
   e.out0 = y_ntc; e.out0_ld = W.N; e.out0_f32 = 1;
+  if (const char* v = std::getenv("MB200_PROBE_EPI")) {   // developer probe: HiFi-GAN ResBlock c2-style epilogue
+    if (std::atoi(v) && Cin == Cout && cpad == Cin && !transposed && stride == 1 && dtype != MB200_F32) {
+      e.resid = xa; e.resid_ld = cpad;
+      e.out1 = dalloc(static_cast<size_t>(B) * T_o * W.N * es); e.out1_ld = W.N; e.out1_slope = 0.1f;
+      if (std::atoi(v) > 1) { e.out0 = dalloc(static_cast<size_t>(B) * T_o * W.N * es); e.out0_f32 = 0; }
+    }
+  }
   Launch op = conv_op(W, Src{xa, view_ld, transposed || stride == 1 ? cpad : Cin, view_rows}, nullptr, B, T_out, e);
   MB_CUDA(op(st));
+  if (const char* v = std::getenv("MB200_PROBE")) {       // developer probe: time repeated launches of this op
+    const int reps = std::max(1, std::atoi(v));
+    cudaEvent_t e0, e1;
+    MB_CUDA(cudaEventCreate(&e0)); MB_CUDA(cudaEventCreate(&e1));
+    MB_CUDA(cudaEventRecord(e0, st));
+    for (int r = 0; r < reps; ++r) MB_CUDA(op(st));
+    MB_CUDA(cudaEventRecord(e1, st));
+    MB_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    MB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    std::fprintf(stderr, "[probe] B=%d Cin=%d Cout=%d T=%d K=%d dil=%d: %.1f us/launch, %.1f TFLOP/s\n", B, Cin, Cout, T, K, dil,
+                 1e3 * ms / reps, op.flops * reps / (ms * 1e9));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (probe_out) {
+      std::vector<long long> h(148 * 16);
+      MB_CUDA(cudaMemcpy(h.data(), probe_out, h.size() * 8, cudaMemcpyDeviceToHost));
+      const char* names[5] = {"producer", "mma", "epi-w2", "epi-w6", "kernel"};
+      for (int cta : {0, 147}) {
+        std::fprintf(stderr, "  [cta %3d]", cta);
+        for (int r = 0; r < 5; ++r) std::fprintf(stderr, " %s %lld/%lld", names[r], h[cta * 16 + 2 * r], h[cta * 16 + 2 * r + 1]);
+        std::fprintf(stderr, "  (role: cycles total/in waits; kernel: total/setup)\n");
+      }
+    }
+  }
   // [B][T_o][N] -> (B, Cout, T_o): transpose all N channels, then copy the first Cout rows per batch element
   float* y_full = static_cast<float*>(dalloc(static_cast<size_t>(B) * T_o * W.N * 4));
   MB_CUDA(launch_btc_to_bct(y_ntc, y_full, B, W.N, T_o, st));

@@ -34,6 +34,11 @@ struct ConvGeom {
 // view and channel base; for each K chunk of a group the A tile is loaded ONCE with a halo (128 + 8*extra rows) and
 // every tap of the group reuses it through a row-shifted shared-memory descriptor.
 constexpr int kMaxGroups = 4;
+constexpr int kMaxSched = 192;
+constexpr uint32_t kSchedWFirst = 1u << 28;  // first tap of a streamed weight stage: wait for it
+constexpr uint32_t kSchedWLast = 1u << 29;   // last tap of a streamed weight stage: release it
+constexpr uint32_t kSchedFirst = 1u << 30;   // first tap of an A stage: wait for the halo tile
+constexpr uint32_t kSchedLast = 1u << 31;    // last tap of an A stage: release it
 struct ConvGeom2 {
   int B, T_in, T_out, N, n_phases, K_total;
   int n_groups;
@@ -44,10 +49,19 @@ struct ConvGeom2 {
   int g_wk[kMaxGroups][kMaxTaps];                  // K coordinate of the tap's weight slice for chunk 0
   int w_resident;                                  // all weight tiles stay in shared memory for the CTA's lifetime
   int a_stages, w_stages;                          // ring depths (w_stages unused when resident)
+  int wt;                                          // taps per streamed weight stage (1 or 2): longer steps per handshake
   int m_tiles, n_tiles, total_tiles;
   int mb;                                          // 128-row blocks per tile (1, 2 or 4): narrow-N layers amortise per-tile costs
   int a_bytes;                                     // bytes of one A ring stage: (128*mb + 64) rows
-  int base_off_mode;                               // descriptor base_offset policy for shifted A tiles (bring-up knob)
+  // Flat MMA issue schedule, [phase][n_steps]: one entry per (group, K chunk, tap) in issue order.
+  //   bits 0-15  tap's row shift inside the halo tile, in 16-byte units (shift * row bytes / 16)
+  //   bits 16-27 resident weights: index of the tap's weight tile within the (phase, n_tile) block;
+  //              streamed weights: index of the tap's tile within its ring stage (< wt)
+  //   bits 28-31 kSchedWFirst / kSchedWLast / kSchedFirst / kSchedLast
+  int n_steps;
+  uint32_t sched[kMaxSched];
+  int dbg;   // -DMB200_PROBE builds only: 1 skip weight loads, 2 skip A loads, 4 skip MMAs, 8 skip epilogue work
+  long long* dbg_out;   // -DMB200_PROBE builds only: per-CTA cycle counters [grid][16]
 };
 
 struct EpiParams {

@@ -1,91 +1,65 @@
 // Persistent tcgen05 conv-GEMM (the production tensor-core kernel).
 //
-// One CTA per SM loops over output tiles (128 rows x NTILE channels).  Warp roles:
-//   warp 0      TMA producer: per K chunk ONE halo load of the A tile (128 + 8*extra rows, 128B/64B swizzle) that all
-//               taps of the conv reuse, plus the weight tiles (streamed, or loaded once and kept resident when the
+// One CTA per SM loops over output tiles (mb x 128 rows x NTILE channels).  Warp roles:
+//   warp 0      TMA producer: per K chunk ONE halo load of the A tile (128*mb + 8*extra rows, 128B/64B swizzle) that
+//               all taps of the conv reuse, plus the weight tiles (streamed, or loaded once and kept resident when the
 //               whole weight matrix fits beside the A ring -- the 64/32-channel HiFi-GAN stages).
-//   warp 1      TMEM owner + single-thread tcgen05.mma issuer; taps address the halo tile through row-shifted
-//               shared-memory descriptors.  Accumulators are a ring of NACC TMEM buffers.
-//   warps 2-5, 6-9   two epilogue groups that drain alternate tiles (tcgen05.ld -> fused epilogue -> global), so the
-//               epilogue of tile i overlaps the loads and MMAs of tiles i+1, i+2.
+//   warp 1      TMEM owner; issues every tcgen05.mma from a flat host-built schedule (ConvGeom2::sched):
+//               taps address the halo tile through row-shifted shared-memory descriptors, operands advance by 32-bit
+//               adds on the descriptors' low words.  Accumulators are a ring of NACC TMEM buffers.
+//   warps 2-9   epilogue (epilogue3.cuh): the eight warps split every tile's 32-column blocks between them, so the
+//               epilogue of tile i overlaps the loads and MMAs of tile i+1.
 #include "conv.cuh"
-#include "epilogue2.cuh"
+#include "epilogue3.cuh"
 #include "launch.h"
 #include "ptx.cuh"
 
 namespace mb {
 
-constexpr int kARows = 192;  // halo capacity: 128 + 8*8 rows (largest span on the path is 50: k=11, dilation 5)
+#ifdef MB200_PROBE
+#define MB_DBG(bit) (g.dbg & (bit))
+// cycle accounting of one role: total loop time and time spent inside barrier waits
+#define MB_T0() const long long probe_t0 = clock64(); long long probe_w = 0
+#define MB_WAIT(stmt) do { const long long probe_a = clock64(); stmt; probe_w += clock64() - probe_a; } while (0)
+#define MB_TEND(slot) do { if (lane == 0 && g.dbg_out) { g.dbg_out[blockIdx.x * 16 + 2 * (slot)] = clock64() - probe_t0; g.dbg_out[blockIdx.x * 16 + 2 * (slot) + 1] = probe_w; } } while (0)
+#else
+#define MB_DBG(bit) false
+#define MB_T0()
+#define MB_WAIT(stmt) stmt
+#define MB_TEND(slot)
+#endif
+
 constexpr int kMaxRing = 8;
+constexpr int kBarBytes = 512;   // mbarriers + TMEM slot
 
-template <int NTILE, typename T>
-__device__ __forceinline__ void epilogue_tile(const EpiParams& e, int b, int t, bool valid, int phase, int nbase,
-                                              uint32_t taddr) {
-  float v[32];
-  if (e.ln_out == nullptr || NTILE != 256) {
-#pragma unroll 1
-    for (int c = 0; c < NTILE / 32; ++c) {
-      tmem_ld_32x32(taddr + c * 32, v);
-      tmem_ld_wait();
-      epilogue_chunk<T>(e, b, t, phase, nbase + c * 32, valid, true, v);
-    }
-  } else {
-    float s = 0.f, ss = 0.f;
-#pragma unroll 1
-    for (int c = 0; c < NTILE / 32; ++c) {
-      tmem_ld_32x32(taddr + c * 32, v);
-      tmem_ld_wait();
-      epilogue_chunk<T>(e, b, t, phase, nbase + c * 32, valid, true, v);
-#pragma unroll
-      for (int i = 0; i < 32; ++i) { s += v[i]; ss += v[i] * v[i]; }
-    }
-    const float mean = s * (1.f / 256.f);
-    const float rstd = rsqrtf(fmaxf(ss * (1.f / 256.f) - mean * mean, 0.f) + 1e-5f);
-    const long row = static_cast<long>(b) * e.T_o + t * e.o_mul + phase * e.o_phase_step;
-#pragma unroll 1
-    for (int c = 0; c < NTILE / 32; ++c) {
-      tmem_ld_32x32(taddr + c * 32, v);
-      tmem_ld_wait();
-      epilogue_chunk<T>(e, b, t, phase, nbase + c * 32, valid, false, v);
-      if (valid) {
-        T* dst = reinterpret_cast<T*>(e.ln_out) + row * e.ln_ld + c * 32;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          float o[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int n = c * 32 + 8 * j + i;
-            o[i] = (v[8 * j + i] - mean) * rstd * __ldg(e.ln_g + n) + __ldg(e.ln_b + n);
-          }
-          Elem<T>::st8(dst + 8 * j, o);
-        }
-      }
-    }
-  }
-}
-
-template <int NTILE, int KC, typename T>
+template <int NTILE, int KC, int MB, typename T>
 __global__ void __launch_bounds__(320, 1)
 conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                        const __grid_constant__ CUtensorMap tmA0x, const __grid_constant__ CUtensorMap tmA1x,
                        const __grid_constant__ CUtensorMap tmW, const __grid_constant__ ConvGeom2 g,
                        const __grid_constant__ EpiParams e) {
+#ifdef MB200_PROBE
+  const long long probe_k0 = clock64();
+#endif
   constexpr int ROWB = KC * 2;
   constexpr int W_TILE = NTILE * ROWB;
   constexpr int TMEM_COLS = 512;   // one CTA per SM: take all of TMEM
+  constexpr int SLOT_COLS = MB * NTILE;
+  constexpr int NACC = (512 / SLOT_COLS) < 4 ? (512 / SLOT_COLS) : 4;
+  constexpr int TROWS = 128 * MB;
   const int A_BYTES = g.a_bytes;
-  const int SLOT_COLS = g.mb * NTILE;
-  const int NACC = (512 / SLOT_COLS) < 4 ? (512 / SLOT_COLS) : 4;
-  const int TROWS = 128 * g.mb;
+  const int W_STAGE = g.wt * W_TILE;   // streamed weights: one ring stage holds the tiles of g.wt consecutive taps
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment for the swizzled tiles; offsets stay relative to smem_raw so accesses compile to LDS/STS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
 
   int kchunks = 0;  // K chunks per (phase, n_tile): sum over groups of chunks * taps
   for (int q = 0; q < g.n_groups; ++q) kchunks += g.g_chunks[q] * g.g_ntaps[q];
-  const int w_tiles = g.w_resident ? g.n_phases * g.n_tiles * kchunks : g.w_stages;
+  const int w_bytes = g.w_resident ? g.n_phases * g.n_tiles * kchunks * W_TILE : g.w_stages * W_STAGE;
   uint8_t* a_ring = smem;
   uint8_t* w_base = smem + g.a_stages * A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(w_base + static_cast<size_t>(w_tiles) * W_TILE);
+  uint8_t* tail = w_base + w_bytes;   // multiple of 1024 from smem
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
   uint64_t* a_full = bars;
   uint64_t* a_empty = a_full + kMaxRing;
   uint64_t* w_full = a_empty + kMaxRing;
@@ -94,8 +68,8 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   uint64_t* t_empty = t_full + 4;
   uint64_t* wres = t_empty + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres + 1);
-  // 8 warp-private epilogue staging tiles, 16-byte aligned
-  uint8_t* stage_base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(wres + 2) + 15) & ~uintptr_t(15));
+  uint8_t* stage_base = tail + kBarBytes;                                   // 8 warp-private staging tiles
+  float2* lnx = reinterpret_cast<float2*>(stage_base + 8 * kStageBytes);    // LayerNorm partial-sum exchange
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int np = g.n_tiles * g.n_phases;
@@ -103,7 +77,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmA0x); tma_prefetch_desc(&tmW);
     for (int s = 0; s < kMaxRing; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    for (int s = 0; s < 4; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4); }
+    for (int s = 0; s < 4; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 8); }
     mbar_init(wres, 1);
     fence_barrier_init();
   }
@@ -112,133 +86,181 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+#ifdef MB200_PROBE
+  const long long probe_k1 = clock64();
+#endif
 
   if (warp == 0) {
-    // ================================================================= TMA producer
-    if (lane == 0) {
-      if (g.w_resident) {
-        mbar_expect_tx(wres, static_cast<uint32_t>(w_tiles) * W_TILE);
+    // ================================================================= TMA producer (converged warp, elected issue)
+    if (g.w_resident) {
+      if (elect_one()) {
+        mbar_expect_tx(wres, static_cast<uint32_t>(w_bytes));
         for (int pn = 0; pn < np; ++pn)   // pn = phase * n_tiles + n_tile
           for (int kk = 0; kk < kchunks; ++kk)
             tma_load_2d(w_base + static_cast<size_t>(pn * kchunks + kk) * W_TILE, &tmW, wres, kk * KC,
                         (pn / g.n_tiles) * g.N + (pn % g.n_tiles) * NTILE);
       }
-      int as = 0, ws = 0;
-      uint32_t aph = 0, wph = 0;
-      for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
-        const int nn = tile % np, mm = tile / np;
-        const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
-        const int t0 = (mm % g.m_tiles) * TROWS, b = mm / g.m_tiles;
-        for (int q = 0; q < g.n_groups; ++q) {
-          const CUtensorMap* m128 = g.g_src[q] ? &tmA1 : &tmA0;
-          const CUtensorMap* m8 = g.g_src[q] ? &tmA1x : &tmA0x;
-          const int row0 = t0 + g.g_rowmin[phase][q], extra = g.g_extra[phase][q];
-          for (int c = 0; c < g.g_chunks[q]; ++c) {
-            mbar_wait(&a_empty[as], aph ^ 1);
-            uint8_t* dst = a_ring + as * A_BYTES;
-            mbar_expect_tx(&a_full[as], (TROWS + 8 * extra) * ROWB);
-            const int ch = g.g_ch[q] + c * KC;
-            for (int i = 0; i < g.mb; ++i) tma_load_3d(dst + i * 128 * ROWB, m128, &a_full[as], ch, row0 + 128 * i, b);
-            for (int x = 0; x < extra; ++x) tma_load_3d(dst + (TROWS + 8 * x) * ROWB, m8, &a_full[as], ch, row0 + TROWS + 8 * x, b);
-            if (++as == g.a_stages) { as = 0; aph ^= 1; }
-            if (!g.w_resident) {
-              for (int tp = 0; tp < g.g_ntaps[q]; ++tp) {
-                mbar_wait(&w_empty[ws], wph ^ 1);
-                mbar_expect_tx(&w_full[ws], W_TILE);
-                tma_load_2d(w_base + ws * W_TILE, &tmW, &w_full[ws], g.g_wk[q][tp] + c * KC, phase * g.N + n_tile * NTILE);
-                if (++ws == g.w_stages) { ws = 0; wph ^= 1; }
-              }
-            }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ================================================================= MMA issuer
-    constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 128, NTILE);
-    if (g.w_resident) mbar_wait(wres, 0);
-    int as = 0, ws = 0, it = 0;
-    uint32_t aph = 0, wph = 0;
-    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++it) {
-      const int nn = tile % np;
-      const int phase = nn / g.n_tiles;
-      const int slot = it % NACC;
-      mbar_wait(&t_empty[slot], (((it / NACC) & 1) ^ 1));
-      tc_fence_after();
-      const uint32_t dtm = tmem_base + slot * SLOT_COLS;
-      uint32_t first = 1;
-      for (int q = 0; q < g.n_groups; ++q) {
-        for (int c = 0; c < g.g_chunks[q]; ++c) {
-          mbar_wait(&a_full[as], aph);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(a_ring + as * A_BYTES);
-          for (int tp = 0; tp < g.g_ntaps[q]; ++tp) {
-            uint32_t w_addr;
-            if (g.w_resident) {
-              w_addr = smem_u32(w_base + static_cast<size_t>(nn * kchunks + (g.g_wk[q][tp] / KC) + c) * W_TILE);
-            } else {
-              mbar_wait(&w_full[ws], wph);
-              tc_fence_after();
-              w_addr = smem_u32(w_base + ws * W_TILE);
-            }
-            if (lane == 0) {
-              const uint64_t bdesc = umma_smem_desc<ROWB>(w_addr);
-              for (int i = 0; i < g.mb; ++i) {   // the weight tile is reused by every 128-row block of the tile
-                const uint32_t sa = a_addr + (g.g_shift[phase][q][tp] + 128 * i) * ROWB;
-                uint64_t adesc = umma_smem_desc<ROWB>(sa);
-                if (g.base_off_mode) adesc |= static_cast<uint64_t>((sa >> 7) & 7) << 49;
-#pragma unroll
-                for (int k = 0; k < KC / 16; ++k)
-                  umma_f16(dtm + i * NTILE, adesc + 2 * k, bdesc + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
-              }
-              if (!g.w_resident) umma_commit(&w_empty[ws]);
-            }
-            __syncwarp();
-            if (!g.w_resident) { if (++ws == g.w_stages) { ws = 0; wph ^= 1; } }
-            first = 0;
-          }
-          if (lane == 0) umma_commit(&a_empty[as]);
-          __syncwarp();
-          if (++as == g.a_stages) { as = 0; aph ^= 1; }
-        }
-      }
-      if (lane == 0) umma_commit(&t_full[slot]);
       __syncwarp();
     }
-  } else {
-    // ================================================================= epilogue groups
-    const int grp = (warp - 2) >> 2;       // 0: warps 2-5, 1: warps 6-9
-    const int lane_grp = warp & 3;         // TMEM lanes [32*(warp%4), +32)
-    int it = grp;
-    for (int tile = blockIdx.x + grp * gridDim.x; tile < g.total_tiles; tile += 2 * gridDim.x, it += 2) {
+    int as = 0, ws = 0;
+    uint32_t aph = 0, wph = 0;
+    MB_T0();
+    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
       const int nn = tile % np, mm = tile / np;
       const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
       const int t0 = (mm % g.m_tiles) * TROWS, b = mm / g.m_tiles;
-      const int slot = it % NACC;
-      mbar_wait(&t_full[slot], (it / NACC) & 1);
-      tc_fence_after();
-      for (int i = 0; i < g.mb; ++i) {
-        const int tw = t0 + 128 * i + lane_grp * 32;
-        if (tw >= g.T_out) break;   // warp-uniform: nothing of this block exists
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * SLOT_COLS + i * NTILE;
-        if (epi2_supported(e))
-          epilogue_tile2<NTILE, T>(e, b, tw, g.T_out, phase, n_tile * NTILE, taddr, stage_base + (warp - 2) * kStageBytes, lane);
-        else
-          epilogue_tile<NTILE, T>(e, b, tw + lane, tw + lane < g.T_out, phase, n_tile * NTILE, taddr);
+      for (int q = 0; q < g.n_groups; ++q) {
+        const CUtensorMap* m128 = g.g_src[q] ? &tmA1 : &tmA0;
+        const CUtensorMap* m8 = g.g_src[q] ? &tmA1x : &tmA0x;
+        const int row0 = t0 + g.g_rowmin[phase][q], extra = g.g_extra[phase][q];
+        const int ntaps = g.g_ntaps[q];
+        for (int c = 0; c < g.g_chunks[q]; ++c) {
+          MB_WAIT(mbar_wait(&a_empty[as], aph ^ 1));
+          if (elect_one()) {
+            uint8_t* dst = a_ring + as * A_BYTES;
+            const int ch = g.g_ch[q] + c * KC;
+            if (MB_DBG(2)) {
+              mbar_arrive(&a_full[as]);
+            } else {
+              mbar_expect_tx(&a_full[as], (TROWS + 8 * extra) * ROWB);
+#pragma unroll
+              for (int i = 0; i < MB; ++i) tma_load_3d(dst + i * 128 * ROWB, m128, &a_full[as], ch, row0 + 128 * i, b);
+              for (int x = 0; x < extra; ++x) tma_load_3d(dst + (TROWS + 8 * x) * ROWB, m8, &a_full[as], ch, row0 + TROWS + 8 * x, b);
+            }
+          }
+          __syncwarp();
+          if (++as == g.a_stages) { as = 0; aph ^= 1; }
+          if (!g.w_resident) {
+            for (int tp = 0; tp < ntaps; tp += g.wt) {   // one ring stage = up to wt taps of this K chunk
+              const int nt = min(g.wt, ntaps - tp);
+              MB_WAIT(mbar_wait(&w_empty[ws], wph ^ 1));
+              if (elect_one()) {
+                if (MB_DBG(1)) {
+                  mbar_arrive(&w_full[ws]);
+                } else {
+                  mbar_expect_tx(&w_full[ws], nt * W_TILE);
+                  for (int j = 0; j < nt; ++j)
+                    tma_load_2d(w_base + ws * W_STAGE + j * W_TILE, &tmW, &w_full[ws], g.g_wk[q][tp + j] + c * KC,
+                                phase * g.N + n_tile * NTILE);
+                }
+              }
+              __syncwarp();
+              if (++ws == g.w_stages) { ws = 0; wph ^= 1; }
+            }
+          }
+        }
       }
+    }
+    MB_TEND(0);
+  } else if (warp == 1) {
+    // ================================================================= MMA issuer (converged warp, elected issue)
+    constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 128, NTILE);
+    constexpr uint32_t W16 = W_TILE >> 4, BLK16 = (128 * ROWB) >> 4;
+    const uint32_t desc_hi = static_cast<uint32_t>(umma_smem_desc<ROWB>(0) >> 32);
+    const uint32_t a_lo0 = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(a_ring)));
+    const uint32_t w_lo0 = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(w_base)));
+    const uint32_t a_stage16 = static_cast<uint32_t>(A_BYTES) >> 4, w_stage16 = static_cast<uint32_t>(W_STAGE) >> 4;
+    const int n_steps = g.n_steps, resident = g.w_resident;
+    if (resident) { mbar_wait(wres, 0); tc_fence_after(); }
+    int as = 0, ws = 0, slot = 0;
+    uint32_t aph = 0, wph = 0, tph = 0;
+    bool w_ready = false;   // result of the early probe of the next weight stage's barrier
+    MB_T0();
+    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
+      const int nn = tile % np;
+      const uint32_t* sch = g.sched + (nn / g.n_tiles) * n_steps;
+      const bool last_tile = tile + static_cast<int>(gridDim.x) >= g.total_tiles;
+      MB_WAIT(mbar_wait(&t_empty[slot], tph ^ 1));
+      const uint32_t dtm = tmem_base + slot * SLOT_COLS;
+      const uint32_t wres_lo = w_lo0 + static_cast<uint32_t>(nn * kchunks) * W16;
+      uint32_t a_lo = 0;
+      uint32_t en = sch[0];
+#pragma unroll 1
+      for (int s = 0; s < n_steps; ++s) {
+        const uint32_t en_next = sch[s + 1 < n_steps ? s + 1 : 0];
+        if (en & kSchedFirst) {
+          MB_WAIT(mbar_wait(&a_full[as], aph));
+          a_lo = a_lo0 + as * a_stage16;
+        }
+        uint32_t w_lo;
+        if (resident) {
+          w_lo = wres_lo + ((en >> 16) & 0xfffu) * W16;
+        } else {
+          if ((en & kSchedWFirst) && !w_ready) MB_WAIT(mbar_wait(&w_full[ws], wph));
+          w_lo = w_lo0 + ws * w_stage16 + ((en >> 16) & 0xfffu) * W16;
+        }
+        int ws_n = ws;
+        uint32_t wph_n = wph;
+        if (!resident && (en & kSchedWLast)) {
+          if (++ws_n == g.w_stages) { ws_n = 0; wph_n ^= 1; }
+          // probe the next stage's barrier now: the answer arrives while this step's MMAs are being issued
+          w_ready = (s + 1 < n_steps || !last_tile) ? mbar_try_wait(&w_full[ws_n], wph_n) : false;
+        }
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a = a_lo + (en & 0xffffu);
+          const uint32_t acc0 = s != 0;
+#pragma unroll
+          for (int i = 0; i < MB; ++i) {   // the weight tile is reused by every 128-row block of the tile
+#pragma unroll
+            for (int k = 0; k < KC / 16; ++k)
+              if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a + i * BLK16 + 2 * k, w_lo + 2 * k, desc_hi, idesc, k == 0 ? acc0 : 1u);
+          }
+          if (!resident && (en & kSchedWLast)) umma_commit(&w_empty[ws]);
+          if (en & kSchedLast) umma_commit(&a_empty[as]);
+          if (s == n_steps - 1) umma_commit(&t_full[slot]);
+        }
+        __syncwarp();
+        ws = ws_n; wph = wph_n;
+        if (en & kSchedLast) { if (++as == g.a_stages) { as = 0; aph ^= 1; } }
+        en = en_next;
+      }
+      if (++slot == NACC) { slot = 0; tph ^= 1; }
+    }
+    MB_TEND(1);
+  } else {
+    // ================================================================= epilogue: warps 2-5 (group 0), 6-9 (group 1)
+    const int grp = (warp - 2) >> 2;
+    const int lane_grp = warp & 3;         // TMEM lanes [32*(warp%4), +32)
+    uint8_t* stg = stage_base + (warp - 2) * kStageBytes;
+    int slot = 0, it = 0;
+    uint32_t tph = 0;
+    MB_T0();
+    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++it) {
+      const int nn = tile % np, mm = tile / np;
+      const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
+      const int t0 = (mm % g.m_tiles) * TROWS, b = mm / g.m_tiles;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * SLOT_COLS;
+#ifdef MB200_PROBE
+      if (MB_DBG(8)) {
+        MB_WAIT(mbar_wait(&t_full[slot], tph));
+      } else {
+        epilogue_tile3<NTILE, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, MB, taddr, stg, lnx + (it & 1) * 256, lane,
+                                 lane_grp, grp, &t_full[slot], tph, &probe_w);
+      }
+#else
+      epilogue_tile3<NTILE, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, MB, taddr, stg, lnx + (it & 1) * 256, lane,
+                               lane_grp, grp, &t_full[slot], tph);
+#endif
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&t_empty[slot]);
+      if (++slot == NACC) { slot = 0; tph ^= 1; }
     }
+    if (warp == 2) { MB_TEND(2); }
+    if (warp == 6) { MB_TEND(3); }
   }
   tc_fence_before();
   __syncthreads();
+#ifdef MB200_PROBE
+  if (threadIdx.x == 0 && g.dbg_out) { g.dbg_out[blockIdx.x * 16 + 8] = clock64() - probe_k0; g.dbg_out[blockIdx.x * 16 + 9] = probe_k1 - probe_k0; }
+#endif
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-template <int NTILE, int KC, typename T>
+template <int NTILE, int KC, int MB, typename T>
 static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
-  auto kern = conv_gemm_umma2_kernel<NTILE, KC, T>;
+  auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, T>;
   static int configured = 0;
   if (configured < L.smem_bytes) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -252,12 +274,16 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
 
 template <typename T>
 cudaError_t launch_conv_umma2(const ConvLaunch& L, cudaStream_t st) {
-  const int nt = L.ntile, kc = L.kc;
-  if (kc == 64 && nt == 256) return launch_umma2_inst<256, 64, T>(L, st);
-  if (kc == 64 && nt == 128) return launch_umma2_inst<128, 64, T>(L, st);
-  if (kc == 64 && nt == 64) return launch_umma2_inst<64, 64, T>(L, st);
-  if (kc == 64 && nt == 32) return launch_umma2_inst<32, 64, T>(L, st);
-  if (kc == 32 && nt == 32) return launch_umma2_inst<32, 32, T>(L, st);
+  const int nt = L.ntile, kc = L.kc, mb = L.g2.mb;
+  if (kc == 64 && nt == 256 && mb == 1) return launch_umma2_inst<256, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 128 && mb == 1) return launch_umma2_inst<128, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 128 && mb == 2) return launch_umma2_inst<128, 64, 2, T>(L, st);
+  if (kc == 64 && nt == 64 && mb == 1) return launch_umma2_inst<64, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 64 && mb == 2) return launch_umma2_inst<64, 64, 2, T>(L, st);
+  if (kc == 64 && nt == 32 && mb == 1) return launch_umma2_inst<32, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 32 && mb == 4) return launch_umma2_inst<32, 64, 4, T>(L, st);
+  if (kc == 32 && nt == 32 && mb == 1) return launch_umma2_inst<32, 32, 1, T>(L, st);
+  if (kc == 32 && nt == 32 && mb == 4) return launch_umma2_inst<32, 32, 4, T>(L, st);
   return cudaErrorInvalidConfiguration;
 }
 template cudaError_t launch_conv_umma2<__nv_bfloat16>(const ConvLaunch&, cudaStream_t);

@@ -1,0 +1,344 @@
+// Epilogue of the persistent tcgen05 kernel.
+//
+// tcgen05.ld hands every thread one accumulator ROW (32 lanes = 32 rows x 32 fp32 columns).  Doing the fused
+// element-wise work in that layout makes every global access touch 32 different lines and needs one scalar load per
+// channel parameter.  Instead each warp transposes its 32x32 fp32 block once through a private shared-memory tile
+// (pitch 144 B, conflict-free both ways) into a COALESCED layout:
+//     lane = 4*rq + p   ->  rows rq, rq+8, rq+16, rq+24 ; channels 8p .. 8p+7 of the 32-column block
+// so that every residual / GroupNorm input / output access is a 16-byte piece of a 64-byte row segment (four lanes per
+// row, fully used sectors), channel parameters are two float4 loads per block, and the first input stream of the next
+// block is requested before the current block is processed (and before the accumulator barrier is waited on).
+//
+// A tile's (128-row block, 32-column block) items are split between the two epilogue groups, so all eight warps drain
+// every tile.  LayerNorm row sums are exchanged between the two warps that share a row through shared memory.
+#pragma once
+#include "conv.cuh"
+#include "ptx.cuh"
+
+namespace mb {
+
+constexpr int kStagePitch = 144;                 // bytes per staged row: 32 fp32 + 16 B pad
+constexpr int kStageBytes = 32 * kStagePitch;    // per epilogue warp
+constexpr int kLnXFloat2 = 2 * 2 * 128;          // [tile parity][group][row] partial LayerNorm sums
+
+__device__ __forceinline__ float mish_fast(float x) {
+  if (x > 20.f) return x;
+  const float n = __expf(x);
+  const float w = n * (n + 2.f);
+  return x * __fdividef(w, w + 2.f);
+}
+
+template <typename T> __device__ __forceinline__ void unpack8(const uint4& u, float* f);
+template <> __device__ __forceinline__ void unpack8<__half>(const uint4& u, float* f) {
+  const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 x = __half22float2(h[i]); f[2 * i] = x.x; f[2 * i + 1] = x.y; }
+}
+template <> __device__ __forceinline__ void unpack8<__nv_bfloat16>(const uint4& u, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 x = __bfloat1622float2(h[i]); f[2 * i] = x.x; f[2 * i + 1] = x.y; }
+}
+template <typename T> __device__ __forceinline__ uint4 pack8(const float* f);
+template <> __device__ __forceinline__ uint4 pack8<__half>(const float* f) {
+  uint4 u; __half2* h = reinterpret_cast<__half2*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+template <> __device__ __forceinline__ uint4 pack8<__nv_bfloat16>(const float* f) {
+  uint4 u; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+__device__ __forceinline__ void ldg8f(const float* p, float* f) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+// 8 consecutive elements of an activation row, stored as T or as fp32
+template <typename T>
+__device__ __forceinline__ void load8(const void* base, long elem, int f32, float* f) {
+  if (f32) {
+    const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(base) + elem);
+    const float4 a = p[0], b = p[1];
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+  } else {
+    unpack8<T>(*reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(base) + elem), f);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void store8(void* base, long elem, int f32, const float* f) {
+  if (f32) {
+    float4* p = reinterpret_cast<float4*>(reinterpret_cast<float*>(base) + elem);
+    p[0] = make_float4(f[0], f[1], f[2], f[3]);
+    p[1] = make_float4(f[4], f[5], f[6], f[7]);
+  } else {
+    *reinterpret_cast<uint4*>(reinterpret_cast<T*>(base) + elem) = pack8<T>(f);
+  }
+}
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+// Everything one epilogue warp does for one tile.  `tmem_tile` already holds the warp's lane offset and the accumulator
+// slot; `lnx` is this tile's LayerNorm exchange buffer ([group][128 rows]).  The accumulator barrier is waited on here
+// so that the first input stream can be requested ahead of it.
+template <int NTILE, typename T>
+__device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, const int t0, const int T_out,
+                                               const int phase, const int nbase, const int mb, const uint32_t tmem_tile,
+                                               uint8_t* stg, float2* lnx, const int lane, const int lane_grp,
+                                               const int grp, uint64_t* t_full, const uint32_t t_parity,
+                                               long long* probe_wait = nullptr) {
+  constexpr int NP = NTILE / 32;            // 32-column blocks per 128-row block
+  const int p = lane & 3, rq = lane >> 2;
+  const long row_base = static_cast<long>(b) * e.T_o + phase * e.o_phase_step;
+  const int items = mb * NP;
+  const int tw0 = t0 + lane_grp * 32 + rq;  // this lane's first row of block 0
+  // stream A = the first half-precision input stream; it is requested one item ahead
+  const T* inA = reinterpret_cast<const T*>(e.gn_raw ? e.gn_raw : (e.resid_f32 ? nullptr : e.resid));
+  const int ldA = e.gn_raw ? e.gn_ld : e.resid_ld;
+  const bool resid_is_A = (e.gn_raw == nullptr) && (inA != nullptr);
+
+  auto issueA = [&](int item, uint4 (&u)[4]) {
+    const int i = item / NP, c = item % NP;
+    const int n0 = nbase + c * 32 + 8 * p;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int t = tw0 + 128 * i + 8 * k;
+      u[k] = make_uint4(0, 0, 0, 0);
+      if (t < T_out && n0 < e.n_valid)
+        u[k] = __ldg(reinterpret_cast<const uint4*>(inA + (row_base + static_cast<long>(t) * e.o_mul) * ldA + n0));
+    }
+  };
+
+  uint4 nxt[4];
+  int item = grp;
+  if (inA && item < items) issueA(item, nxt);
+  if (probe_wait) {
+    const long long a = clock64();
+    mbar_wait(t_full, t_parity);
+    *probe_wait += clock64() - a;
+  } else {
+    mbar_wait(t_full, t_parity);
+  }
+  tc_fence_after();
+
+  const bool do_ln = (NTILE == 256) && (e.ln_out != nullptr);
+  float ln_s[4] = {0.f, 0.f, 0.f, 0.f}, ln_ss[4] = {0.f, 0.f, 0.f, 0.f};
+
+#pragma unroll 1
+  for (; item < items; item += 2) {
+    const int i = item / NP, c = item % NP;
+    uint4 cur[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) cur[k] = nxt[k];
+    if (inA && item + 2 < items) issueA(item + 2, nxt);
+    if (t0 + 128 * i + lane_grp * 32 >= T_out) continue;   // warp-uniform: no row of this block exists
+
+    // ---- accumulators: TMEM -> registers (row per lane) -> staging -> coalesced layout
+    float v[4][8];
+    {
+      float acc[32];
+      tmem_ld_32x32(tmem_tile + i * NTILE + c * 32, acc);
+      tmem_ld_wait();
+      float4* srow = reinterpret_cast<float4*>(stg + lane * kStagePitch);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) srow[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float4* q = reinterpret_cast<const float4*>(stg + (rq + 8 * k) * kStagePitch + p * 32);
+        const float4 x = q[0], y = q[1];
+        v[k][0] = x.x; v[k][1] = x.y; v[k][2] = x.z; v[k][3] = x.w;
+        v[k][4] = y.x; v[k][5] = y.y; v[k][6] = y.z; v[k][7] = y.w;
+      }
+      __syncwarp();
+    }
+    const int n0 = nbase + c * 32 + 8 * p;
+    const bool cv = n0 < e.n_valid;
+    bool rok[4];
+    long grow[4];
+    float m[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int t = tw0 + 128 * i + 8 * k;
+      rok[k] = t < T_out;
+      grow[k] = row_base + static_cast<long>(t) * e.o_mul;
+      m[k] = (e.mask && rok[k]) ? __ldg(e.mask + grow[k]) : 1.f;
+    }
+    if (e.bias) {
+      float bv[8];
+      ldg8f(e.bias + n0, bv);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] += bv[ch];
+    }
+    if (e.gn_raw) {
+      const float* st = e.gn_stats + (static_cast<long>(b) * 8 + (n0 >> 5)) * 2;
+      const float mean = st[0] * e.gn_inv_count;
+      const float rstd = rsqrtf(fmaxf(st[1] * e.gn_inv_count - mean * mean, 0.f) + 1e-5f);
+      float ga[8], be[8];
+      ldg8f(e.gn_gamma + n0, ga);
+      ldg8f(e.gn_beta + n0, be);
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) { ga[ch] *= rstd; be[ch] -= mean * ga[ch]; }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float r[8];
+        unpack8<T>(cur[k], r);
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] += mish_fast(fmaf(r[ch], ga[ch], be[ch])) * m[k];
+      }
+    }
+    if (e.resid) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float r[8];
+        if (resid_is_A) {
+          unpack8<T>(cur[k], r);
+        } else {
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) r[ch] = 0.f;
+          if (rok[k] && cv) load8<T>(e.resid, grow[k] * e.resid_ld + n0, e.resid_f32, r);
+        }
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] += r[ch];
+      }
+    }
+    if (e.resid2) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (rok[k] && cv) {
+          float r[8];
+          load8<T>(e.resid2, grow[k] * e.resid2_ld + n0, e.resid2_f32, r);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) v[k][ch] += r[ch];
+        }
+      }
+    }
+    if (e.scale != 1.f) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] *= e.scale;
+    }
+    if (e.snake_a) {
+      float sa[8], sb[8];
+      ldg8f(e.snake_a + n0, sa);
+      ldg8f(e.snake_invb + n0, sb);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) {
+          const float s = __sinf(v[k][ch] * sa[ch]);
+          v[k][ch] = fmaf(sb[ch] * s, s, v[k][ch]);
+        }
+    }
+    if (e.mask_out) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] *= m[k];
+    }
+    if (e.stats_out) {   // one GroupNorm group per 32-column block; warp-collective
+      float s = 0.f, ss = 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (rok[k]) {
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) { s += v[k][ch]; ss = fmaf(v[k][ch], v[k][ch], ss); }
+        }
+      s = warp_sum(s);
+      ss = warp_sum(ss);
+      if (lane == 0) {
+        float* st = e.stats_out + (static_cast<long>(b) * 8 + ((nbase + c * 32) >> 5)) * 2;
+        atomicAdd(st, s);
+        atomicAdd(st + 1, ss);
+      }
+    }
+    if (e.x_state) {     // Euler update of the fp32 state; the stored copy below is x * mask
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (rok[k] && cv) {
+          float x[8];
+          const long at = grow[k] * e.x_ld + n0;
+          load8<T>(e.x_state, at, 1, x);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) x[ch] = fmaf(e.dt, v[k][ch], x[ch]);
+          store8<T>(e.x_state, at, 1, x);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) v[k][ch] = x[ch] * m[k];
+        }
+    }
+    if (do_ln) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) { ln_s[k] += v[k][ch]; ln_ss[k] = fmaf(v[k][ch], v[k][ch], ln_ss[k]); }
+    }
+    if (e.out0) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (rok[k] && cv) {
+          float o[8];
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) o[ch] = e.out0_slope == 1.f ? v[k][ch] : fmaxf(v[k][ch], v[k][ch] * e.out0_slope);
+          store8<T>(e.out0, grow[k] * e.out0_ld + n0, e.out0_f32, o);
+        }
+    }
+    if (e.out1) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (rok[k] && cv) {
+          float o[8];
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) o[ch] = e.out1_slope == 1.f ? v[k][ch] : fmaxf(v[k][ch], v[k][ch] * e.out1_slope);
+          store8<T>(e.out1, grow[k] * e.out1_ld + n0, 0, o);
+        }
+    }
+  }
+
+  if (do_ln) {
+    // Row sums: four lanes share a row inside the warp, the other half of the columns belongs to the partner warp of
+    // the other epilogue group.  The finished row is re-read from out0 (this thread's own stores, operand dtype).
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      ln_s[k] += __shfl_xor_sync(0xffffffffu, ln_s[k], 1);
+      ln_ss[k] += __shfl_xor_sync(0xffffffffu, ln_ss[k], 1);
+      ln_s[k] += __shfl_xor_sync(0xffffffffu, ln_s[k], 2);
+      ln_ss[k] += __shfl_xor_sync(0xffffffffu, ln_ss[k], 2);
+      if (p == 0) lnx[grp * 128 + lane_grp * 32 + rq + 8 * k] = make_float2(ln_s[k], ln_ss[k]);
+    }
+    named_bar_sync(1 + lane_grp, 64);
+    float mean[4], rstd[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 o = lnx[(grp ^ 1) * 128 + lane_grp * 32 + rq + 8 * k];
+      mean[k] = (ln_s[k] + o.x) * (1.f / 256.f);
+      rstd[k] = rsqrtf(fmaxf((ln_ss[k] + o.y) * (1.f / 256.f) - mean[k] * mean[k], 0.f) + 1e-5f);
+    }
+#pragma unroll 1
+    for (int c = grp; c < NP; c += 2) {
+      const int n0 = c * 32 + 8 * p;
+      float ga[8], be[8];
+      ldg8f(e.ln_g + n0, ga);
+      ldg8f(e.ln_b + n0, be);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int t = tw0 + 8 * k;
+        if (t < T_out) {
+          const long row = row_base + static_cast<long>(t) * e.o_mul;
+          float x[8];
+          load8<T>(e.out0, row * e.out0_ld + n0, 0, x);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) x[ch] = fmaf((x[ch] - mean[k]) * rstd[k], ga[ch], be[ch]);
+          store8<T>(e.ln_out, row * e.ln_ld + n0, 0, x);
+        }
+      }
+    }
+  }
+}
+
+}  // namespace mb

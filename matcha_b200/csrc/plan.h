@@ -133,7 +133,7 @@ class Plan {
   long long bytes_allocated = 0;
   // built-in profiler: when on, programs run eagerly with an event pair around every op
   int kernel_version = 2;   // 2 = persistent conv_gemm2.cu (default), 1 = first non-persistent kernel (MB200_KERNEL=1)
-  int base_off_mode = 0;    // row-shifted A descriptors need no base_offset: the swizzle is a function of absolute smem address bits (measured; MB200_BASEOFF=1 to test the other policy)
+  long long* probe_out = nullptr;   // developer probe (MB200_DBG): cycle counters of the last conv_op built
   int num_sms = 148;
   bool profiling = false;
   double prof[kProfRegions][kProfKinds][3] = {};   // [region][kind] = {launches, milliseconds, flops}

@@ -37,7 +37,6 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   MB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
   MB_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
   if (const char* v = std::getenv("MB200_KERNEL")) kernel_version = std::atoi(v);
-  if (const char* v = std::getenv("MB200_BASEOFF")) base_off_mode = std::atoi(v);
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -282,20 +281,62 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     g2.m_tiles = (T_out + 128 * g2.mb - 1) / (128 * g2.mb);
     g2.n_tiles = W.N / W.ntile;
     g2.total_tiles = B * g2.m_tiles * g2.n_tiles * W.n_phases;
-    g2.base_off_mode = base_off_mode;
-    const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = W.ntile * W.kc * 2, budget = 182 * 1024;   // 227 KB minus barriers, alignment slack and 8 x 4.5 KB epilogue staging
+    // shared memory: A ring | weights | 1 KB alignment slack, 512 B barriers, 8 x 4.5 KB epilogue staging, 4 KB LayerNorm exchange
+    const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = W.ntile * W.kc * 2;
+    const int tail_bytes = 1024 + 512 + 8 * 4608 + 4096, budget = 227 * 1024 - tail_bytes;
     const long w_total = static_cast<long>(W.n_phases) * W.N * W.K_total * 2;
     g2.a_bytes = a_bytes;
     if (w_total <= 100 * 1024) {
       g2.w_resident = 1;
+      g2.wt = 1;
       g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
       g2.w_stages = 0;
-      L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + 2048 + 8 * 4608;
+      L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + tail_bytes;
     } else {
       g2.w_resident = 0;
       g2.a_stages = (W.ntile == 256 || g2.mb > 1) ? 2 : 3;
-      g2.w_stages = std::min(8, (budget - g2.a_stages * a_bytes) / w_tile);
-      L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * w_tile + 2048 + 8 * 4608;
+      // narrow tiles pair two taps per ring stage: half as many producer/issuer handshakes per tensor-pipe cycle
+      int max_taps = 1;
+      for (int q = 0; q < ng; ++q) max_taps = std::max(max_taps, g2.g_ntaps[q]);
+      g2.wt = (w_tile <= 16 * 1024 && max_taps >= 2) ? 2 : 1;
+      g2.w_stages = std::min(8, (budget - g2.a_stages * a_bytes) / (g2.wt * w_tile));
+      if (g2.w_stages < 2) throw Error("conv_op: weight ring does not fit");
+      L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * g2.wt * w_tile + tail_bytes;
+    }
+    if (e.ln_out && g2.mb != 1) throw Error("conv_op: fused LayerNorm needs single-block tiles");
+    if (e.ln_out && (!e.out0 || e.out0_f32)) throw Error("conv_op: fused LayerNorm re-reads out0 in the operand dtype");
+    g2.dbg = 0;
+    g2.dbg_out = nullptr;
+    if (const char* v = std::getenv("MB200_DBG")) {
+      g2.dbg = std::atoi(v);
+      g2.dbg_out = static_cast<long long*>(dalloc(148 * 16 * sizeof(long long)));
+      probe_out = g2.dbg_out;
+    }
+    // flat MMA issue schedule (see ConvGeom2::sched)
+    {
+      int steps = 0;
+      for (int q = 0; q < ng; ++q) steps += g2.g_chunks[q] * g2.g_ntaps[q];
+      if (steps * W.n_phases > kMaxSched) throw Error("conv_op: MMA schedule exceeds kMaxSched");
+      g2.n_steps = steps;
+      const int row16 = W.kc * 2 / 16;
+      for (int ph = 0; ph < W.n_phases; ++ph) {
+        int s = 0;
+        for (int q = 0; q < ng; ++q)
+          for (int c = 0; c < g2.g_chunks[q]; ++c)
+            for (int tp = 0; tp < g2.g_ntaps[q]; ++tp) {
+              uint32_t en = static_cast<uint32_t>(g2.g_shift[ph][q][tp] * row16);
+              if (g2.w_resident) {
+                en |= static_cast<uint32_t>(g2.g_wk[q][tp] / W.kc + c) << 16;
+              } else {
+                en |= static_cast<uint32_t>(tp % g2.wt) << 16;
+                if (tp % g2.wt == 0) en |= kSchedWFirst;
+                if (tp % g2.wt == g2.wt - 1 || tp == g2.g_ntaps[q] - 1) en |= kSchedWLast;
+              }
+              if (tp == 0) en |= kSchedFirst;
+              if (tp == g2.g_ntaps[q] - 1) en |= kSchedLast;
+              g2.sched[ph * steps + s++] = en;
+            }
+      }
     }
     L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8);
     L.tmA8[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 8) : L.tmA8[0];

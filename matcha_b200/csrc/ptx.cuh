@@ -12,13 +12,16 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One lane of a CONVERGED warp.  Role loops (TMA producer, MMA issuer) are run by the whole warp with the single-thread
+// instructions under this predicate: a lone thread spinning on an mbarrier while its 31 siblings sit at the final
+// __syncthreads was measured 3-7x slower per pipeline step than the converged form (tools/umma_issue.cu).
 __device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
+  uint32_t pred = 0;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "elect.sync _|p, 0xffffffff;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}\n"
-      : "=r"(pred));
+      "@p mov.s32 %0, 1;\n\t}\n"
+      : "+r"(pred));
   return pred != 0;
 }
 
@@ -125,6 +128,19 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Same, with both descriptors given as their low words (start address, LBO) plus the shared high word (SBO, version,
+// swizzle): the issue loop advances operands with 32-bit adds only.
+__device__ __forceinline__ void umma_f16_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %3};\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}\n" ::"r"(d_tmem),
+      "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
 // Arrives on the mbarrier once all previously issued tcgen05.mma of this thread have completed.
