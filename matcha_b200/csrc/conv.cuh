@@ -35,6 +35,7 @@ struct ConvGeom {
 // every tap of the group reuses it through a row-shifted shared-memory descriptor.
 constexpr int kMaxGroups = 4;
 constexpr int kMaxSched = 192;
+constexpr uint32_t kSchedNull = 1u << 27;    // padding entry: the issuer handles two entries per iteration
 constexpr uint32_t kSchedWFirst = 1u << 28;  // first tap of a streamed weight stage: wait for it
 constexpr uint32_t kSchedWLast = 1u << 29;   // last tap of a streamed weight stage: release it
 constexpr uint32_t kSchedFirst = 1u << 30;   // first tap of an A stage: wait for the halo tile
@@ -55,9 +56,10 @@ struct ConvGeom2 {
   int a_bytes;                                     // bytes of one A ring stage: (128*mb + 64) rows
   // Flat MMA issue schedule, [phase][n_steps]: one entry per (group, K chunk, tap) in issue order.
   //   bits 0-15  tap's row shift inside the halo tile, in 16-byte units (shift * row bytes / 16)
-  //   bits 16-27 resident weights: index of the tap's weight tile within the (phase, n_tile) block;
+  //   bits 16-26 resident weights: index of the tap's weight tile within the (phase, n_tile) block;
   //              streamed weights: index of the tap's tile within its ring stage (< wt)
-  //   bits 28-31 kSchedWFirst / kSchedWLast / kSchedFirst / kSchedLast
+  //   bits 27-31 kSchedNull / kSchedWFirst / kSchedWLast / kSchedFirst / kSchedLast
+  // Every K chunk's taps are padded to an even count, so n_steps is even and a pair never straddles an A stage.
   int n_steps;
   uint32_t sched[kMaxSched];
   int dbg;   // -DMB200_PROBE builds only: 1 skip weight loads, 2 skip A loads, 4 skip MMAs, 8 skip epilogue work

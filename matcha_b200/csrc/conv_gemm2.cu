@@ -164,56 +164,66 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     if (resident) { mbar_wait(wres, 0); tc_fence_after(); }
     int as = 0, ws = 0, slot = 0;
     uint32_t aph = 0, wph = 0, tph = 0;
-    bool w_ready = false;   // result of the early probe of the next weight stage's barrier
     MB_T0();
     for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
       const int nn = tile % np;
       const uint32_t* sch = g.sched + (nn / g.n_tiles) * n_steps;
-      const bool last_tile = tile + static_cast<int>(gridDim.x) >= g.total_tiles;
       MB_WAIT(mbar_wait(&t_empty[slot], tph ^ 1));
       const uint32_t dtm = tmem_base + slot * SLOT_COLS;
       const uint32_t wres_lo = w_lo0 + static_cast<uint32_t>(nn * kchunks) * W16;
       uint32_t a_lo = 0;
-      uint32_t en = sch[0];
 #pragma unroll 1
-      for (int s = 0; s < n_steps; ++s) {
-        const uint32_t en_next = sch[s + 1 < n_steps ? s + 1 : 0];
-        if (en & kSchedFirst) {
+      for (int s = 0; s < n_steps; s += 2) {   // two schedule entries (taps) per iteration
+        const uint32_t en0 = sch[s], en1 = sch[s + 1];
+        const bool two = !(en1 & kSchedNull);
+        if (en0 & kSchedFirst) {
           MB_WAIT(mbar_wait(&a_full[as], aph));
           a_lo = a_lo0 + as * a_stage16;
         }
-        uint32_t w_lo;
+        uint32_t w_lo_0, w_lo_1;
+        int ws1 = ws;          // ring stage of the second entry (== ws when both taps share one stage)
+        uint32_t wph1 = wph;
         if (resident) {
-          w_lo = wres_lo + ((en >> 16) & 0xfffu) * W16;
+          w_lo_0 = wres_lo + ((en0 >> 16) & 0x7ffu) * W16;
+          w_lo_1 = wres_lo + ((en1 >> 16) & 0x7ffu) * W16;
         } else {
-          if ((en & kSchedWFirst) && !w_ready) MB_WAIT(mbar_wait(&w_full[ws], wph));
-          w_lo = w_lo0 + ws * w_stage16 + ((en >> 16) & 0xfffu) * W16;
-        }
-        int ws_n = ws;
-        uint32_t wph_n = wph;
-        if (!resident && (en & kSchedWLast)) {
-          if (++ws_n == g.w_stages) { ws_n = 0; wph_n ^= 1; }
-          // probe the next stage's barrier now: the answer arrives while this step's MMAs are being issued
-          w_ready = (s + 1 < n_steps || !last_tile) ? mbar_try_wait(&w_full[ws_n], wph_n) : false;
+          MB_WAIT(mbar_wait(&w_full[ws], wph));
+          w_lo_0 = w_lo0 + ws * w_stage16 + ((en0 >> 16) & 0x7ffu) * W16;
+          if (two && (en1 & kSchedWFirst)) {
+            if (++ws1 == g.w_stages) { ws1 = 0; wph1 ^= 1; }
+            MB_WAIT(mbar_wait(&w_full[ws1], wph1));
+          }
+          w_lo_1 = w_lo0 + ws1 * w_stage16 + ((en1 >> 16) & 0x7ffu) * W16;
         }
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t a = a_lo + (en & 0xffffu);
+          const uint32_t a0 = a_lo + (en0 & 0xffffu), a1 = a_lo + (en1 & 0xffffu);
           const uint32_t acc0 = s != 0;
 #pragma unroll
           for (int i = 0; i < MB; ++i) {   // the weight tile is reused by every 128-row block of the tile
 #pragma unroll
             for (int k = 0; k < KC / 16; ++k)
-              if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a + i * BLK16 + 2 * k, w_lo + 2 * k, desc_hi, idesc, k == 0 ? acc0 : 1u);
+              if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a0 + i * BLK16 + 2 * k, w_lo_0 + 2 * k, desc_hi, idesc, k == 0 ? acc0 : 1u);
           }
-          if (!resident && (en & kSchedWLast)) umma_commit(&w_empty[ws]);
-          if (en & kSchedLast) umma_commit(&a_empty[as]);
-          if (s == n_steps - 1) umma_commit(&t_full[slot]);
+          if (!resident && (en0 & kSchedWLast)) umma_commit(&w_empty[ws]);
+          if (two) {
+#pragma unroll
+            for (int i = 0; i < MB; ++i) {
+#pragma unroll
+              for (int k = 0; k < KC / 16; ++k)
+                if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a1 + i * BLK16 + 2 * k, w_lo_1 + 2 * k, desc_hi, idesc, 1u);
+            }
+            if (!resident && (en1 & kSchedWLast)) umma_commit(&w_empty[ws1]);
+          }
+          if ((en0 | en1) & kSchedLast) umma_commit(&a_empty[as]);
+          if (s + 2 >= n_steps) umma_commit(&t_full[slot]);
         }
         __syncwarp();
-        ws = ws_n; wph = wph_n;
-        if (en & kSchedLast) { if (++as == g.a_stages) { as = 0; aph ^= 1; } }
-        en = en_next;
+        if (!resident) {
+          ws = ws1; wph = wph1;
+          if ((two ? en1 : en0) & kSchedWLast) { if (++ws == g.w_stages) { ws = 0; wph ^= 1; } }
+        }
+        if ((en0 | en1) & kSchedLast) { if (++as == g.a_stages) { as = 0; aph ^= 1; } }
       }
       if (++slot == NACC) { slot = 0; tph ^= 1; }
     }

@@ -125,6 +125,11 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
   tc_fence_after();
 
   const bool do_ln = (NTILE == 256) && (e.ln_out != nullptr);
+  // fp16 layers whose epilogue is only bias / residuals / scale / LeakyReLU (every HiFi-GAN conv) finish in packed half
+  // arithmetic: a third of the instructions of the general fp32 path; the extra roundings are fp16 ulps of values that
+  // are stored as fp16 anyway.  bf16 keeps the fp32 path.
+  const bool fast = std::is_same<T, __half>::value && !e.gn_raw && !e.snake_a && !e.mask && !e.mask_out && !e.stats_out &&
+                    !e.x_state && !do_ln && !e.out0_f32 && !e.resid_f32 && !e.resid2_f32;
   float ln_s[4] = {0.f, 0.f, 0.f, 0.f}, ln_ss[4] = {0.f, 0.f, 0.f, 0.f};
 
 #pragma unroll 1
@@ -135,6 +140,21 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
     for (int k = 0; k < 4; ++k) cur[k] = nxt[k];
     if (inA && item + 2 < items) issueA(item + 2, nxt);
     if (t0 + 128 * i + lane_grp * 32 >= T_out) continue;   // warp-uniform: no row of this block exists
+
+    const int n0 = nbase + c * 32 + 8 * p;
+    const bool cv = n0 < e.n_valid;
+    bool rok[4];
+    long grow[4];
+    float m[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int t = tw0 + 128 * i + 8 * k;
+      rok[k] = t < T_out;
+      grow[k] = row_base + static_cast<long>(t) * e.o_mul;
+      m[k] = (e.mask && rok[k]) ? __ldg(e.mask + grow[k]) : 1.f;
+    }
+    float bv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (e.bias) ldg8f(e.bias + n0, bv);   // in flight while the accumulators are fetched
 
     // ---- accumulators: TMEM -> registers (row per lane) -> staging -> coalesced layout
     float v[4][8];
@@ -150,30 +170,58 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
       for (int k = 0; k < 4; ++k) {
         const float4* q = reinterpret_cast<const float4*>(stg + (rq + 8 * k) * kStagePitch + p * 32);
         const float4 x = q[0], y = q[1];
-        v[k][0] = x.x; v[k][1] = x.y; v[k][2] = x.z; v[k][3] = x.w;
-        v[k][4] = y.x; v[k][5] = y.y; v[k][6] = y.z; v[k][7] = y.w;
+        v[k][0] = x.x + bv[0]; v[k][1] = x.y + bv[1]; v[k][2] = x.z + bv[2]; v[k][3] = x.w + bv[3];
+        v[k][4] = y.x + bv[4]; v[k][5] = y.y + bv[5]; v[k][6] = y.z + bv[6]; v[k][7] = y.w + bv[7];
       }
       __syncwarp();
     }
-    const int n0 = nbase + c * 32 + 8 * p;
-    const bool cv = n0 < e.n_valid;
-    bool rok[4];
-    long grow[4];
-    float m[4];
+    if (fast) {
+      // ---- packed-half path: bias + residual(s) + scale + LeakyReLU copies, two channels per instruction
+      if constexpr (std::is_same<T, __half>::value) {
+        const __half2 sc = __float2half2_rn(e.scale);
+        const __half2 s0 = __float2half2_rn(e.out0_slope), s1 = __float2half2_rn(e.out1_slope);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int t = tw0 + 128 * i + 8 * k;
-      rok[k] = t < T_out;
-      grow[k] = row_base + static_cast<long>(t) * e.o_mul;
-      m[k] = (e.mask && rok[k]) ? __ldg(e.mask + grow[k]) : 1.f;
-    }
-    if (e.bias) {
-      float bv[8];
-      ldg8f(e.bias + n0, bv);
+        for (int k = 0; k < 4; ++k) {
+          if (!(rok[k] && cv)) continue;
+          uint4 hu = pack8<__half>(v[k]);
+          __half2* h = reinterpret_cast<__half2*>(&hu);
+          if (e.resid) {
+            uint4 ru = resid_is_A ? cur[k] : *reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(e.resid) + grow[k] * e.resid_ld + n0);
+            const __half2* r = reinterpret_cast<const __half2*>(&ru);
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
+            for (int j = 0; j < 4; ++j) h[j] = __hadd2(h[j], r[j]);
+          }
+          if (e.resid2) {
+            const uint4 ru = *reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(e.resid2) + grow[k] * e.resid2_ld + n0);
+            const __half2* r = reinterpret_cast<const __half2*>(&ru);
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch) v[k][ch] += bv[ch];
+            for (int j = 0; j < 4; ++j) h[j] = __hadd2(h[j], r[j]);
+          }
+          if (e.scale != 1.f) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) h[j] = __hmul2(h[j], sc);
+          }
+          if (e.out0) {
+            uint4 ou = hu;
+            if (e.out0_slope != 1.f) {
+              __half2* o = reinterpret_cast<__half2*>(&ou);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], s0));
+            }
+            *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(e.out0) + grow[k] * e.out0_ld + n0) = ou;
+          }
+          if (e.out1) {
+            uint4 ou = hu;
+            if (e.out1_slope != 1.f) {
+              __half2* o = reinterpret_cast<__half2*>(&ou);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], s1));
+            }
+            *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(e.out1) + grow[k] * e.out1_ld + n0) = ou;
+          }
+        }
+      }
+      continue;
     }
     if (e.gn_raw) {
       const float* st = e.gn_stats + (static_cast<long>(b) * 8 + (n0 >> 5)) * 2;

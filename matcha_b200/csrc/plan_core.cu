@@ -315,27 +315,30 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     // flat MMA issue schedule (see ConvGeom2::sched)
     {
       int steps = 0;
-      for (int q = 0; q < ng; ++q) steps += g2.g_chunks[q] * g2.g_ntaps[q];
+      for (int q = 0; q < ng; ++q) steps += g2.g_chunks[q] * ((g2.g_ntaps[q] + 1) / 2 * 2);
       if (steps * W.n_phases > kMaxSched) throw Error("conv_op: MMA schedule exceeds kMaxSched");
       g2.n_steps = steps;
       const int row16 = W.kc * 2 / 16;
       for (int ph = 0; ph < W.n_phases; ++ph) {
         int s = 0;
         for (int q = 0; q < ng; ++q)
-          for (int c = 0; c < g2.g_chunks[q]; ++c)
-            for (int tp = 0; tp < g2.g_ntaps[q]; ++tp) {
+          for (int c = 0; c < g2.g_chunks[q]; ++c) {
+            const int nt = g2.g_ntaps[q];
+            for (int tp = 0; tp < nt; ++tp) {
               uint32_t en = static_cast<uint32_t>(g2.g_shift[ph][q][tp] * row16);
               if (g2.w_resident) {
                 en |= static_cast<uint32_t>(g2.g_wk[q][tp] / W.kc + c) << 16;
               } else {
                 en |= static_cast<uint32_t>(tp % g2.wt) << 16;
                 if (tp % g2.wt == 0) en |= kSchedWFirst;
-                if (tp % g2.wt == g2.wt - 1 || tp == g2.g_ntaps[q] - 1) en |= kSchedWLast;
+                if (tp % g2.wt == g2.wt - 1 || tp == nt - 1) en |= kSchedWLast;
               }
               if (tp == 0) en |= kSchedFirst;
-              if (tp == g2.g_ntaps[q] - 1) en |= kSchedLast;
+              if (tp == nt - 1) en |= kSchedLast;
               g2.sched[ph * steps + s++] = en;
             }
+            if (nt & 1) g2.sched[ph * steps + s++] = kSchedNull;
+          }
       }
     }
     L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8);

@@ -56,6 +56,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // Bounded wait: a pipeline bug must surface as a trapped launch (an error code at the C ABI),
 // never as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1   // keep the role loops small: they share an instruction cache with the epilogue warps
   for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
     if (mbar_try_wait(bar, parity)) return;
   }
