@@ -89,6 +89,9 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
 #ifdef MB200_PROBE
   const long long probe_k1 = clock64();
 #endif
+  // Programmatic dependent launch: everything above (and the resident weight loads below) overlaps the previous
+  // kernel's tail; activations are only touched after griddep_wait().
+  if (threadIdx.x == 0) griddep_launch();
 
   if (warp == 0) {
     // ================================================================= TMA producer (converged warp, elected issue)
@@ -102,6 +105,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       }
       __syncwarp();
     }
+    griddep_wait();
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0;
     MB_T0();
@@ -161,6 +165,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     const uint32_t w_lo0 = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(w_base)));
     const uint32_t a_stage16 = static_cast<uint32_t>(A_BYTES) >> 4, w_stage16 = static_cast<uint32_t>(W_STAGE) >> 4;
     const int n_steps = g.n_steps, resident = g.w_resident;
+    griddep_wait();
     if (resident) { mbar_wait(wres, 0); tc_fence_after(); }
     int as = 0, ws = 0, slot = 0;
     uint32_t aph = 0, wph = 0, tph = 0;
@@ -233,6 +238,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     const int grp = (warp - 2) >> 2;
     const int lane_grp = warp & 3;         // TMEM lanes [32*(warp%4), +32)
     uint8_t* stg = stage_base + (warp - 2) * kStageBytes;
+    griddep_wait();
     int slot = 0, it = 0;
     uint32_t tph = 0;
     MB_T0();
@@ -245,11 +251,11 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       if (MB_DBG(8)) {
         MB_WAIT(mbar_wait(&t_full[slot], tph));
       } else {
-        epilogue_tile3<NTILE, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, MB, taddr, stg, lnx + (it & 1) * 256, lane,
+        epilogue_tile3<NTILE, MB, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * 256, lane,
                                  lane_grp, grp, &t_full[slot], tph, &probe_w);
       }
 #else
-      epilogue_tile3<NTILE, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, MB, taddr, stg, lnx + (it & 1) * 256, lane,
+      epilogue_tile3<NTILE, MB, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * 256, lane,
                                lane_grp, grp, &t_full[slot], tph);
 #endif
       tc_fence_before();
@@ -278,8 +284,17 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
     configured = 227 * 1024;
   }
   const bool two = L.g.n_src > 1;
-  kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmA[0], L.tmA[two ? 1 : 0], L.tmA8[0], L.tmA8[two ? 1 : 0], L.tmW, L.g2, L.e);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(L.grid);
+  cfg.blockDim = dim3(320);
+  cfg.dynamicSmemBytes = L.smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = L.pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, L.tmA[0], L.tmA[two ? 1 : 0], L.tmA8[0], L.tmA8[two ? 1 : 0], L.tmW, L.g2, L.e);
 }
 
 template <typename T>

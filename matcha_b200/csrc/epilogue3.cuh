@@ -84,21 +84,26 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 // Everything one epilogue warp does for one tile.  `tmem_tile` already holds the warp's lane offset and the accumulator
 // slot; `lnx` is this tile's LayerNorm exchange buffer ([group][128 rows]).  The accumulator barrier is waited on here
 // so that the first input stream can be requested ahead of it.
-template <int NTILE, typename T>
+//
+// The profile of this function is flat and latency-bound (two epilogue warps per scheduler), so the code is organised
+// to keep the instruction count per 32x32 item low: options are tested once per item (feature-major, row-minor loops),
+// row offsets are 32-bit element indices computed once, and memory operations are predicated rather than branched.
+template <int NTILE, int MB, typename T>
 __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, const int t0, const int T_out,
-                                               const int phase, const int nbase, const int mb, const uint32_t tmem_tile,
+                                               const int phase, const int nbase, const uint32_t tmem_tile,
                                                uint8_t* stg, float2* lnx, const int lane, const int lane_grp,
                                                const int grp, uint64_t* t_full, const uint32_t t_parity,
                                                long long* probe_wait = nullptr) {
   constexpr int NP = NTILE / 32;            // 32-column blocks per 128-row block
+  constexpr int ITEMS = MB * NP;
   const int p = lane & 3, rq = lane >> 2;
-  const long row_base = static_cast<long>(b) * e.T_o + phase * e.o_phase_step;
-  const int items = mb * NP;
+  const int row_base = b * e.T_o + phase * e.o_phase_step;   // tensors on this path stay below 2^31 elements
   const int tw0 = t0 + lane_grp * 32 + rq;  // this lane's first row of block 0
   // stream A = the first half-precision input stream; it is requested one item ahead
   const T* inA = reinterpret_cast<const T*>(e.gn_raw ? e.gn_raw : (e.resid_f32 ? nullptr : e.resid));
   const int ldA = e.gn_raw ? e.gn_ld : e.resid_ld;
   const bool resid_is_A = (e.gn_raw == nullptr) && (inA != nullptr);
+  const int n_valid = e.n_valid, o_mul = e.o_mul;
 
   auto issueA = [&](int item, uint4 (&u)[4]) {
     const int i = item / NP, c = item % NP;
@@ -107,14 +112,13 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
     for (int k = 0; k < 4; ++k) {
       const int t = tw0 + 128 * i + 8 * k;
       u[k] = make_uint4(0, 0, 0, 0);
-      if (t < T_out && n0 < e.n_valid)
-        u[k] = __ldg(reinterpret_cast<const uint4*>(inA + (row_base + static_cast<long>(t) * e.o_mul) * ldA + n0));
+      if (t < T_out && n0 < n_valid) u[k] = __ldg(reinterpret_cast<const uint4*>(inA + static_cast<size_t>(row_base + t * o_mul) * ldA + n0));
     }
   };
 
   uint4 nxt[4];
   int item = grp;
-  if (inA && item < items) issueA(item, nxt);
+  if (inA && item < ITEMS) issueA(item, nxt);
   if (probe_wait) {
     const long long a = clock64();
     mbar_wait(t_full, t_parity);
@@ -133,25 +137,23 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
   float ln_s[4] = {0.f, 0.f, 0.f, 0.f}, ln_ss[4] = {0.f, 0.f, 0.f, 0.f};
 
 #pragma unroll 1
-  for (; item < items; item += 2) {
+  for (; item < ITEMS; item += 2) {
     const int i = item / NP, c = item % NP;
     uint4 cur[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) cur[k] = nxt[k];
-    if (inA && item + 2 < items) issueA(item + 2, nxt);
+    if (inA && item + 2 < ITEMS) issueA(item + 2, nxt);
     if (t0 + 128 * i + lane_grp * 32 >= T_out) continue;   // warp-uniform: no row of this block exists
 
     const int n0 = nbase + c * 32 + 8 * p;
-    const bool cv = n0 < e.n_valid;
-    bool rok[4];
-    long grow[4];
-    float m[4];
+    const bool cv = n0 < n_valid;
+    bool ok[4];     // row exists and this lane's channels exist: gates every load and store
+    int grow[4];    // output row index of the lane's four rows
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int t = tw0 + 128 * i + 8 * k;
-      rok[k] = t < T_out;
-      grow[k] = row_base + static_cast<long>(t) * e.o_mul;
-      m[k] = (e.mask && rok[k]) ? __ldg(e.mask + grow[k]) : 1.f;
+      ok[k] = (t < T_out) && cv;
+      grow[k] = row_base + t * o_mul;
     }
     float bv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (e.bias) ldg8f(e.bias + n0, bv);   // in flight while the accumulators are fetched
@@ -178,53 +180,84 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
     if (fast) {
       // ---- packed-half path: bias + residual(s) + scale + LeakyReLU copies, two channels per instruction
       if constexpr (std::is_same<T, __half>::value) {
-        const __half2 sc = __float2half2_rn(e.scale);
-        const __half2 s0 = __float2half2_rn(e.out0_slope), s1 = __float2half2_rn(e.out1_slope);
+        uint4 hu[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          if (!(rok[k] && cv)) continue;
-          uint4 hu = pack8<__half>(v[k]);
-          __half2* h = reinterpret_cast<__half2*>(&hu);
-          if (e.resid) {
-            uint4 ru = resid_is_A ? cur[k] : *reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(e.resid) + grow[k] * e.resid_ld + n0);
+        for (int k = 0; k < 4; ++k) hu[k] = pack8<__half>(v[k]);
+        if (e.resid) {
+          const __half* rp = reinterpret_cast<const __half*>(e.resid);
+          const int ld = e.resid_ld;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            uint4 ru = cur[k];
+            if (!resid_is_A) { ru = make_uint4(0, 0, 0, 0); if (ok[k]) ru = *reinterpret_cast<const uint4*>(rp + static_cast<size_t>(grow[k]) * ld + n0); }
+            __half2* h = reinterpret_cast<__half2*>(&hu[k]);
             const __half2* r = reinterpret_cast<const __half2*>(&ru);
 #pragma unroll
             for (int j = 0; j < 4; ++j) h[j] = __hadd2(h[j], r[j]);
           }
-          if (e.resid2) {
-            const uint4 ru = *reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(e.resid2) + grow[k] * e.resid2_ld + n0);
-            const __half2* r = reinterpret_cast<const __half2*>(&ru);
+        }
+        if (e.resid2) {
+          const __half* rp = reinterpret_cast<const __half*>(e.resid2);
+          const int ld = e.resid2_ld;
+          uint4 ru[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) { ru[k] = make_uint4(0, 0, 0, 0); if (ok[k]) ru[k] = *reinterpret_cast<const uint4*>(rp + static_cast<size_t>(grow[k]) * ld + n0); }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            __half2* h = reinterpret_cast<__half2*>(&hu[k]);
+            const __half2* r = reinterpret_cast<const __half2*>(&ru[k]);
 #pragma unroll
             for (int j = 0; j < 4; ++j) h[j] = __hadd2(h[j], r[j]);
           }
-          if (e.scale != 1.f) {
+        }
+        if (e.scale != 1.f) {
+          const __half2 sc = __float2half2_rn(e.scale);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            __half2* h = reinterpret_cast<__half2*>(&hu[k]);
 #pragma unroll
             for (int j = 0; j < 4; ++j) h[j] = __hmul2(h[j], sc);
           }
-          if (e.out0) {
-            uint4 ou = hu;
-            if (e.out0_slope != 1.f) {
-              __half2* o = reinterpret_cast<__half2*>(&ou);
+        }
+        if (e.out0) {   // LeakyReLU(x) = max(x, slope * x) for 0 < slope <= 1
+          __half* op = reinterpret_cast<__half*>(e.out0);
+          const int ld = e.out0_ld;
+          const __half2 sl = __float2half2_rn(e.out0_slope);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], s0));
-            }
-            *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(e.out0) + grow[k] * e.out0_ld + n0) = ou;
+          for (int k = 0; k < 4; ++k) {
+            uint4 ou;
+            __half2* o = reinterpret_cast<__half2*>(&ou);
+            const __half2* h = reinterpret_cast<const __half2*>(&hu[k]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], sl));
+            if (ok[k]) *reinterpret_cast<uint4*>(op + static_cast<size_t>(grow[k]) * ld + n0) = ou;
           }
-          if (e.out1) {
-            uint4 ou = hu;
-            if (e.out1_slope != 1.f) {
-              __half2* o = reinterpret_cast<__half2*>(&ou);
+        }
+        if (e.out1) {
+          __half* op = reinterpret_cast<__half*>(e.out1);
+          const int ld = e.out1_ld;
+          const __half2 sl = __float2half2_rn(e.out1_slope);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], s1));
-            }
-            *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(e.out1) + grow[k] * e.out1_ld + n0) = ou;
+          for (int k = 0; k < 4; ++k) {
+            uint4 ou;
+            __half2* o = reinterpret_cast<__half2*>(&ou);
+            const __half2* h = reinterpret_cast<const __half2*>(&hu[k]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], sl));
+            if (ok[k]) *reinterpret_cast<uint4*>(op + static_cast<size_t>(grow[k]) * ld + n0) = ou;
           }
         }
       }
       continue;
     }
+    // ---- general fp32 path
+    float m[4] = {1.f, 1.f, 1.f, 1.f};
+    if (e.mask) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) if (ok[k]) m[k] = __ldg(e.mask + grow[k]);
+    }
     if (e.gn_raw) {
-      const float* st = e.gn_stats + (static_cast<long>(b) * 8 + (n0 >> 5)) * 2;
+      const float* st = e.gn_stats + (b * 8 + (n0 >> 5)) * 2;
       const float mean = st[0] * e.gn_inv_count;
       const float rstd = rsqrtf(fmaxf(st[1] * e.gn_inv_count - mean * mean, 0.f) + 1e-5f);
       float ga[8], be[8];
@@ -241,6 +274,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
       }
     }
     if (e.resid) {
+      const int ld = e.resid_ld, f32 = e.resid_f32;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         float r[8];
@@ -249,28 +283,30 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
         } else {
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) r[ch] = 0.f;
-          if (rok[k] && cv) load8<T>(e.resid, grow[k] * e.resid_ld + n0, e.resid_f32, r);
+          if (ok[k]) load8<T>(e.resid, static_cast<long>(grow[k]) * ld + n0, f32, r);
         }
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) v[k][ch] += r[ch];
       }
     }
     if (e.resid2) {
+      const int ld = e.resid2_ld, f32 = e.resid2_f32;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        if (rok[k] && cv) {
-          float r[8];
-          load8<T>(e.resid2, grow[k] * e.resid2_ld + n0, e.resid2_f32, r);
+        float r[8];
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) v[k][ch] += r[ch];
-        }
+        for (int ch = 0; ch < 8; ++ch) r[ch] = 0.f;
+        if (ok[k]) load8<T>(e.resid2, static_cast<long>(grow[k]) * ld + n0, f32, r);
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] += r[ch];
       }
     }
     if (e.scale != 1.f) {
+      const float sc = e.scale;
 #pragma unroll
       for (int k = 0; k < 4; ++k)
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch) v[k][ch] *= e.scale;
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] *= sc;
     }
     if (e.snake_a) {
       float sa[8], sb[8];
@@ -280,8 +316,8 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
       for (int k = 0; k < 4; ++k)
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) {
-          const float s = __sinf(v[k][ch] * sa[ch]);
-          v[k][ch] = fmaf(sb[ch] * s, s, v[k][ch]);
+          const float sn = __sinf(v[k][ch] * sa[ch]);
+          v[k][ch] = fmaf(sb[ch] * sn, sn, v[k][ch]);
         }
     }
     if (e.mask_out) {
@@ -291,30 +327,32 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
         for (int ch = 0; ch < 8; ++ch) v[k][ch] *= m[k];
     }
     if (e.stats_out) {   // one GroupNorm group per 32-column block; warp-collective
-      float s = 0.f, ss = 0.f;
+      float sm = 0.f, ss = 0.f;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (rok[k]) {
+      for (int k = 0; k < 4; ++k) {
+        const float w = ok[k] ? 1.f : 0.f;
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) { s += v[k][ch]; ss = fmaf(v[k][ch], v[k][ch], ss); }
-        }
-      s = warp_sum(s);
+        for (int ch = 0; ch < 8; ++ch) { sm = fmaf(w, v[k][ch], sm); ss = fmaf(w * v[k][ch], v[k][ch], ss); }
+      }
+      sm = warp_sum(sm);
       ss = warp_sum(ss);
       if (lane == 0) {
-        float* st = e.stats_out + (static_cast<long>(b) * 8 + ((nbase + c * 32) >> 5)) * 2;
-        atomicAdd(st, s);
+        float* st = e.stats_out + (b * 8 + ((nbase + c * 32) >> 5)) * 2;
+        atomicAdd(st, sm);
         atomicAdd(st + 1, ss);
       }
     }
     if (e.x_state) {     // Euler update of the fp32 state; the stored copy below is x * mask
+      const int ld = e.x_ld;
+      const float dt = e.dt;
 #pragma unroll
       for (int k = 0; k < 4; ++k)
-        if (rok[k] && cv) {
+        if (ok[k]) {
           float x[8];
-          const long at = grow[k] * e.x_ld + n0;
+          const long at = static_cast<long>(grow[k]) * ld + n0;
           load8<T>(e.x_state, at, 1, x);
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) x[ch] = fmaf(e.dt, v[k][ch], x[ch]);
+          for (int ch = 0; ch < 8; ++ch) x[ch] = fmaf(dt, v[k][ch], x[ch]);
           store8<T>(e.x_state, at, 1, x);
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) v[k][ch] = x[ch] * m[k];
@@ -327,24 +365,26 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
         for (int ch = 0; ch < 8; ++ch) { ln_s[k] += v[k][ch]; ln_ss[k] = fmaf(v[k][ch], v[k][ch], ln_ss[k]); }
     }
     if (e.out0) {
+      const int ld = e.out0_ld, f32 = e.out0_f32;
+      const float sl = e.out0_slope;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (rok[k] && cv) {
-          float o[8];
+      for (int k = 0; k < 4; ++k) {
+        float o[8];
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) o[ch] = e.out0_slope == 1.f ? v[k][ch] : fmaxf(v[k][ch], v[k][ch] * e.out0_slope);
-          store8<T>(e.out0, grow[k] * e.out0_ld + n0, e.out0_f32, o);
-        }
+        for (int ch = 0; ch < 8; ++ch) o[ch] = fmaxf(v[k][ch], v[k][ch] * sl);
+        if (ok[k]) store8<T>(e.out0, static_cast<long>(grow[k]) * ld + n0, f32, o);
+      }
     }
     if (e.out1) {
+      const int ld = e.out1_ld;
+      const float sl = e.out1_slope;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (rok[k] && cv) {
-          float o[8];
+      for (int k = 0; k < 4; ++k) {
+        float o[8];
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) o[ch] = e.out1_slope == 1.f ? v[k][ch] : fmaxf(v[k][ch], v[k][ch] * e.out1_slope);
-          store8<T>(e.out1, grow[k] * e.out1_ld + n0, 0, o);
-        }
+        for (int ch = 0; ch < 8; ++ch) o[ch] = fmaxf(v[k][ch], v[k][ch] * sl);
+        if (ok[k]) store8<T>(e.out1, static_cast<long>(grow[k]) * ld + n0, 0, o);
+      }
     }
   }
 
@@ -377,7 +417,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
       for (int k = 0; k < 4; ++k) {
         const int t = tw0 + 8 * k;
         if (t < T_out) {
-          const long row = row_base + static_cast<long>(t) * e.o_mul;
+          const long row = row_base + t * o_mul;
           float x[8];
           load8<T>(e.out0, row * e.out0_ld + n0, 0, x);
 #pragma unroll

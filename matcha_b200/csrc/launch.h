@@ -19,6 +19,7 @@ struct ConvLaunch {
   ConvGeom2 g2;
   CUtensorMap tmA8[2];  // same views, 8-row boxes (halo rows beyond the first 128)
   int smem_bytes, grid;
+  int pdl;              // launch with programmatic stream serialization (prologue overlaps the previous kernel's tail)
 };
 
 template <typename T> cudaError_t launch_conv_umma(const ConvLaunch& L, cudaStream_t st);

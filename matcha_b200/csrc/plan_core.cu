@@ -36,6 +36,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   MB_CUDA(cudaGetDevice(&dev));
   MB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
   MB_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  if (const char* v = std::getenv("MB200_PDL")) use_pdl = std::atoi(v);
   if (const char* v = std::getenv("MB200_KERNEL")) kernel_version = std::atoi(v);
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
@@ -344,6 +345,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8);
     L.tmA8[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 8) : L.tmA8[0];
     L.grid = std::min(g2.total_tiles, num_sms);
+    L.pdl = use_pdl;
   }
   const int dtype = cfg.dtype;
   const bool tc = tensor_core();

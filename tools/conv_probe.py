@@ -18,18 +18,23 @@ CASES = {  # name: (B, C, T, K, dil)
     "s4k11": (2, 32, 462848, 11, 1),
     "s4k3": (2, 32, 462848, 3, 1),
     "s1k11": (16, 256, 3616, 11, 1),
+    "e_c3": (64, 256, 452, 3, 1),          # estimator Block1D conv at full resolution
+    "e_ff1": (64, 256, 452, 1, 1, 1024),   # feed-forward up projection
+    "e_ff2": (64, 1024, 452, 1, 1, 256),
+    "e_c3_mid": (64, 256, 113, 3, 1),
 }
 
 
 def one(name):
     import torch
     from matcha_b200._lib import Plan
-    b, c, t, k, dil = CASES[name]
+    b, c, t, k, dil = CASES[name][:5]
+    cout = CASES[name][5] if len(CASES[name]) > 5 else c
     plan = Plan("fp16", 160, use_graph=False)
     g = torch.Generator().manual_seed(0)
     x = torch.randn(b, c, t, generator=g)
-    w = torch.randn(c, c, k, generator=g) / (c * k) ** 0.5
-    bias = torch.randn(c, generator=g)
+    w = torch.randn(cout, c, k, generator=g) / (c * k) ** 0.5
+    bias = torch.randn(cout, generator=g)
     os.environ["MB200_PROBE"] = os.environ.get("MB200_PROBE", "20")
     only = os.environ.get("CONV_PROBE_ONLY")   # "epi,dbg": run a single configuration (for ncu)
     for epi, dbg in [tuple(only.split(","))] if only else [("0", "0"), ("2", "0"), ("2", "1"), ("2", "2"), ("2", "4"), ("2", "8"), ("2", "12"), ("2", "3"), ("2", "7"), ("2", "15")]:
