@@ -155,8 +155,17 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
       ok[k] = (t < T_out) && cv;
       grow[k] = row_base + t * o_mul;
     }
+    // per-channel parameters: requested here so that they are in flight while the accumulators are fetched
     float bv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (e.bias) ldg8f(e.bias + n0, bv);   // in flight while the accumulators are fetched
+    float pa[8], pb[8];   // GroupNorm gamma/beta or SnakeBeta a / 1/b (never both on one layer)
+    if (e.bias) ldg8f(e.bias + n0, bv);
+    float gsum = 0.f, gsq = 0.f;   // GroupNorm partial sums of this item's 32-channel group
+    if (e.gn_raw) {
+      ldg8f(e.gn_gamma + n0, pa); ldg8f(e.gn_beta + n0, pb);
+      const float* st = e.gn_stats + (b * 8 + (n0 >> 5)) * 2;
+      gsum = st[0]; gsq = st[1];
+    }
+    else if (e.snake_a) { ldg8f(e.snake_a + n0, pa); ldg8f(e.snake_invb + n0, pb); }
 
     // ---- accumulators: TMEM -> registers (row per lane) -> staging -> coalesced layout
     float v[4][8];
@@ -257,20 +266,16 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
       for (int k = 0; k < 4; ++k) if (ok[k]) m[k] = __ldg(e.mask + grow[k]);
     }
     if (e.gn_raw) {
-      const float* st = e.gn_stats + (b * 8 + (n0 >> 5)) * 2;
-      const float mean = st[0] * e.gn_inv_count;
-      const float rstd = rsqrtf(fmaxf(st[1] * e.gn_inv_count - mean * mean, 0.f) + 1e-5f);
-      float ga[8], be[8];
-      ldg8f(e.gn_gamma + n0, ga);
-      ldg8f(e.gn_beta + n0, be);
+      const float mean = gsum * e.gn_inv_count;
+      const float rstd = rsqrtf(fmaxf(gsq * e.gn_inv_count - mean * mean, 0.f) + 1e-5f);
 #pragma unroll
-      for (int ch = 0; ch < 8; ++ch) { ga[ch] *= rstd; be[ch] -= mean * ga[ch]; }
+      for (int ch = 0; ch < 8; ++ch) { pa[ch] *= rstd; pb[ch] -= mean * pa[ch]; }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         float r[8];
         unpack8<T>(cur[k], r);
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch) v[k][ch] += mish_fast(fmaf(r[ch], ga[ch], be[ch])) * m[k];
+        for (int ch = 0; ch < 8; ++ch) v[k][ch] += mish_fast(fmaf(r[ch], pa[ch], pb[ch])) * m[k];
       }
     }
     if (e.resid) {
@@ -309,15 +314,12 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
         for (int ch = 0; ch < 8; ++ch) v[k][ch] *= sc;
     }
     if (e.snake_a) {
-      float sa[8], sb[8];
-      ldg8f(e.snake_a + n0, sa);
-      ldg8f(e.snake_invb + n0, sb);
 #pragma unroll
       for (int k = 0; k < 4; ++k)
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) {
-          const float sn = __sinf(v[k][ch] * sa[ch]);
-          v[k][ch] = fmaf(sb[ch] * sn, sn, v[k][ch]);
+          const float sn = __sinf(v[k][ch] * pa[ch]);
+          v[k][ch] = fmaf(pb[ch] * sn, sn, v[k][ch]);
         }
     }
     if (e.mask_out) {
@@ -367,12 +369,18 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
     if (e.out0) {
       const int ld = e.out0_ld, f32 = e.out0_f32;
       const float sl = e.out0_slope;
+      if (sl == 1.f) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        float o[8];
+        for (int k = 0; k < 4; ++k)
+          if (ok[k]) store8<T>(e.out0, static_cast<long>(grow[k]) * ld + n0, f32, v[k]);
+      } else {
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch) o[ch] = fmaxf(v[k][ch], v[k][ch] * sl);
-        if (ok[k]) store8<T>(e.out0, static_cast<long>(grow[k]) * ld + n0, f32, o);
+        for (int k = 0; k < 4; ++k) {
+          float o[8];
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) o[ch] = fmaxf(v[k][ch], v[k][ch] * sl);
+          if (ok[k]) store8<T>(e.out0, static_cast<long>(grow[k]) * ld + n0, f32, o);
+        }
       }
     }
     if (e.out1) {
