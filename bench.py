@@ -159,6 +159,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback for the product path")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL logs to stdout by default; stdout carries the JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
