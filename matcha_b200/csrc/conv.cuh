@@ -50,6 +50,7 @@ struct ConvGeom2 {
   int g_wk[kMaxGroups][kMaxTaps];                  // K coordinate of the tap's weight slice for chunk 0
   int w_resident;                                  // all weight tiles stay in shared memory for the CTA's lifetime
   int a_stages, w_stages;                          // ring depths (w_stages unused when resident)
+  int eg;                                          // epilogue groups of four warps (2 or 4)
   int wt;                                          // taps per streamed weight stage (1 or 2): longer steps per handshake
   int m_tiles, n_tiles, total_tiles;
   int mb;                                          // 128-row blocks per tile (1, 2 or 4): narrow-N layers amortise per-tile costs

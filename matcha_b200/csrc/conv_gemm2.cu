@@ -32,8 +32,8 @@ namespace mb {
 constexpr int kMaxRing = 8;
 constexpr int kBarBytes = 512;   // mbarriers + TMEM slot
 
-template <int NTILE, int KC, int MB, typename T>
-__global__ void __launch_bounds__(320, 1)
+template <int NTILE, int KC, int MB, int EG, typename T>
+__global__ void __launch_bounds__(64 + 128 * EG, 1)
 conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                        const __grid_constant__ CUtensorMap tmA0x, const __grid_constant__ CUtensorMap tmA1x,
                        const __grid_constant__ CUtensorMap tmW, const __grid_constant__ ConvGeom2 g,
@@ -69,7 +69,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   uint64_t* wres = t_empty + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres + 1);
   uint8_t* stage_base = tail + kBarBytes;                                   // 8 warp-private staging tiles
-  float2* lnx = reinterpret_cast<float2*>(stage_base + 8 * kStageBytes);    // LayerNorm partial-sum exchange
+  float2* lnx = reinterpret_cast<float2*>(stage_base + 4 * EG * kStageBytes);    // LayerNorm partial-sum exchange
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int np = g.n_tiles * g.n_phases;
@@ -77,7 +77,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmA0x); tma_prefetch_desc(&tmW);
     for (int s = 0; s < kMaxRing; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    for (int s = 0; s < 4; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 8); }
+    for (int s = 0; s < 4; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4 * EG); }
     mbar_init(wres, 1);
     fence_barrier_init();
   }
@@ -251,11 +251,11 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       if (MB_DBG(8)) {
         MB_WAIT(mbar_wait(&t_full[slot], tph));
       } else {
-        epilogue_tile3<NTILE, MB, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * 256, lane,
+        epilogue_tile3<NTILE, MB, EG, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
                                  lane_grp, grp, &t_full[slot], tph, &probe_w);
       }
 #else
-      epilogue_tile3<NTILE, MB, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * 256, lane,
+      epilogue_tile3<NTILE, MB, EG, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
                                lane_grp, grp, &t_full[slot], tph);
 #endif
       tc_fence_before();
@@ -274,9 +274,9 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-template <int NTILE, int KC, int MB, typename T>
+template <int NTILE, int KC, int MB, int EG, typename T>
 static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
-  auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, T>;
+  auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, EG, T>;
   static int configured = 0;
   if (configured < L.smem_bytes) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -286,7 +286,7 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
   const bool two = L.g.n_src > 1;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(L.grid);
-  cfg.blockDim = dim3(320);
+  cfg.blockDim = dim3(64 + 128 * EG);
   cfg.dynamicSmemBytes = L.smem_bytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -297,18 +297,23 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
   return cudaLaunchKernelEx(&cfg, kern, L.tmA[0], L.tmA[two ? 1 : 0], L.tmA8[0], L.tmA8[two ? 1 : 0], L.tmW, L.g2, L.e);
 }
 
+template <int NTILE, int KC, int MB, typename T>
+static cudaError_t launch_umma2_eg(const ConvLaunch& L, cudaStream_t st) {
+  return L.g2.eg == 4 ? launch_umma2_inst<NTILE, KC, MB, 4, T>(L, st) : launch_umma2_inst<NTILE, KC, MB, 2, T>(L, st);
+}
+
 template <typename T>
 cudaError_t launch_conv_umma2(const ConvLaunch& L, cudaStream_t st) {
   const int nt = L.ntile, kc = L.kc, mb = L.g2.mb;
-  if (kc == 64 && nt == 256 && mb == 1) return launch_umma2_inst<256, 64, 1, T>(L, st);
-  if (kc == 64 && nt == 128 && mb == 1) return launch_umma2_inst<128, 64, 1, T>(L, st);
-  if (kc == 64 && nt == 128 && mb == 2) return launch_umma2_inst<128, 64, 2, T>(L, st);
-  if (kc == 64 && nt == 64 && mb == 1) return launch_umma2_inst<64, 64, 1, T>(L, st);
-  if (kc == 64 && nt == 64 && mb == 2) return launch_umma2_inst<64, 64, 2, T>(L, st);
-  if (kc == 64 && nt == 32 && mb == 1) return launch_umma2_inst<32, 64, 1, T>(L, st);
-  if (kc == 64 && nt == 32 && mb == 4) return launch_umma2_inst<32, 64, 4, T>(L, st);
-  if (kc == 32 && nt == 32 && mb == 1) return launch_umma2_inst<32, 32, 1, T>(L, st);
-  if (kc == 32 && nt == 32 && mb == 4) return launch_umma2_inst<32, 32, 4, T>(L, st);
+  if (kc == 64 && nt == 256 && mb == 1) return launch_umma2_eg<256, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 128 && mb == 1) return launch_umma2_eg<128, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 128 && mb == 2) return launch_umma2_eg<128, 64, 2, T>(L, st);
+  if (kc == 64 && nt == 64 && mb == 1) return launch_umma2_eg<64, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 64 && mb == 2) return launch_umma2_eg<64, 64, 2, T>(L, st);
+  if (kc == 64 && nt == 32 && mb == 1) return launch_umma2_eg<32, 64, 1, T>(L, st);
+  if (kc == 64 && nt == 32 && mb == 4) return launch_umma2_eg<32, 64, 4, T>(L, st);
+  if (kc == 32 && nt == 32 && mb == 1) return launch_umma2_eg<32, 32, 1, T>(L, st);
+  if (kc == 32 && nt == 32 && mb == 4) return launch_umma2_eg<32, 32, 4, T>(L, st);
   return cudaErrorInvalidConfiguration;
 }
 template cudaError_t launch_conv_umma2<__nv_bfloat16>(const ConvLaunch&, cudaStream_t);

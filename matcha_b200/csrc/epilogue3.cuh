@@ -19,7 +19,7 @@ namespace mb {
 
 constexpr int kStagePitch = 144;                 // bytes per staged row: 32 fp32 + 16 B pad
 constexpr int kStageBytes = 32 * kStagePitch;    // per epilogue warp
-constexpr int kLnXFloat2 = 2 * 2 * 128;          // [tile parity][group][row] partial LayerNorm sums
+constexpr int kLnXBytes = 2 * 4 * 128 * 8;        // [tile parity][group <= 4][row] partial LayerNorm sums (float2)
 
 __device__ __forceinline__ float mish_fast(float x) {
   if (x > 20.f) return x;
@@ -88,7 +88,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 // The profile of this function is flat and latency-bound (two epilogue warps per scheduler), so the code is organised
 // to keep the instruction count per 32x32 item low: options are tested once per item (feature-major, row-minor loops),
 // row offsets are 32-bit element indices computed once, and memory operations are predicated rather than branched.
-template <int NTILE, int MB, typename T>
+template <int NTILE, int MB, int EG, typename T>
 __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, const int t0, const int T_out,
                                                const int phase, const int nbase, const uint32_t tmem_tile,
                                                uint8_t* stg, float2* lnx, const int lane, const int lane_grp,
@@ -137,12 +137,12 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
   float ln_s[4] = {0.f, 0.f, 0.f, 0.f}, ln_ss[4] = {0.f, 0.f, 0.f, 0.f};
 
 #pragma unroll 1
-  for (; item < ITEMS; item += 2) {
+  for (; item < ITEMS; item += EG) {
     const int i = item / NP, c = item % NP;
     uint4 cur[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) cur[k] = nxt[k];
-    if (inA && item + 2 < ITEMS) issueA(item + 2, nxt);
+    if (inA && item + EG < ITEMS) issueA(item + EG, nxt);
     if (t0 + 128 * i + lane_grp * 32 >= T_out) continue;   // warp-uniform: no row of this block exists
 
     const int n0 = nbase + c * 32 + 8 * p;
@@ -407,16 +407,21 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
       ln_ss[k] += __shfl_xor_sync(0xffffffffu, ln_ss[k], 2);
       if (p == 0) lnx[grp * 128 + lane_grp * 32 + rq + 8 * k] = make_float2(ln_s[k], ln_ss[k]);
     }
-    named_bar_sync(1 + lane_grp, 64);
+    named_bar_sync(1 + lane_grp, 32 * EG);
     float mean[4], rstd[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float2 o = lnx[(grp ^ 1) * 128 + lane_grp * 32 + rq + 8 * k];
-      mean[k] = (ln_s[k] + o.x) * (1.f / 256.f);
-      rstd[k] = rsqrtf(fmaxf((ln_ss[k] + o.y) * (1.f / 256.f) - mean[k] * mean[k], 0.f) + 1e-5f);
+      float sm = 0.f, sq = 0.f;   // same summation order in every group: bit-identical statistics
+#pragma unroll
+      for (int gi = 0; gi < EG; ++gi) {
+        const float2 o = lnx[gi * 128 + lane_grp * 32 + rq + 8 * k];
+        sm += o.x; sq += o.y;
+      }
+      mean[k] = sm * (1.f / 256.f);
+      rstd[k] = rsqrtf(fmaxf(sq * (1.f / 256.f) - mean[k] * mean[k], 0.f) + 1e-5f);
     }
 #pragma unroll 1
-    for (int c = grp; c < NP; c += 2) {
+    for (int c = grp; c < NP; c += EG) {
       const int n0 = c * 32 + 8 * p;
       float ga[8], be[8];
       ldg8f(e.ln_g + n0, ga);

@@ -135,6 +135,7 @@ class Plan {
   int kernel_version = 2;   // 2 = persistent conv_gemm2.cu (default), 1 = first non-persistent kernel (MB200_KERNEL=1)
   long long* probe_out = nullptr;   // developer probe (MB200_DBG): cycle counters of the last conv_op built
   int num_sms = 148;
+  int tile_policy = 0;      // 1: 256-row x 128-channel tiles for wide layers (halves the weight stream; measured neutral at cfg2); 0: 128 x 256 (MB200_TILE_POLICY)
   int use_pdl = 0;          // programmatic dependent launch for the persistent conv kernel (MB200_PDL=1 enables; measured neutral inside CUDA graphs)
   bool profiling = false;
   double prof[kProfRegions][kProfKinds][3] = {};   // [region][kind] = {launches, milliseconds, flops}

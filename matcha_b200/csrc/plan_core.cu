@@ -37,6 +37,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   MB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
   MB_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
   if (const char* v = std::getenv("MB200_PDL")) use_pdl = std::atoi(v);
+  if (const char* v = std::getenv("MB200_TILE_POLICY")) tile_policy = std::atoi(v);
   if (const char* v = std::getenv("MB200_KERNEL")) kernel_version = std::atoi(v);
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
@@ -239,12 +240,17 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
   e.o_mul = W.o_mul; e.o_phase_step = 1; e.T_o = T_out * W.o_mul; e.n_valid = W.n_valid; e.bias = W.bias;
   L.e = e;
   L.a[0] = s0.p; L.a[1] = s1 ? s1->p : s0.p;
-  L.w = W.w; L.ntile = W.ntile; L.kc = W.kc;
+  // Tile shape.  Weights are streamed from L2 once per tile, so a 128-row x 256-channel tile re-reads them twice as
+  // often per output element as a 256-row x 128-channel one; at batch 64 that stream is what saturates L2 in the
+  // estimator and in HiFi-GAN stage 1.  Only the fused-LayerNorm layers need the whole 256-channel row in one tile.
+  int ntile = W.ntile;
+  if (ntile == 256 && !e.ln_out && T_out > 128 && tile_policy == 1) ntile = 128;
+  L.w = W.w; L.ntile = ntile; L.kc = W.kc;
   if (e.ln_out && (W.N != 256 || !tensor_core())) throw Error("conv_op: fused LayerNorm needs the tensor-core kernel and N == 256");
   if (tensor_core()) {
     L.tmA[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc);
     L.tmA[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc) : L.tmA[0];
-    L.tmW = W.tm;
+    L.tmW = ntile == W.ntile ? W.tm : tmap_w(W.w, W.K_total, W.n_phases * W.N, W.kc, ntile);
     // ---- persistent kernel geometry: A-load groups = (source, channel base); taps of a group share one halo tile
     ConvGeom2& g2 = L.g2;
     g2.B = B; g2.T_in = s0.rows; g2.T_out = T_out; g2.N = W.N; g2.n_phases = W.n_phases; g2.K_total = W.K_total;
@@ -278,31 +284,42 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     g2.n_groups = ng;
     // narrow-N layers (HiFi-GAN stages 2-4) process 2-4 blocks of 128 rows per tile to amortise per-tile latencies
     g2.mb = 1;
-    if (T_out >= 2048) g2.mb = W.ntile == 32 ? 4 : (W.ntile <= 128 ? 2 : 1);
+    if (T_out >= 2048) g2.mb = ntile == 32 ? 4 : (ntile <= 128 ? 2 : 1);
+    else if (ntile == 128 && T_out > 128 && tile_policy == 1) g2.mb = 2;
     g2.m_tiles = (T_out + 128 * g2.mb - 1) / (128 * g2.mb);
-    g2.n_tiles = W.N / W.ntile;
+    g2.n_tiles = W.N / ntile;
     g2.total_tiles = B * g2.m_tiles * g2.n_tiles * W.n_phases;
-    // shared memory: A ring | weights | 1 KB alignment slack, 512 B barriers, 8 x 4.5 KB epilogue staging, 4 KB LayerNorm exchange
-    const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = W.ntile * W.kc * 2;
-    const int tail_bytes = 1024 + 512 + 8 * 4608 + 4096, budget = 227 * 1024 - tail_bytes;
+    // shared memory: A ring | weights | 1 KB alignment slack, 512 B barriers, 4.5 KB epilogue staging per epilogue warp,
+    // LayerNorm exchange.  Sixteen epilogue warps (eg = 4) when the rings still get their depth: the epilogue is
+    // latency-bound, so more warps in flight is what speeds it up; layers with large rings keep eight.
+    const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = ntile * W.kc * 2;
     const long w_total = static_cast<long>(W.n_phases) * W.N * W.K_total * 2;
     g2.a_bytes = a_bytes;
-    if (w_total <= 100 * 1024) {
-      g2.w_resident = 1;
-      g2.wt = 1;
-      g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
-      g2.w_stages = 0;
-      L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + tail_bytes;
-    } else {
+    int max_taps = 1;
+    for (int q = 0; q < ng; ++q) max_taps = std::max(max_taps, g2.g_ntaps[q]);
+    auto layout = [&](int eg) -> bool {   // fills g2 ring fields + L.smem_bytes; false = rings too shallow for this eg
+      const int tail_bytes = 1024 + 512 + 4 * eg * 4608 + 8192, budget = 227 * 1024 - tail_bytes;
+      g2.eg = eg;
+      if (w_total <= 100 * 1024 && (budget - w_total) / a_bytes >= 2) {
+        g2.w_resident = 1;
+        g2.wt = 1;
+        g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
+        g2.w_stages = 0;
+        L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + tail_bytes;
+        return true;
+      }
       g2.w_resident = 0;
-      g2.a_stages = (W.ntile == 256 || g2.mb > 1) ? 2 : 3;
+      g2.a_stages = (ntile == 256 || g2.mb > 1) ? 2 : 3;
       // narrow tiles pair two taps per ring stage: half as many producer/issuer handshakes per tensor-pipe cycle
-      int max_taps = 1;
-      for (int q = 0; q < ng; ++q) max_taps = std::max(max_taps, g2.g_ntaps[q]);
       g2.wt = (w_tile <= 16 * 1024 && max_taps >= 2) ? 2 : 1;
       g2.w_stages = std::min(8, (budget - g2.a_stages * a_bytes) / (g2.wt * w_tile));
-      if (g2.w_stages < 2) throw Error("conv_op: weight ring does not fit");
       L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * g2.wt * w_tile + tail_bytes;
+      return g2.w_stages >= 3;
+    };
+    int want_eg = 2;   // sixteen epilogue warps measured slower (register cap 96, same L2-bound stores): opt-in only
+    if (const char* v = std::getenv("MB200_EG")) want_eg = std::atoi(v) == 4 ? 4 : 2;
+    if (want_eg == 2 || !layout(4)) {
+      if (!layout(2) && g2.w_stages < 2) throw Error("conv_op: weight ring does not fit");
     }
     if (e.ln_out && g2.mb != 1) throw Error("conv_op: fused LayerNorm needs single-block tiles");
     if (e.ln_out && (!e.out0 || e.out0_f32)) throw Error("conv_op: fused LayerNorm re-reads out0 in the operand dtype");
