@@ -244,8 +244,16 @@ def run_ours(args):
             if k == 0:
                 g_ms, g_fl, g_n = g_ms + pms, g_fl + fl, g_n + n
         achieved = g_fl / g_ms / 1e9 if g_ms else 0.0
-        roofline = {"bound": "tensor", "kernel": "conv_gemm_umma_kernel (all instantiations)", "achieved": achieved,
-                    "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": None,
+        traffic, traffic_src = None, None
+        try:   # DRAM bytes per launch of the same kernel family from the committed ncu pass (bench.py cannot run under ncu)
+            with open(os.path.join(ROOT, "profiles", "r01_dram_traffic.json")) as f:
+                tj = json.load(f)
+            traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+        except (OSError, KeyError, ValueError):
+            pass
+        roofline = {"bound": "tensor", "kernel": "conv_gemm_umma2_kernel (all instantiations)", "achieved": achieved,
+                    "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": traffic,
+                    "traffic_unit": "bytes/launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_src,
                     "peak_source": peaks["source"], "launches_per_step": g_n, "avg_launch_us": g_ms * 1e3 / max(g_n, 1),
                     "share_of_step_time": g_ms / tot_ms if tot_ms else None,
                     "flops_per_step": g_fl}
