@@ -48,7 +48,7 @@ void Plan::test_conv1d(const float* x, const float* w, const float* bias, int B,
     MB_CUDA(cudaMemcpy(xa, up, padded.size() * es, cudaMemcpyDeviceToDevice));
   }
   EpiParams e{};
-  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f;
+  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f; e.resid_inv = 1.f;
   e.out0 = y_ntc; e.out0_ld = W.N; e.out0_f32 = 1;
   if (const char* v = std::getenv("MB200_PROBE_EPI")) {   // developer probe: HiFi-GAN ResBlock c2-style epilogue
     if (std::atoi(v) && Cin == Cout && cpad == Cin && !transposed && stride == 1 && dtype != MB200_F32) {

@@ -77,6 +77,8 @@ struct EpiParams {
   const void* gn_raw;  int gn_ld;  const float* gn_stats;  const float* gn_gamma;  const float* gn_beta;  float gn_inv_count;
   // v += resid (+ resid2)
   const void* resid;   int resid_ld;   int resid_f32;
+  float resid_inv;         // != 1: the stored residual is LeakyReLU(x, 1/resid_inv); x = min(r, r * resid_inv) is what is added
+                           // (HiFi-GAN keeps only lrelu(x): one store per conv instead of two; tcgen05 path only)
   const void* resid2;  int resid2_ld;  int resid2_f32;
   float scale;             // v *= scale (HiFi-GAN xs / num_kernels: hifigan/models.py:192)
   const float* snake_a;    // SnakeBeta exp(alpha), 1/(exp(beta)+1e-9) (transformer.py:70-78); null = off

@@ -189,10 +189,25 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
     if (fast) {
       // ---- packed-half path: bias + residual(s) + scale + LeakyReLU copies, two channels per instruction
       if constexpr (std::is_same<T, __half>::value) {
+        const bool inv_resid = e.resid && e.resid_inv != 1.f;
+        if (inv_resid) {   // the stored stream is lrelu(x): undo it in fp32 (exact inverse of the stored slope) and add
+          const __half* rp = reinterpret_cast<const __half*>(e.resid);
+          const int ld = e.resid_ld;
+          const float inv = e.resid_inv;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            uint4 ru = cur[k];
+            if (!resid_is_A) { ru = make_uint4(0, 0, 0, 0); if (ok[k]) ru = *reinterpret_cast<const uint4*>(rp + static_cast<size_t>(grow[k]) * ld + n0); }
+            float r[8];
+            unpack8<__half>(ru, r);
+#pragma unroll
+            for (int ch = 0; ch < 8; ++ch) v[k][ch] += fminf(r[ch], r[ch] * inv);
+          }
+        }
         uint4 hu[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) hu[k] = pack8<__half>(v[k]);
-        if (e.resid) {
+        if (e.resid && !inv_resid) {
           const __half* rp = reinterpret_cast<const __half*>(e.resid);
           const int ld = e.resid_ld;
 #pragma unroll
@@ -280,6 +295,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
     }
     if (e.resid) {
       const int ld = e.resid_ld, f32 = e.resid_f32;
+      const float inv = e.resid_inv;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         float r[8];
@@ -289,6 +305,10 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) r[ch] = 0.f;
           if (ok[k]) load8<T>(e.resid, static_cast<long>(grow[k]) * ld + n0, f32, r);
+        }
+        if (inv != 1.f) {
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) r[ch] = fminf(r[ch], r[ch] * inv);
         }
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) v[k][ch] += r[ch];

@@ -26,7 +26,7 @@ void expect_shape(const StateDict& sd, const std::string& k, std::vector<long lo
 }
 EpiParams epi() {
   EpiParams e{};
-  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f; e.o_mul = 1;
+  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f; e.resid_inv = 1.f; e.o_mul = 1;
   return e;
 }
 }  // namespace

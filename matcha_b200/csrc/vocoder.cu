@@ -1,6 +1,7 @@
 // HiFi-GAN v1 generator (matcha/hifigan/models.py:149-197) as a launch program: every Conv1d / ConvTranspose1d is
 // a conv-GEMM launch; LeakyReLU, residual adds, the 3-branch mean and the stage hand-over live in the epilogues.
 #include <cmath>
+#include <cuda_fp16.h>
 
 #include "plan.h"
 
@@ -39,7 +40,7 @@ HostTensor effective_weight(const StateDict& sd, const std::string& name, std::v
 }
 EpiParams epi() {
   EpiParams e{};
-  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f; e.o_mul = 1;
+  e.scale = 1.f; e.out0_slope = 1.f; e.out1_slope = 1.f; e.resid_inv = 1.f; e.o_mul = 1;
   return e;
 }
 }  // namespace
@@ -85,13 +86,22 @@ void Plan::vocoder_buffers(int B, int L) {
   const size_t es = esize(cfg.dtype);
   const size_t bl = static_cast<size_t>(B) * L;
   ensure(ws_voc_[V_MEL], bl * 128 * es);
-  for (int b : {V_A, V_X, V_XL, V_R, V_RL, V_C1, V_SUM}) ensure(ws_voc_[b], bl * 8192 * es);
+  const bool single = tensor_core() && kernel_version >= 2 && cfg.dtype != MB200_F32;   // see build_vocoder
+  for (int b : {V_A, V_X, V_XL, V_R, V_RL, V_C1, V_SUM})
+    if (!(single && (b == V_X || b == V_R))) ensure(ws_voc_[b], bl * 8192 * es);
 }
 
 // Everything between the packed mel and the conv_post input; conv_post itself writes to the caller's buffer and is
 // launched outside the cached program.
 void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
   const int f32 = cfg.dtype == MB200_F32;
+  // Tensor-core path: a ResBlock input is kept ONLY as lrelu(x) (what the convs read); the residual read inverts it
+  // (x = min(r, r / slope), slope = the f16/bf16-rounded 0.1 the store used), so every conv writes one stream instead
+  // of two.  The fp32 SIMT path keeps both x and lrelu(x).
+  const bool single = tensor_core() && kernel_version >= 2 && !f32;
+  float slope_stored = 0.1f;
+  if (cfg.dtype == MB200_F16) slope_stored = __half2float(__float2half_rn(0.1f));
+  const float inv_slope = 1.f / slope_stored;
   auto buf = [&](int i) { return ws_voc_[i].p; };
   int region = 1;
   auto add = [&](Launch l) { l.region = region; prog.ops.push_back(std::move(l)); prog.kernels++; };
@@ -107,8 +117,12 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
     region = i + 1;
     {  // ups[i]: x and leaky_relu(x) for the three ResBlocks (models.py:185, :92)
       EpiParams e = epi();
-      e.out0 = buf(V_X); e.out0_ld = C; e.out0_f32 = f32;
-      e.out1 = buf(V_XL); e.out1_ld = C; e.out1_slope = 0.1f;
+      if (single) {
+        e.out0 = buf(V_XL); e.out0_ld = C; e.out0_slope = 0.1f;
+      } else {
+        e.out0 = buf(V_X); e.out0_ld = C; e.out0_f32 = f32;
+        e.out1 = buf(V_XL); e.out1_ld = C; e.out1_slope = 0.1f;
+      }
       add(conv_op(G.ups[i], Src{buf(V_A), ch, ch, len}, nullptr, B, len, e));
     }
     len *= kRates[i];
@@ -123,8 +137,15 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
           add(conv_op(W1, Src{m == 0 ? buf(V_XL) : buf(V_RL), C, C, len}, nullptr, B, len, e));
         }
         EpiParams e = epi();  // r = c2(xt) + r   (models.py:95-96)
-        e.resid = m == 0 ? buf(V_X) : buf(V_R); e.resid_ld = C; e.resid_f32 = f32;
-        if (m < 2) {
+        if (single) {
+          e.resid = m == 0 ? buf(V_XL) : buf(V_RL); e.resid_ld = C; e.resid_inv = inv_slope;
+        } else {
+          e.resid = m == 0 ? buf(V_X) : buf(V_R); e.resid_ld = C; e.resid_f32 = f32;
+        }
+        if (m < 2 && single) {
+          // in place: every thread reads exactly the residual elements it overwrites, and the conv input is V_C1
+          e.out0 = buf(V_RL); e.out0_ld = C; e.out0_slope = 0.1f;
+        } else if (m < 2) {
           e.out0 = buf(V_R); e.out0_ld = C; e.out0_f32 = f32;
           e.out1 = buf(V_RL); e.out1_ld = C; e.out1_slope = 0.1f;
         } else if (j == 0) {
