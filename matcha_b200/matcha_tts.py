@@ -1,0 +1,273 @@
+"""`MatchaTTS` drop-in for synthesis (SURVEY.md §8(b) boundary #1; reference matcha/models/matcha_tts.py:24-148).
+
+What runs where:
+  * the hot path -- `self.decoder(mu_y, y_mask, n_timesteps, temperature, spks)` (matcha_tts.py:135) -- is the CUDA path of
+    this package (`matcha_b200.cfm.CFM` -> libmatcha_b200.so);
+  * the upstream of the path (text encoder, duration predictor, length regulation) is host-side PyTorch written for
+    this package: it is SURVEY §8(f) rows 2-3 ("next"), not yet CUDA kernels.  It keeps the reference's parameter names
+    (`encoder.emb`, `encoder.prenet.*`, `encoder.encoder.attn_layers.N.conv_q ...`, `encoder.proj_m`, `encoder.proj_w.*`,
+    `spk_emb`, `decoder.estimator.*`) so `load_state_dict(strict=True)` of a reference checkpoint's `state_dict` works;
+  * length regulation does not form the dense (B, Lx, T) alignment matmul (matcha_tts.py:129-131): `mu_y` is a gather
+    of `mu_x` by the token index of each frame, which is what the 0/1 alignment computes; `attn` is still returned for
+    API compatibility.
+
+Training (`forward`, MAS, losses) is out of scope for this round.
+"""
+from __future__ import annotations
+
+import datetime as dt
+import math
+from types import SimpleNamespace
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .cfm import CFM
+
+
+def _get(cfg, name, default=None):
+    """Config access for dicts, namespaces and OmegaConf-like objects."""
+    if isinstance(cfg, dict):
+        return cfg.get(name, default)
+    return getattr(cfg, name, default)
+
+
+def sequence_mask(length, max_length=None):
+    """(B,) lengths -> (B, max_length) bool prefix masks (reference utils/model.py:7-11)."""
+    if max_length is None:
+        max_length = int(length.max())
+    return torch.arange(max_length, dtype=length.dtype, device=length.device)[None, :] < length[:, None]
+
+
+def fix_len_compatibility(length, num_downsamplings_in_unet=2):
+    """Round up to a multiple of 2**n (reference utils/model.py:14-20)."""
+    f = 2 ** num_downsamplings_in_unet
+    return int(math.ceil(float(length) / f) * f)
+
+
+def generate_path(duration, mask):
+    """0/1 monotonic alignment (B, Lx, T) from integer-valued durations (reference utils/model.py:29-41)."""
+    b, t_x, t_y = mask.shape
+    cum = torch.cumsum(duration, 1)
+    path = sequence_mask(cum.reshape(b * t_x), t_y).to(mask.dtype).view(b, t_x, t_y)
+    path = path - F.pad(path, (0, 0, 1, 0))[:, :-1]
+    return path * mask
+
+
+class ChannelNorm(nn.Module):
+    """LayerNorm over the channel axis of (B, C, T), eps 1e-4, parameters `gamma`/`beta` (text_encoder.py:16-33)."""
+
+    def __init__(self, channels, eps=1e-4):
+        super().__init__()
+        self.eps = eps
+        self.gamma = nn.Parameter(torch.ones(channels))
+        self.beta = nn.Parameter(torch.zeros(channels))
+
+    def forward(self, x):
+        return F.layer_norm(x.transpose(1, 2), (x.shape[1],), self.gamma, self.beta, self.eps).transpose(1, 2)
+
+
+class _Prenet(nn.Module):  # text_encoder.py:36-67
+    def __init__(self, ch, k=5, n_layers=3):
+        super().__init__()
+        self.conv_layers = nn.ModuleList(nn.Conv1d(ch, ch, k, padding=k // 2) for _ in range(n_layers))
+        self.norm_layers = nn.ModuleList(ChannelNorm(ch) for _ in range(n_layers))
+        self.proj = nn.Conv1d(ch, ch, 1)
+        nn.init.zeros_(self.proj.weight)
+        nn.init.zeros_(self.proj.bias)
+
+    def forward(self, x, x_mask):
+        h = x
+        for conv, norm in zip(self.conv_layers, self.norm_layers):
+            h = torch.relu(norm(conv(h * x_mask)))   # dropout is identity at inference
+        return (x + self.proj(h)) * x_mask
+
+
+class _DurationPredictor(nn.Module):  # text_encoder.py:70-93
+    def __init__(self, cin, filt, k):
+        super().__init__()
+        self.conv_1 = nn.Conv1d(cin, filt, k, padding=k // 2)
+        self.norm_1 = ChannelNorm(filt)
+        self.conv_2 = nn.Conv1d(filt, filt, k, padding=k // 2)
+        self.norm_2 = ChannelNorm(filt)
+        self.proj = nn.Conv1d(filt, 1, 1)
+
+    def forward(self, x, x_mask):
+        x = self.norm_1(torch.relu(self.conv_1(x * x_mask)))
+        x = self.norm_2(torch.relu(self.conv_2(x * x_mask)))
+        return self.proj(x * x_mask) * x_mask
+
+
+def _rope(x, d, base=10000.0):
+    """Rotary embedding on the first `d` features of (B, H, T, Dh), positions along T (text_encoder.py:96-166)."""
+    t = x.shape[2]
+    theta = 1.0 / (base ** (torch.arange(0, d, 2, device=x.device).float() / d))
+    ang = torch.arange(t, device=x.device).float()[:, None] * theta[None, :]
+    ang = torch.cat([ang, ang], dim=1)                       # (T, d)
+    cos, sin = ang.cos()[None, None], ang.sin()[None, None]
+    xr, xp = x[..., :d], x[..., d:]
+    half = d // 2
+    rot = torch.cat([-xr[..., half:], xr[..., :half]], dim=-1)
+    return torch.cat([xr * cos + rot * sin, xp], dim=-1)
+
+
+class _SelfAttention(nn.Module):  # text_encoder.py:169-237 (no proximal bias in the shipped configs)
+    def __init__(self, ch, n_heads):
+        super().__init__()
+        assert ch % n_heads == 0
+        self.n_heads, self.k_channels = n_heads, ch // n_heads
+        self.conv_q, self.conv_k, self.conv_v, self.conv_o = (nn.Conv1d(ch, ch, 1) for _ in range(4))
+        for c in (self.conv_q, self.conv_k, self.conv_v):
+            nn.init.xavier_uniform_(c.weight)
+        self.rope_dims = int(self.k_channels * 0.5)
+
+    def forward(self, x, attn_mask):
+        b, c, t = x.shape
+        split = lambda y: y.view(b, self.n_heads, self.k_channels, t).transpose(2, 3)   # (B, H, T, Dh)
+        q, k, v = split(self.conv_q(x)), split(self.conv_k(x)), split(self.conv_v(x))
+        q, k = _rope(q, self.rope_dims), _rope(k, self.rope_dims)
+        scores = torch.matmul(q, k.transpose(-2, -1)) / math.sqrt(self.k_channels)
+        scores = scores.masked_fill(attn_mask == 0, -1e4)    # replaces, does not add (text_encoder.py:222)
+        o = torch.matmul(torch.softmax(scores, dim=-1), v)
+        return self.conv_o(o.transpose(2, 3).reshape(b, c, t))
+
+
+class _FFN(nn.Module):  # text_encoder.py:240-257
+    def __init__(self, ch, filt, k):
+        super().__init__()
+        self.conv_1 = nn.Conv1d(ch, filt, k, padding=k // 2)
+        self.conv_2 = nn.Conv1d(filt, ch, k, padding=k // 2)
+
+    def forward(self, x, x_mask):
+        return self.conv_2(torch.relu(self.conv_1(x * x_mask)) * x_mask) * x_mask
+
+
+class _Encoder(nn.Module):  # text_encoder.py:260-310
+    def __init__(self, ch, filt, n_heads, n_layers, k):
+        super().__init__()
+        self.attn_layers = nn.ModuleList(_SelfAttention(ch, n_heads) for _ in range(n_layers))
+        self.norm_layers_1 = nn.ModuleList(ChannelNorm(ch) for _ in range(n_layers))
+        self.ffn_layers = nn.ModuleList(_FFN(ch, filt, k) for _ in range(n_layers))
+        self.norm_layers_2 = nn.ModuleList(ChannelNorm(ch) for _ in range(n_layers))
+
+    def forward(self, x, x_mask):
+        attn_mask = x_mask.unsqueeze(2) * x_mask.unsqueeze(-1)
+        for attn, n1, ffn, n2 in zip(self.attn_layers, self.norm_layers_1, self.ffn_layers, self.norm_layers_2):
+            x = x * x_mask
+            x = n1(x + attn(x, attn_mask))
+            x = n2(x + ffn(x, x_mask))
+        return x * x_mask
+
+
+class TextEncoder(nn.Module):
+    """Phoneme ids -> (mu_x (B,n_feats,Lx), logw (B,1,Lx), x_mask (B,1,Lx)); reference text_encoder.py:313-410."""
+
+    def __init__(self, encoder_type, encoder_params, duration_predictor_params, n_vocab, n_spks=1, spk_emb_dim=128):
+        super().__init__()
+        p = encoder_params
+        self.n_vocab, self.n_spks, self.spk_emb_dim = n_vocab, n_spks, spk_emb_dim
+        self.n_feats, self.n_channels = _get(p, "n_feats"), _get(p, "n_channels")
+        self.emb = nn.Embedding(n_vocab, self.n_channels)
+        nn.init.normal_(self.emb.weight, 0.0, self.n_channels ** -0.5)
+        self.prenet = _Prenet(self.n_channels) if _get(p, "prenet", True) else None
+        ch = self.n_channels + (spk_emb_dim if n_spks > 1 else 0)
+        self.encoder = _Encoder(ch, _get(p, "filter_channels"), _get(p, "n_heads"), _get(p, "n_layers"),
+                                _get(p, "kernel_size"))
+        self.proj_m = nn.Conv1d(ch, self.n_feats, 1)
+        d = duration_predictor_params
+        self.proj_w = _DurationPredictor(ch, _get(d, "filter_channels_dp"), _get(d, "kernel_size"))
+
+    def forward(self, x, x_lengths, spks=None):
+        h = self.emb(x).transpose(1, 2) * math.sqrt(self.n_channels)
+        x_mask = sequence_mask(x_lengths, h.shape[2]).unsqueeze(1).to(h.dtype)
+        if self.prenet is not None:
+            h = self.prenet(h, x_mask)
+        if self.n_spks > 1:
+            h = torch.cat([h, spks.unsqueeze(-1).expand(-1, -1, h.shape[-1])], dim=1)
+        h = self.encoder(h, x_mask)
+        return self.proj_m(h) * x_mask, self.proj_w(h.detach(), x_mask), x_mask
+
+
+def length_regulate(mu_x, w_ceil, x_mask, y_lengths, t_pad):
+    """mu_y (B, n_feats, t_pad) and attn (B, Lx, t_pad) from per-token frame counts.
+
+    Same result as `attn = generate_path(...)`, `mu_y = attn^T @ mu_x` (matcha_tts.py:126-131) without the dense matmul:
+    frame j of utterance b copies token `searchsorted(cumsum(w), j, right=True)`, and frames at or beyond
+    y_lengths[b] are zero.
+    """
+    b, c, lx = mu_x.shape
+    y_mask = sequence_mask(y_lengths, t_pad).unsqueeze(1).to(x_mask.dtype)           # (B, 1, T)
+    attn_mask = x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)                            # (B, 1, Lx, T)
+    attn = generate_path(w_ceil.squeeze(1), attn_mask.squeeze(1))                     # (B, Lx, T)
+    cum = torch.cumsum(w_ceil.squeeze(1), 1)                                          # (B, Lx)
+    frames = torch.arange(t_pad, device=mu_x.device, dtype=cum.dtype)[None, :].expand(b, -1).contiguous()
+    tok = torch.searchsorted(cum.contiguous(), frames, right=True).clamp_(max=lx - 1)  # (B, T)
+    covered = attn.sum(1) > 0                                                         # frames some token owns
+    mu_y = torch.gather(mu_x, 2, tok[:, None, :].expand(-1, c, -1)) * covered[:, None, :].to(mu_x.dtype)
+    return mu_y, attn, y_mask
+
+
+class MatchaTTS(nn.Module):
+    """Synthesis-side drop-in for the reference `MatchaTTS` (constructor and `synthesise` contract: matcha_tts.py:24-148)."""
+
+    def __init__(self, n_vocab, n_spks, spk_emb_dim, n_feats, encoder, decoder, cfm, data_statistics, out_size=None,
+                 optimizer=None, scheduler=None, prior_loss=True):
+        super().__init__()
+        self.n_vocab, self.n_spks, self.spk_emb_dim, self.n_feats = n_vocab, n_spks, spk_emb_dim, n_feats
+        self.out_size, self.prior_loss = out_size, prior_loss
+        if n_spks > 1:
+            self.spk_emb = nn.Embedding(n_spks, spk_emb_dim)
+        enc_params = _get(encoder, "encoder_params")
+        self.encoder = TextEncoder(_get(encoder, "encoder_type"), enc_params, _get(encoder, "duration_predictor_params"),
+                                   n_vocab, n_spks, spk_emb_dim)
+        nf = _get(enc_params, "n_feats")
+        self.decoder = CFM(in_channels=2 * nf, out_channel=nf, cfm_params=cfm, decoder_params=decoder, n_spks=n_spks,
+                           spk_emb_dim=spk_emb_dim)
+        self.update_data_statistics(data_statistics)
+
+    def update_data_statistics(self, data_statistics):   # baselightningmodule.py:20-28
+        if data_statistics is None:
+            data_statistics = {"mel_mean": 0.0, "mel_std": 1.0}
+        self.register_buffer("mel_mean", torch.tensor(float(_get(data_statistics, "mel_mean"))))
+        self.register_buffer("mel_std", torch.tensor(float(_get(data_statistics, "mel_std"))))
+
+    @torch.inference_mode()
+    def synthesise(self, x, x_lengths, n_timesteps, temperature=1.0, spks=None, length_scale=1.0):
+        t0 = dt.datetime.now()
+        if self.n_spks > 1:
+            spks = self.spk_emb(spks.long())
+        mu_x, logw, x_mask = self.encoder(x, x_lengths, spks)
+        w_ceil = torch.ceil(torch.exp(logw) * x_mask) * length_scale
+        y_lengths = torch.clamp_min(torch.sum(w_ceil, [1, 2]), 1).long()
+        y_max_length = int(y_lengths.max())
+        mu_y, attn, y_mask = length_regulate(mu_x, w_ceil, x_mask, y_lengths, fix_len_compatibility(y_max_length))
+        encoder_outputs = mu_y[:, :, :y_max_length]
+        decoder_outputs = self.decoder(mu_y, y_mask, n_timesteps, temperature, spks)[:, :, :y_max_length]
+        seconds = (dt.datetime.now() - t0).total_seconds()
+        return {
+            "encoder_outputs": encoder_outputs,
+            "decoder_outputs": decoder_outputs,
+            "attn": attn.unsqueeze(1)[:, :, :y_max_length],   # the reference slices the Lx axis here (matcha_tts.py:144)
+            "mel": decoder_outputs * self.mel_std + self.mel_mean,
+            "mel_lengths": y_lengths,
+            "rtf": seconds * 22050 / (decoder_outputs.shape[-1] * 256),
+        }
+
+    def forward(self, *args, **kwargs):
+        raise NotImplementedError("matcha_b200.MatchaTTS covers synthesis; training (MAS, losses, estimator backward) "
+                                  "is not built in this round")
+
+
+def default_config(n_spks=1):
+    """The shipped hyper-parameters (configs/model/matcha.yaml, encoder/default.yaml, decoder/default.yaml, cfm/default.yaml)."""
+    ns = SimpleNamespace
+    enc = ns(encoder_type="RoPE Encoder",
+             encoder_params=ns(n_feats=80, n_channels=192, filter_channels=768, filter_channels_dp=256, n_heads=2,
+                               n_layers=6, kernel_size=3, p_dropout=0.1, spk_emb_dim=64, n_spks=n_spks, prenet=True),
+             duration_predictor_params=ns(filter_channels_dp=256, kernel_size=3, p_dropout=0.1))
+    dec = dict(channels=(256, 256), dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=2,
+               act_fn="snakebeta")
+    cfm = ns(name="CFM", solver="euler", sigma_min=1e-4)
+    return dict(n_vocab=178, n_spks=n_spks, spk_emb_dim=64, n_feats=80, encoder=enc, decoder=dec, cfm=cfm,
+                data_statistics=dict(mel_mean=-5.536622, mel_std=2.116101), out_size=None)

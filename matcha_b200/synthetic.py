@@ -109,3 +109,42 @@ def prefix_mask(lengths, t_pad):
     """sequence_mask (matcha/utils/model.py:7-11) as float (B,1,T)."""
     lengths = torch.as_tensor(lengths)
     return (torch.arange(t_pad).unsqueeze(0) < lengths.unsqueeze(1)).float().unsqueeze(1)
+
+
+def text_encoder_state_dict(n_spks=1, spk_emb_dim=64, seed=1234, n_vocab=178, n_channels=192, filter_channels=768,
+                            filter_channels_dp=256, n_layers=6, kernel_size=3, n_feats=80, prefix=""):
+    """`TextEncoder` parameters with the reference key layout (text_encoder.py:313-375); every constant-initialised
+    tensor (prenet.proj zeros, LayerNorm gamma/beta, biases) is randomised.  Durations stay moderate: the duration
+    head's output scale gives exp(logw) of a few frames per token."""
+    g = _g(seed)
+    sd = {}
+    ch = n_channels + (spk_emb_dim if n_spks > 1 else 0)
+
+    def conv(name, out_c, in_c, k, gain=1.0):
+        sd[prefix + name + ".weight"] = torch.randn(out_c, in_c, k, generator=g) * (gain * math.sqrt(1.0 / (in_c * k)))
+        sd[prefix + name + ".bias"] = torch.randn(out_c, generator=g) * 0.05
+
+    def norm(name, c):
+        sd[prefix + name + ".gamma"] = 1.0 + 0.2 * torch.randn(c, generator=g)
+        sd[prefix + name + ".beta"] = 0.1 * torch.randn(c, generator=g)
+
+    sd[prefix + "emb.weight"] = torch.randn(n_vocab, n_channels, generator=g) * n_channels ** -0.5
+    for i in range(3):
+        conv(f"prenet.conv_layers.{i}", n_channels, n_channels, 5)
+        norm(f"prenet.norm_layers.{i}", n_channels)
+    conv("prenet.proj", n_channels, n_channels, 1, gain=0.5)
+    for i in range(n_layers):
+        for p in ("conv_q", "conv_k", "conv_v", "conv_o"):
+            conv(f"encoder.attn_layers.{i}.{p}", ch, ch, 1)
+        norm(f"encoder.norm_layers_1.{i}", ch)
+        conv(f"encoder.ffn_layers.{i}.conv_1", filter_channels, ch, kernel_size)
+        conv(f"encoder.ffn_layers.{i}.conv_2", ch, filter_channels, kernel_size)
+        norm(f"encoder.norm_layers_2.{i}", ch)
+    conv("proj_m", n_feats, ch, 1)
+    conv("proj_w.conv_1", filter_channels_dp, ch, kernel_size)
+    norm("proj_w.norm_1", filter_channels_dp)
+    conv("proj_w.conv_2", filter_channels_dp, filter_channels_dp, kernel_size)
+    norm("proj_w.norm_2", filter_channels_dp)
+    conv("proj_w.proj", 1, filter_channels_dp, 1, gain=0.6)
+    sd[prefix + "proj_w.proj.bias"] = torch.full((1,), 0.6)
+    return sd

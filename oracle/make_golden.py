@@ -81,6 +81,42 @@ def generator_case(name, b, t, seed, weight_norm):
     print(name, "wav", float(wav.abs().max()), float(wav.abs().mean()))
 
 
+def encoder_case(name, n_spks, lengths, seed, length_scale):
+    """Upstream of the hot path: the reference TextEncoder + the duration / alignment steps of
+    MatchaTTS.synthesise (matcha_tts.py:115-131), run with the reference's own functions."""
+    ref_shims.install()
+    from matcha.models.components.text_encoder import TextEncoder
+    from matcha.utils.model import fix_len_compatibility, generate_path, sequence_mask
+    ns = types.SimpleNamespace
+    params = ns(n_feats=80, n_channels=192, filter_channels=768, filter_channels_dp=256, n_heads=2, n_layers=6,
+                kernel_size=3, p_dropout=0.1, spk_emb_dim=64, n_spks=n_spks, prenet=True)
+    dp = ns(filter_channels_dp=256, kernel_size=3, p_dropout=0.1)
+    enc = TextEncoder("RoPE Encoder", params, dp, 178, n_spks, 64).eval()
+    enc.load_state_dict(weights.text_encoder_state_dict(n_spks=n_spks, seed=seed), strict=True)
+    g = torch.Generator().manual_seed(seed)
+    b, lx = len(lengths), max(lengths)
+    x = torch.randint(1, 178, (b, lx), generator=g)
+    x_lengths = torch.tensor(lengths)
+    for i, n in enumerate(lengths):
+        x[i, n:] = 0
+    spks = torch.randn(b, 64, generator=g) if n_spks > 1 else None
+    with torch.inference_mode():
+        mu_x, logw, x_mask = enc(x, x_lengths, spks)
+        w_ceil = torch.ceil(torch.exp(logw) * x_mask) * length_scale
+        y_lengths = torch.clamp_min(torch.sum(w_ceil, [1, 2]), 1).long()
+        y_max = y_lengths.max()
+        t_pad = fix_len_compatibility(y_max)
+        y_mask = sequence_mask(y_lengths, t_pad).unsqueeze(1).to(x_mask.dtype)
+        attn_mask = x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)
+        attn = generate_path(w_ceil.squeeze(1), attn_mask.squeeze(1)).unsqueeze(1)
+        mu_y = torch.matmul(attn.squeeze(1).transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
+    fx = dict(n_spks=n_spks, seed=seed, length_scale=length_scale, x=x, x_lengths=x_lengths, spks=spks,
+              mu_x=mu_x.clone(), logw=logw.clone(), x_mask=x_mask.clone(), y_lengths=y_lengths.clone(), t_pad=int(t_pad),
+              attn=attn.clone().to(torch.uint8), mu_y=mu_y.clone())
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "Lx", lx, "y_lengths", y_lengths.tolist(), "t_pad", int(t_pad))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
@@ -91,6 +127,8 @@ def main():
     estimator_case("est_lj_t140", 160, (140, 77), 140, seed=14, n_steps=2, t_scalar=0.5)
     generator_case("gen_plain", 2, 9, seed=21, weight_norm=False)
     generator_case("gen_weightnorm", 1, 5, seed=22, weight_norm=True)
+    encoder_case("enc_lj_ragged", 1, (23, 9, 16), seed=31, length_scale=1.0)
+    encoder_case("enc_vctk_scaled", 109, (12, 20), seed=32, length_scale=1.5)
 
 
 if __name__ == "__main__":

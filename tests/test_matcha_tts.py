@@ -1,0 +1,117 @@
+"""`matcha_b200.MatchaTTS`: the synthesis-side drop-in (SURVEY §8(b) boundary #1).
+
+CPU tests pin the upstream of the hot path (text encoder, durations, length regulation) against golden vectors made by
+the UNMODIFIED reference TextEncoder / generate_path (oracle/make_golden.py: encoder_case).  The GPU test runs the
+whole `synthesise` call and checks the decoder output against the CPU oracle fed the same mu_y.
+"""
+import os
+
+import pytest
+import torch
+
+import matcha_b200 as mb
+from matcha_b200 import matcha_tts as mt
+from matcha_b200 import synthetic
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _fx(name):
+    return torch.load(os.path.join(GOLDEN, name + ".pt"), weights_only=False)
+
+
+def _encoder(fx):
+    cfg = mt.default_config(n_spks=fx["n_spks"])
+    enc = mt.TextEncoder(cfg["encoder"].encoder_type, cfg["encoder"].encoder_params,
+                         cfg["encoder"].duration_predictor_params, 178, fx["n_spks"], 64).eval()
+    enc.load_state_dict(synthetic.text_encoder_state_dict(n_spks=fx["n_spks"], seed=fx["seed"]), strict=True)
+    return enc
+
+
+@pytest.mark.parametrize("name", ["enc_lj_ragged", "enc_vctk_scaled"])
+def test_text_encoder_matches_reference_golden(name):
+    fx = _fx(name)
+    enc = _encoder(fx)
+    with torch.inference_mode():
+        mu_x, logw, x_mask = enc(fx["x"], fx["x_lengths"], fx["spks"])
+    assert torch.equal(x_mask, fx["x_mask"])
+    assert float((mu_x - fx["mu_x"]).abs().max()) < 2e-4
+    assert float((logw - fx["logw"]).abs().max()) < 2e-4
+
+
+@pytest.mark.parametrize("name", ["enc_lj_ragged", "enc_vctk_scaled"])
+def test_length_regulation_is_the_alignment_matmul(name):
+    fx = _fx(name)
+    # from the reference's own mu_x / logw, so that ceil() sees identical inputs
+    w_ceil = torch.ceil(torch.exp(fx["logw"]) * fx["x_mask"]) * fx["length_scale"]
+    y_lengths = torch.clamp_min(torch.sum(w_ceil, [1, 2]), 1).long()
+    assert torch.equal(y_lengths, fx["y_lengths"])
+    t_pad = mt.fix_len_compatibility(int(y_lengths.max()))
+    assert t_pad == fx["t_pad"]
+    mu_y, attn, y_mask = mt.length_regulate(fx["mu_x"], w_ceil, fx["x_mask"], y_lengths, t_pad)
+    assert torch.equal(attn.to(torch.uint8), fx["attn"].squeeze(1))
+    assert torch.equal(mu_y, fx["mu_y"])          # a 0/1 alignment matmul is a gather: bit-exact
+    assert torch.equal(y_mask.squeeze(1).sum(1).long(), y_lengths)
+    assert float(mu_y[0, :, int(y_lengths[0]):].abs().max() if int(y_lengths[0]) < t_pad else 0.0) == 0.0
+
+
+def test_fix_len_and_generate_path_edges():
+    assert [mt.fix_len_compatibility(n) for n in (1, 4, 5, 451, 3001)] == [4, 4, 8, 452, 3004]
+    dur = torch.tensor([[2.0, 0.0, 3.0]])
+    mask = torch.ones(1, 3, 8)
+    path = mt.generate_path(dur, mask)
+    assert path[0].tolist() == [[1, 1, 0, 0, 0, 0, 0, 0], [0] * 8, [0, 0, 1, 1, 1, 0, 0, 0]]
+
+
+def test_module_surface_and_state_dict_layout():
+    for n_spks in (1, 109):
+        model = mb.MatchaTTS(**mt.default_config(n_spks=n_spks))
+        keys = set(model.state_dict().keys())
+        assert {"mel_mean", "mel_std", "encoder.emb.weight", "encoder.prenet.proj.weight",
+                "encoder.encoder.attn_layers.5.conv_o.bias", "encoder.encoder.norm_layers_2.0.gamma",
+                "encoder.proj_w.norm_2.beta", "encoder.proj_m.weight",
+                "decoder.estimator.final_proj.weight"} <= keys
+        assert ("spk_emb.weight" in keys) == (n_spks > 1)
+        enc_keys = {k[len("encoder."):] for k in keys if k.startswith("encoder.")}
+        assert enc_keys == set(synthetic.text_encoder_state_dict(n_spks=n_spks).keys())
+        c_in = 160 if n_spks == 1 else 224
+        assert model.state_dict()["decoder.estimator.time_mlp.linear_1.weight"].shape == (1024, c_in)
+    with pytest.raises(NotImplementedError):
+        model(None)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_spks", [1, 109])
+def test_synthesise_end_to_end_against_oracle(n_spks):
+    from oracle import matcha_oracle as mo
+    c_in = 160 if n_spks == 1 else 224
+    model = mb.MatchaTTS(**mt.default_config(n_spks=n_spks))
+    enc_sd = synthetic.text_encoder_state_dict(n_spks=n_spks, seed=5)
+    est_sd = synthetic.estimator_state_dict(c_in, seed=6)
+    sd = {"encoder." + k: v for k, v in enc_sd.items()}
+    sd.update({"decoder." + k: v for k, v in est_sd.items()})
+    sd["mel_mean"], sd["mel_std"] = torch.tensor(-5.5), torch.tensor(2.1)
+    g = torch.Generator().manual_seed(3)
+    if n_spks > 1:
+        sd["spk_emb.weight"] = torch.randn(n_spks, 64, generator=g)
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().eval()
+    model.decoder.estimator.precision = "fp32"
+    x = torch.randint(1, 178, (3, 19), generator=g)
+    x_lengths = torch.tensor([19, 7, 12])
+    spk_ids = torch.tensor([4, 100, 0]) if n_spks > 1 else None
+    out = model.synthesise(x.cuda(), x_lengths.cuda(), n_timesteps=3, temperature=0.0,
+                           spks=None if spk_ids is None else spk_ids.cuda(), length_scale=1.0)
+    y_len = out["mel_lengths"].cpu()
+    y_max = int(y_len.max())
+    assert out["decoder_outputs"].shape == (3, 80, y_max) and out["encoder_outputs"].shape == (3, 80, y_max)
+    assert out["attn"].shape[0] == 3 and out["attn"].shape[1] == 1 and isinstance(out["rtf"], float)
+    # oracle: same mu_y (padded to the estimator's length), zero noise (temperature 0), CPU fp32 Euler decode
+    t_pad = mt.fix_len_compatibility(y_max)
+    mu_y = torch.zeros(3, 80, t_pad)
+    mu_y[:, :, :y_max] = out["encoder_outputs"].cpu()
+    mask = mt.sequence_mask(y_len, t_pad).unsqueeze(1).float()
+    spk_vec = None if spk_ids is None else sd["spk_emb.weight"][spk_ids]
+    ref = mo.solve_euler(est_sd, torch.zeros_like(mu_y), mu_y, mask, 3, spks=spk_vec)[:, :, :y_max]
+    assert float((out["decoder_outputs"].cpu() - ref).abs().max()) <= 1e-3
+    assert torch.allclose(out["mel"].cpu(), out["decoder_outputs"].cpu() * 2.1 - 5.5, atol=1e-5)
