@@ -247,3 +247,43 @@ def test_full_size_properties_cfg2():
     assert torch.equal(dec16[pad], z[pad]) and torch.equal(dec32[pad], z[pad])
     assert float(wav16.abs().max()) <= 1.0 and torch.isfinite(wav16).all()
     assert wav16.shape == (b, 1, 451 * 256)
+
+
+@pytest.mark.parametrize("cfg", ["cfg3", "cfg4"])
+def test_full_size_properties_other_configs(cfg):
+    """BASELINE.json's other configurations as parity cases: cfg3 = VCTK (C_in 224, speaker vectors),
+    4 Euler steps, one GPU's share of the batch; cfg4 = long form, B=16, 3001 valid frames (T_pad 3004, vocoder length
+    not a multiple of 4), 10 steps.  Same size-independent properties as cfg2."""
+    g = torch.Generator().manual_seed(1234)
+    if cfg == "cfg3":
+        b, t_valid, n_steps, c_in = 64, 451, 4, 224
+        mean, std = -6.630575, 2.482914
+    else:
+        b, t_valid, n_steps, c_in = 16, 3001, 10, 160
+        mean, std = -5.536622, 2.116101
+    t_pad = (t_valid + 3) // 4 * 4
+    lens = [t_valid] * (b - 4) + [int(v) for v in torch.randint(t_valid // 8, t_valid, (4,), generator=g)]
+    est_sd, gen_sd = weights.estimator_state_dict(c_in, seed=1234), weights.generator_state_dict(1234)
+    mu = torch.randn(b, 80, t_pad, generator=g).cuda()
+    z = (torch.randn(b, 80, t_pad, generator=g) * 0.667).cuda()
+    spks = torch.randn(b, 64, generator=g).cuda() if c_in == 224 else None
+    mask = weights.prefix_mask(lens, t_pad).cuda()
+    out = {}
+    for prec in ("fp16", "fp32"):
+        plan = Plan(prec, c_in)
+        plan.load_estimator(est_sd)
+        plan.load_generator(gen_sd)
+        out[prec] = tuple(t.cpu() for t in plan.synthesise(mu, mask, z, n_steps, t_valid, mean, std, spks=spks))
+        if prec == "fp16":   # CUDA-graph replay gives the same result (atomics order only)
+            again = plan.synthesise(mu, mask, z, n_steps, t_valid, mean, std, spks=spks)
+            assert rel_l2(again[2].cpu(), out[prec][2]) < 5e-3
+        del plan
+        torch.cuda.empty_cache()
+    dec16, mel16, wav16 = out["fp16"]
+    dec32, mel32, wav32 = out["fp32"]
+    assert rel_l2(dec16, dec32) <= HALF_REL_L2
+    assert rel_l2(wav16, wav32) <= 2 * HALF_REL_L2   # long vocoder chains on random weights: still within 2 %
+    pad = (mask.expand_as(z) == 0).cpu()
+    assert torch.equal(dec16[pad], z.cpu()[pad]) and torch.equal(dec32[pad], z.cpu()[pad])
+    assert float(wav16.abs().max()) <= 1.0 and torch.isfinite(wav16).all()
+    assert wav16.shape == (b, 1, t_valid * 256)
