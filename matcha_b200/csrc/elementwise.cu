@@ -10,6 +10,15 @@ namespace mb {
 
 // ---------------------------------------------------------------- GroupNorm apply + Mish (+temb) + mask
 // out = (mish(gn(raw)) + tadd) * mask   (decoder.py:37-43 followed by :58 and the next block's x*mask, :41)
+// fp32 mode keeps the accurate expf / division; the half modes round the result to 11 / 8 bits anyway and use the SFU forms
+template <typename T> __device__ __forceinline__ float mish_sel(float x) { return mish_f(x); }
+template <> __device__ __forceinline__ float mish_sel<__half>(float x) {
+  if (x > 20.f) return x;
+  const float n = __expf(x), w = n * (n + 2.f);
+  return x * __fdividef(w, w + 2.f);
+}
+template <> __device__ __forceinline__ float mish_sel<__nv_bfloat16>(float x) { return mish_sel<__half>(x); }
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 gn_mish_kernel(const T* __restrict__ raw, const float* __restrict__ stats, const float* __restrict__ gamma,
@@ -17,29 +26,38 @@ gn_mish_kernel(const T* __restrict__ raw, const float* __restrict__ stats, const
                const float* __restrict__ mask, T* __restrict__ out, int Tn, long total_vec, float inv_count) {
   const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;  // one 8-channel vector of a 256-ch row
   if (i >= total_vec) return;
-  const long row = i >> 5;
+  const int row = static_cast<int>(i >> 5);
   const int c0 = static_cast<int>(i & 31) * 8;
-  const int b = static_cast<int>(row / Tn);
+  const int b = row / Tn;
   const float m = __ldg(mask + row);
   float o[8];
   if (m == 0.f) {  // exact: anything times a zero mask is zero (inputs are finite)
 #pragma unroll
     for (int k = 0; k < 8; ++k) o[k] = 0.f;
   } else {
-    const float* st = stats + (static_cast<long>(b) * 8 + (c0 >> 5)) * 2;
-    const float mean = st[0] * inv_count;
-    const float rstd = rsqrtf(fmaxf(st[1] * inv_count - mean * mean, 0.f) + 1e-5f);
     float r[8];
-    Elem<T>::ld8(raw + row * 256 + c0, r);
+    Elem<T>::ld8(raw + static_cast<long>(row) * 256 + c0, r);
+    const float2 st = __ldg(reinterpret_cast<const float2*>(stats + (b * 8 + (c0 >> 5)) * 2));
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c0)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c0 + 4));
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c0)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c0 + 4));
+    float4 t0 = make_float4(0.f, 0.f, 0.f, 0.f), t1 = t0;
+    if (tadd) {
+      const float* tp = tadd + static_cast<long>(b) * tadd_bstride + c0;
+      t0 = __ldg(reinterpret_cast<const float4*>(tp));
+      t1 = __ldg(reinterpret_cast<const float4*>(tp + 4));
+    }
+    const float mean = st.x * inv_count;
+    const float rstd = rsqrtf(fmaxf(st.y * inv_count - mean * mean, 0.f) + 1e-5f);
+    const float ga[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const float be[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    const float ta[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const float y = (r[k] - mean) * rstd * __ldg(gamma + c0 + k) + __ldg(beta + c0 + k);
-      float v = mish_f(y);
-      if (tadd) v += __ldg(tadd + static_cast<long>(b) * tadd_bstride + c0 + k);
-      o[k] = v * m;
+      const float y = (r[k] - mean) * rstd * ga[k] + be[k];
+      o[k] = (mish_sel<T>(y) + ta[k]) * m;
     }
   }
-  Elem<T>::st8(out + row * 256 + c0, o);
+  Elem<T>::st8(out + static_cast<long>(row) * 256 + c0, o);
 }
 
 template <typename T>
@@ -267,21 +285,34 @@ cudaError_t launch_affine_crop(const float* in, int Tsrc, float scale, float shi
 }
 
 // conv_post Conv1d(32,1,7,pad 3) + tanh (hifigan/models.py:177,194-195); the input already carries leaky_relu(0.01).
+// conv_post (32 -> 1, k = 7, pad 3) + tanh (hifigan/models.py:177,193-195; cli.py:118's clamp is a no-op after tanh).
+// One block = 256 consecutive samples of one utterance: the 262 input rows are staged once in shared memory with
+// coalesced 16-byte loads (row pitch padded to 20 words: conflict-free 16-byte reads), then every thread does its 224 FMAs.
 template <typename T>
 __global__ void __launch_bounds__(256)
 conv_post_kernel(const T* __restrict__ in, const float* __restrict__ w, float bias, float* __restrict__ wav, long L) {
+  constexpr int kRows = 256 + 6;
+  constexpr int kPitch = 32 * sizeof(T) + 16;          // bytes
   __shared__ float ws[7 * 32];
+  __shared__ __align__(16) unsigned char tile[kRows * kPitch];
   for (int i = threadIdx.x; i < 7 * 32; i += blockDim.x) ws[i] = w[i];
-  __syncthreads();
-  const long t = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long t0 = static_cast<long>(blockIdx.x) * 256;
   const long b = blockIdx.y;
+  constexpr int kVec = 32 * sizeof(T) / 16;            // 16-byte pieces per row
+  for (int i = threadIdx.x; i < kRows * kVec; i += blockDim.x) {
+    const int r = i / kVec, q = i % kVec;
+    const long srow = t0 + r - 3;
+    uint4 v = make_uint4(0, 0, 0, 0);                  // zero padding outside [0, L)
+    if (srow >= 0 && srow < L) v = __ldg(reinterpret_cast<const uint4*>(in + (b * L + srow) * 32) + q);
+    *reinterpret_cast<uint4*>(tile + r * kPitch + q * 16) = v;
+  }
+  __syncthreads();
+  const long t = t0 + threadIdx.x;
   if (t >= L) return;
   float acc = bias;
 #pragma unroll
   for (int j = 0; j < 7; ++j) {
-    const long s = t + j - 3;
-    if (s < 0 || s >= L) continue;
-    const T* p = in + (b * L + s) * 32;
+    const T* p = reinterpret_cast<const T*>(tile + (threadIdx.x + j) * kPitch);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       float v[8];
