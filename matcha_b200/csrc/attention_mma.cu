@@ -1,8 +1,8 @@
 // Tensor-core self-attention for the half-precision modes (same contract as attention.cu):
 //   out[b, q, h*64:(h+1)*64] = softmax_k(q . k + mask[b, k]) v      2 heads x 64, all L keys, additive 0/1 mask.
 // Flash-style: one CTA = 64 query rows of one (batch, head); 4 warps x 16 rows; K/V streamed in 64-key tiles through
-// XOR-swizzled shared memory; S = Q K^T and O += P V on mma.sync.m16n8k16 (fp32 accumulate), online softmax in
-// registers.  Attention is ~1 % of the path's FLOPs; the tcgen05 budget went to the conv-GEMMs.
+// double-buffered, XOR-swizzled shared memory (cp.async: the next tile lands while this one is multiplied);
+// S = Q K^T and O += P V on mma.sync.m16n8k16 (fp32 accumulate), online softmax in registers; 4 CTAs per SM.  Attention is ~1 % of the path's FLOPs; the tcgen05 budget went to the conv-GEMMs.
 #include "conv.cuh"
 #include "launch.h"
 
@@ -45,22 +45,27 @@ __device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
 // Tile [64 rows][64 halves] = 8 chunks of 16 bytes per row; chunk index XOR (row & 7) kills ldmatrix bank conflicts.
 __device__ __forceinline__ uint32_t swz(int row, int chunk) { return static_cast<uint32_t>(row * 128 + ((chunk ^ (row & 7)) << 4)); }
 
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
+  const int bytes = valid ? 16 : 0;   // src-size 0: the 16 destination bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 }  // namespace
 
 template <typename T>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 4)
 attention_mma_kernel(const T* __restrict__ qkv, const float* __restrict__ mask, T* __restrict__ out, int L) {
   __shared__ __align__(128) uint8_t Qs[64 * 128];
-  __shared__ __align__(128) uint8_t Ks[64 * 128];
-  __shared__ __align__(128) uint8_t Vs[64 * 128];
-  __shared__ float Ms[64];
+  __shared__ __align__(128) uint8_t KVs[2][2][64 * 128];   // [buffer][K / V]
+  __shared__ float Msb[2][64];
   const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * 64;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, tq = lane & 3;
   const T* base = qkv + static_cast<long>(b) * L * 384;
   const uint32_t qs = static_cast<uint32_t>(__cvta_generic_to_shared(Qs));
-  const uint32_t ks = static_cast<uint32_t>(__cvta_generic_to_shared(Ks));
-  const uint32_t vs = static_cast<uint32_t>(__cvta_generic_to_shared(Vs));
+  const uint32_t kv0 = static_cast<uint32_t>(__cvta_generic_to_shared(&KVs[0][0][0]));
 
   // tile loader: 64 rows x 8 chunks = 512 x 16 B, 4 per thread
   auto load_tile = [&](uint8_t* dst, int row0, int col0) {
@@ -72,6 +77,20 @@ attention_mma_kernel(const T* __restrict__ qkv, const float* __restrict__ mask, 
       *reinterpret_cast<uint4*>(dst + swz(r, c)) = v;
     }
   };
+  // asynchronous K/V tile: 2 x 512 pieces of 16 B, 8 per thread; rows beyond L are zero-filled
+  auto issue_kv = [&](int buf, int k0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int idx = tid + i * 128, r = idx >> 3, c = idx & 7;
+      const bool ok = k0 + r < L;
+      const T* src = base + static_cast<long>(ok ? k0 + r : 0) * 384 + h * 64 + c * 8;
+      cp_async16(kv0 + (buf * 2 + 0) * 8192 + swz(r, c), src + 128, ok);
+      cp_async16(kv0 + (buf * 2 + 1) * 8192 + swz(r, c), src + 256, ok);
+    }
+    if (tid < 64) Msb[buf][tid] = (k0 + tid < L) ? mask[static_cast<long>(b) * L + k0 + tid] : -INFINITY;
+    cp_async_commit();
+  };
+  issue_kv(0, 0);
   load_tile(Qs, q0, h * 64);
   __syncthreads();
   uint32_t qa[4][4];  // A fragments of this warp's 16 query rows for the 4 k-steps over d
@@ -85,12 +104,17 @@ attention_mma_kernel(const T* __restrict__ qkv, const float* __restrict__ mask, 
   for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;  // rows g and g+8
 
-  for (int k0 = 0; k0 < L; k0 += 64) {
-    __syncthreads();  // previous tile fully consumed
-    load_tile(Ks, k0, 128 + h * 64);
-    load_tile(Vs, k0, 256 + h * 64);
-    if (tid < 64) Ms[tid] = (k0 + tid < L) ? mask[static_cast<long>(b) * L + k0 + tid] : -INFINITY;
-    __syncthreads();
+  int buf = 0;
+  for (int k0 = 0; k0 < L; k0 += 64, buf ^= 1) {
+    if (k0 + 64 < L) {          // the other buffer was released by the barrier that ended the previous iteration
+      issue_kv(buf ^ 1, k0 + 64);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();            // this tile (and its mask row) is visible to every warp
+    const uint32_t ks = kv0 + (buf * 2 + 0) * 8192, vs = kv0 + (buf * 2 + 1) * 8192;
+    const float* Ms = Msb[buf];
     // S = Q K^T : 16 x 64 per warp
     float s[8][4];
 #pragma unroll
@@ -146,6 +170,7 @@ attention_mma_kernel(const T* __restrict__ qkv, const float* __restrict__ mask, 
         MmaT<T>::mma(o[2 * jp + 1], pa[kk], vb[2], vb[3]);
       }
     }
+    __syncthreads();            // every warp is done with this buffer before it is refilled
   }
   l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
   l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
