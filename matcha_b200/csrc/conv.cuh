@@ -67,6 +67,21 @@ struct ConvGeom2 {
   long long* dbg_out;   // -DMB200_PROBE builds only: per-CTA cycle counters [grid][16]
 };
 
+// Geometry of the fused ResBlock step (resblock_pair.cu): c1 (K taps, dilation dil) and c2 (K taps, dilation 1) on C
+// channels, tiles of 128*mb intermediate rows that advance by S output rows.
+struct PairGeom {
+  int B, T;                      // batch, rows per batch element
+  int K, dil;
+  int S;                         // output rows per tile = 128*mb - (K-1)
+  int tiles_per_b, total_tiles;
+  int extra;                     // 8-row halo boxes after the first 128*mb rows of the input tile
+  int a_stages, a_bytes;         // input ring
+  int mid_bytes;                 // intermediate tile (128*mb + 16 rows)
+  int w_resident, w_stages;      // both convs' weights resident, or streamed two taps per ring stage
+  const float* bias1;            // c1 bias [C]
+  float slope;                   // LeakyReLU between the convs
+};
+
 struct EpiParams {
   int T_o;                 // output rows per batch (T_out * o_mul)
   int o_mul;               // output row = t * o_mul + phase * o_phase_step

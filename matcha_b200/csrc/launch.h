@@ -22,6 +22,14 @@ struct ConvLaunch {
   int pdl;              // launch with programmatic stream serialization (prologue overlaps the previous kernel's tail)
 };
 
+struct PairLaunch {
+  CUtensorMap tmA, tmA8, tmW1, tmW2;
+  PairGeom g;
+  EpiParams e;        // c2's epilogue (bias2, residual, branch sum, scale, output)
+  int C, mb, smem_bytes, grid;
+};
+
+template <typename T> cudaError_t launch_resblock_pair(const PairLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_conv_umma(const ConvLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_conv_simt(const ConvLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_conv_umma2(const ConvLaunch& L, cudaStream_t st);

@@ -39,6 +39,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_PDL")) use_pdl = std::atoi(v);
   if (const char* v = std::getenv("MB200_TILE_POLICY")) tile_policy = std::atoi(v);
   if (const char* v = std::getenv("MB200_KERNEL")) kernel_version = std::atoi(v);
+  if (const char* v = std::getenv("MB200_FUSE_PAIRS")) fuse_pairs = std::atoi(v);
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -376,6 +377,57 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
   });
   op.kind = 0;
   op.flops = 2.0 * B * T_out * W.n_phases * static_cast<double>(W.n_valid) * W.k_real;
+  return op;
+}
+
+Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* in, int C, int B, int T, EpiParams e) {
+  if (!pair_supported(C)) throw Error("pair_op: unsupported configuration");
+  const int K = W1.n_taps;
+  if (W2.n_taps != K || !(K & 1) || K > kMaxTaps) throw Error("pair_op: both convs need the same odd kernel size");
+  if (W1.N != C || W2.N != C || W1.K_total != K * C || W2.K_total != K * C || W1.kc != C || W1.ntile != C || W2.kc != C ||
+      W2.ntile != C || W1.n_phases != 1 || W2.n_phases != 1)
+    throw Error("pair_op: packed weights do not match a C -> C conv pair");
+  PairLaunch L{};
+  L.C = C;
+  L.mb = C == 64 ? 2 : 4;
+  const int R = 128 * L.mb, rowb = C * 2, w_tile = C * rowb;
+  PairGeom& g = L.g;
+  g.B = B; g.T = T; g.K = K; g.dil = dil;
+  g.S = R - (K - 1);
+  g.tiles_per_b = (T + g.S - 1) / g.S;
+  g.total_tiles = B * g.tiles_per_b;
+  g.extra = ((K - 1) * dil + 7) / 8;
+  if (g.extra > 8) throw Error("pair_op: tap span exceeds the halo capacity");
+  g.a_bytes = (R + 64) * rowb;
+  g.mid_bytes = (R + 16) * rowb;
+  g.bias1 = W1.bias;
+  g.slope = 0.1f;
+  const int tail_bytes = 1024 + 512 + 8 * 4608;
+  const int budget = 227 * 1024 - tail_bytes - g.mid_bytes;
+  const int w_all = 2 * K * w_tile;
+  if ((budget - w_all) / g.a_bytes >= 2) {
+    g.w_resident = 1; g.w_stages = 0;
+    g.a_stages = std::min(4, (budget - w_all) / g.a_bytes);
+    L.smem_bytes = g.a_stages * g.a_bytes + g.mid_bytes + w_all + tail_bytes;
+  } else {
+    g.w_resident = 0; g.a_stages = 2;
+    g.w_stages = std::min(8, (budget - 2 * g.a_bytes) / (2 * w_tile));
+    if (g.w_stages < 3) throw Error("pair_op: weight ring does not fit");
+    L.smem_bytes = 2 * g.a_bytes + g.mid_bytes + g.w_stages * 2 * w_tile + tail_bytes;
+  }
+  e.o_mul = 1; e.o_phase_step = 1; e.T_o = T; e.n_valid = C; e.bias = W2.bias;
+  L.e = e;
+  L.tmA = tmap_act(in, C, T, B, C);
+  L.tmA8 = tmap_act(in, C, T, B, C, 8);
+  L.tmW1 = W1.tm;
+  L.tmW2 = W2.tm;
+  L.grid = std::min(g.total_tiles, num_sms);
+  const int dtype = cfg.dtype;
+  Launch op([L, dtype](cudaStream_t st) -> cudaError_t {
+    return dtype == MB200_BF16 ? launch_resblock_pair<__nv_bfloat16>(L, st) : launch_resblock_pair<__half>(L, st);
+  });
+  op.kind = 0;
+  op.flops = 2.0 * B * T * static_cast<double>(C) * (W1.k_real + W2.k_real);
   return op;
 }
 

@@ -1,0 +1,299 @@
+// One HiFi-GAN ResBlock1 step as ONE persistent tcgen05 kernel (narrow stages, C = 64 / 32 channels):
+//
+//     x <- x + c2( lrelu( c1( lrelu(x) ) ) )            matcha/hifigan/models.py:90-97
+//
+// Run as two conv-GEMM launches the step moves five activation-sized streams through HBM (read lrelu(x), write the
+// intermediate, read it back, read the residual, write the result) and stages 3-4 sit on the HBM roofline.  Here the
+// intermediate never leaves the SM: per tile of R = 128*MB rows
+//     TMA   x halo tile (R + (K-1)*dil rows)                       -> shared memory ring
+//     MMA1  c1 over the halo tile (taps = row-shifted descriptors) -> TMEM accumulator ring 1
+//     E1    + bias1, LeakyReLU, zero outside [0, T), half          -> shared memory "mid" tile in the UMMA K-major
+//                                                                     swizzled layout (the writer swizzles by hand)
+//     MMA2  c2 over the mid tile                                   -> TMEM accumulator ring 2
+//     E2    the usual fused epilogue (epilogue3.cuh): + bias2 + residual (+ branch sum, scale) -> global
+// Tiles advance by S = R - (K-1) output rows: c1 is recomputed on the K-1 halo rows (2-4 %), which is what makes the
+// tiles independent.  Two streams per step instead of five.
+//
+// Warp roles (448 threads): 0 TMA producer, 1 MMA issuer (both convs, software-pipelined M1(n+1) before M2(n)),
+// 2-5 E1, 6-13 E2.  Producer and issuer are converged warps with elected single-thread instructions.
+#include "conv.cuh"
+#include "epilogue3.cuh"
+#include "launch.h"
+#include "ptx.cuh"
+
+namespace mb {
+
+namespace {
+constexpr int kPairBarBytes = 512;
+}
+
+template <int C, int MB, typename T>
+__global__ void __launch_bounds__(448, 1)
+resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA8,
+                     const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2,
+                     const __grid_constant__ PairGeom g, const __grid_constant__ EpiParams e) {
+  constexpr int ROWB = C * 2;             // bytes per activation row = one swizzle span (128 B / 64 B)
+  constexpr int W_TILE = C * ROWB;        // one tap of one conv
+  constexpr int W_STAGE = 2 * W_TILE;     // streamed weights: two taps per ring stage
+  constexpr int SLOT = MB * C;            // TMEM columns of one accumulator buffer
+  constexpr int R = 128 * MB;
+  constexpr int EG = 2;
+  constexpr uint32_t SWZ = ROWB == 128 ? 7u : 3u;
+  static_assert(4 * SLOT <= 512, "two double-buffered accumulator rings must fit TMEM");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+
+  const int K = g.K, p = (K - 1) / 2;
+  const int n_wst = (K + 1) / 2;          // ring stages per conv when the weights are streamed
+  uint8_t* a_ring = smem;
+  uint8_t* mid = a_ring + g.a_stages * g.a_bytes;
+  uint8_t* w_base = mid + g.mid_bytes;
+  const int w_bytes = g.w_resident ? 2 * K * W_TILE : g.w_stages * W_STAGE;
+  uint8_t* tail = w_base + w_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* a_full = bars;            // [4]
+  uint64_t* a_empty = a_full + 4;     // [4]
+  uint64_t* w_full = a_empty + 4;     // [8]
+  uint64_t* w_empty = w_full + 8;     // [8]
+  uint64_t* t1_full = w_empty + 8;    // [2]
+  uint64_t* t1_empty = t1_full + 2;   // [2]
+  uint64_t* t2_full = t1_empty + 2;   // [2]
+  uint64_t* t2_empty = t2_full + 2;   // [2]
+  uint64_t* mid_full = t2_empty + 2;
+  uint64_t* mid_empty = mid_full + 1;
+  uint64_t* wres = mid_empty + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres + 1);
+  uint8_t* stage_base = tail + kPairBarBytes;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nt_cta = (g.total_tiles > static_cast<int>(blockIdx.x))
+                         ? (g.total_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmA8); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
+    for (int s = 0; s < 4; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < 8; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], 4);
+      mbar_init(&t2_full[s], 1); mbar_init(&t2_empty[s], 4 * EG);
+    }
+    mbar_init(mid_full, 4); mbar_init(mid_empty, 1); mbar_init(wres, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================================================= TMA producer
+    int as = 0, ws = 0;
+    uint32_t aph = 0, wph = 0;
+    auto load_A = [&](int n) {
+      const int tile = blockIdx.x + n * gridDim.x;
+      const int b = tile / g.tiles_per_b, t0 = (tile % g.tiles_per_b) * g.S;
+      const int row0 = t0 - p - p * g.dil;
+      mbar_wait(&a_empty[as], aph ^ 1);
+      if (elect_one()) {
+        uint8_t* dst = a_ring + as * g.a_bytes;
+        mbar_expect_tx(&a_full[as], (R + 8 * g.extra) * ROWB);
+#pragma unroll
+        for (int i = 0; i < MB; ++i) tma_load_3d(dst + i * 128 * ROWB, &tmA, &a_full[as], 0, row0 + 128 * i, b);
+        for (int x = 0; x < g.extra; ++x) tma_load_3d(dst + (R + 8 * x) * ROWB, &tmA8, &a_full[as], 0, row0 + R + 8 * x, b);
+      }
+      __syncwarp();
+      if (++as == g.a_stages) { as = 0; aph ^= 1; }
+    };
+    auto load_W = [&](const CUtensorMap* tm) {
+      for (int st = 0; st < n_wst; ++st) {
+        const int nt = min(2, K - 2 * st);
+        mbar_wait(&w_empty[ws], wph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(&w_full[ws], nt * W_TILE);
+          for (int j = 0; j < nt; ++j) tma_load_2d(w_base + ws * W_STAGE + j * W_TILE, tm, &w_full[ws], (2 * st + j) * C, 0);
+        }
+        __syncwarp();
+        if (++ws == g.w_stages) { ws = 0; wph ^= 1; }
+      }
+    };
+    if (g.w_resident) {
+      if (elect_one()) {
+        mbar_expect_tx(wres, static_cast<uint32_t>(w_bytes));
+        for (int j = 0; j < K; ++j) tma_load_2d(w_base + j * W_TILE, &tmW1, wres, j * C, 0);
+        for (int j = 0; j < K; ++j) tma_load_2d(w_base + (K + j) * W_TILE, &tmW2, wres, j * C, 0);
+      }
+      __syncwarp();
+      for (int n = 0; n < nt_cta; ++n) load_A(n);
+    } else if (nt_cta > 0) {
+      // same order as the issuer consumes: M1(0) | M1(n+1), M2(n) ...; the x tile of M1(n+2) is requested as soon as
+      // its ring stage can be free (M1(n) done), one whole c2 ahead of its use
+      load_A(0);
+      if (nt_cta > 1) load_A(1);
+      load_W(&tmW1);
+      for (int n = 0; n < nt_cta; ++n) {
+        if (n + 1 < nt_cta) load_W(&tmW1);
+        if (n + 2 < nt_cta) load_A(n + 2);
+        load_W(&tmW2);
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================= MMA issuer
+    constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 128, C);
+    constexpr uint32_t W16 = W_TILE >> 4, BLK16 = (128 * ROWB) >> 4, ROW16 = ROWB >> 4, WST16 = W_STAGE >> 4;
+    const uint32_t desc_hi = static_cast<uint32_t>(umma_smem_desc<ROWB>(0) >> 32);
+    const uint32_t a_lo0 = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(a_ring)));
+    const uint32_t mid_lo = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(mid)));
+    const uint32_t w_lo0 = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(w_base)));
+    const uint32_t a_stage16 = static_cast<uint32_t>(g.a_bytes) >> 4;
+    const int resident = g.w_resident;
+    if (resident) { mbar_wait(wres, 0); tc_fence_after(); }
+    int as = 0, ws = 0;
+    uint32_t aph = 0, wph = 0;
+    // all taps of one conv for the MB row blocks of a tile; operand rows advance by `row_step` rows per tap
+    auto issue_conv = [&](const uint32_t a_lo, const int row_step, const uint32_t dtm, const int which) {
+#pragma unroll 1
+      for (int st = 0; st < n_wst; ++st) {
+        uint32_t w_lo;
+        if (resident) {
+          w_lo = w_lo0 + static_cast<uint32_t>(which * K + 2 * st) * W16;
+        } else {
+          mbar_wait(&w_full[ws], wph);
+          w_lo = w_lo0 + ws * WST16;
+        }
+        tc_fence_after();
+        if (elect_one()) {
+          const int nt = min(2, K - 2 * st);
+          for (int j = 0; j < nt; ++j) {
+            const int tap = 2 * st + j;
+            const uint32_t a = a_lo + static_cast<uint32_t>(tap * row_step) * ROW16, w = w_lo + j * W16;
+#pragma unroll
+            for (int i = 0; i < MB; ++i) {
+#pragma unroll
+              for (int k = 0; k < C / 16; ++k)
+                umma_f16_lohi(dtm + i * C, a + i * BLK16 + 2 * k, w + 2 * k, desc_hi, idesc, (tap | k) != 0 ? 1u : 0u);
+            }
+          }
+          if (!resident) umma_commit(&w_empty[ws]);
+        }
+        __syncwarp();
+        if (!resident) { if (++ws == g.w_stages) { ws = 0; wph ^= 1; } }
+      }
+    };
+    auto M1 = [&](int n) {
+      const int slot = n & 1;
+      mbar_wait(&t1_empty[slot], ((n >> 1) & 1) ^ 1);
+      mbar_wait(&a_full[as], aph);
+      issue_conv(a_lo0 + as * a_stage16, g.dil, tmem_base + slot * SLOT, 0);
+      if (elect_one()) { umma_commit(&a_empty[as]); umma_commit(&t1_full[slot]); }
+      __syncwarp();
+      if (++as == g.a_stages) { as = 0; aph ^= 1; }
+    };
+    auto M2 = [&](int n) {
+      const int slot = n & 1;
+      mbar_wait(&t2_empty[slot], ((n >> 1) & 1) ^ 1);
+      mbar_wait(mid_full, n & 1);
+      issue_conv(mid_lo, 1, tmem_base + (2 + slot) * SLOT, 1);
+      if (elect_one()) { umma_commit(mid_empty); umma_commit(&t2_full[slot]); }
+      __syncwarp();
+    };
+    if (nt_cta > 0) M1(0);
+    for (int n = 0; n < nt_cta; ++n) {
+      if (n + 1 < nt_cta) M1(n + 1);
+      M2(n);
+    }
+  } else if (warp < 6) {
+    // ================================================================= E1: accumulator 1 -> mid tile (A operand of c2)
+    const int lane_grp = warp & 3;
+    const float slope = g.slope;
+    for (int n = 0; n < nt_cta; ++n) {
+      const int tile = blockIdx.x + n * gridDim.x;
+      const int t0 = (tile % g.tiles_per_b) * g.S, m0 = t0 - p;
+      const int slot = n & 1;
+      mbar_wait(&t1_full[slot], (n >> 1) & 1);
+      mbar_wait(mid_empty, (n & 1) ^ 1);      // c2 of the previous tile has finished reading the mid tile
+      tc_fence_after();
+#pragma unroll 1
+      for (int item = 0; item < MB * (C / 32); ++item) {
+        const int i = item / (C / 32), c = item % (C / 32);
+        const int r = i * 128 + lane_grp * 32 + lane;   // row of the mid tile held by this lane
+        const int m = m0 + r;
+        const bool live = (m >= 0) && (m < g.T);        // c2 zero-pads its INPUT: rows outside the utterance are 0
+        float acc[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * SLOT + i * C + c * 32, acc);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float bv[8], v[8];
+          ldg8f(g.bias1 + c * 32 + 8 * q, bv);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) v[ch] = acc[8 * q + ch] + bv[ch];
+          uint4 o;
+          if constexpr (std::is_same<T, __half>::value) {   // same arithmetic as the unfused fp16 epilogue
+            o = pack8<__half>(v);
+            __half2* h = reinterpret_cast<__half2*>(&o);
+            const __half2 sl = __float2half2_rn(slope);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) h[j] = __hmax2(h[j], __hmul2(h[j], sl));
+          } else {
+#pragma unroll
+            for (int ch = 0; ch < 8; ++ch) v[ch] = fmaxf(v[ch], v[ch] * slope);
+            o = pack8<T>(v);
+          }
+          if (!live) o = make_uint4(0, 0, 0, 0);
+          uint32_t off = static_cast<uint32_t>(r * ROWB + (c * 4 + q) * 16);
+          off ^= ((off >> 7) & SWZ) << 4;
+          *reinterpret_cast<uint4*>(mid + off) = o;
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async-proxy reads
+      __syncwarp();
+      if (lane == 0) { mbar_arrive(&t1_empty[slot]); mbar_arrive(mid_full); }
+    }
+  } else {
+    // ================================================================= E2: accumulator 2 -> global (fused epilogue)
+    const int grp = (warp - 6) >> 2;
+    const int lane_grp = warp & 3;
+    uint8_t* stg = stage_base + (warp - 6) * kStageBytes;
+    for (int n = 0; n < nt_cta; ++n) {
+      const int tile = blockIdx.x + n * gridDim.x;
+      const int b = tile / g.tiles_per_b, t0 = (tile % g.tiles_per_b) * g.S;
+      const int slot = n & 1;
+      const int t_lim = min(g.T, t0 + g.S);     // rows past S belong to the next tile
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + (2 + slot) * SLOT;
+      epilogue_tile3<C, MB, EG, T>(e, b, t0, t_lim, 0, 0, taddr, stg, nullptr, lane, lane_grp, grp, &t2_full[slot],
+                                   (n >> 1) & 1);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&t2_empty[slot]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+template <int C, int MB, typename T>
+static cudaError_t launch_pair_inst(const PairLaunch& L, cudaStream_t st) {
+  auto kern = resblock_pair_kernel<C, MB, T>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (err != cudaSuccess) return err;
+    configured = true;
+  }
+  kern<<<L.grid, 448, L.smem_bytes, st>>>(L.tmA, L.tmA8, L.tmW1, L.tmW2, L.g, L.e);
+  return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t launch_resblock_pair(const PairLaunch& L, cudaStream_t st) {
+  if (L.C == 64 && L.mb == 2) return launch_pair_inst<64, 2, T>(L, st);
+  if (L.C == 32 && L.mb == 4) return launch_pair_inst<32, 4, T>(L, st);
+  return cudaErrorInvalidConfiguration;
+}
+template cudaError_t launch_resblock_pair<__nv_bfloat16>(const PairLaunch&, cudaStream_t);
+template cudaError_t launch_resblock_pair<__half>(const PairLaunch&, cudaStream_t);
+
+}  // namespace mb

@@ -131,6 +131,25 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
       for (int m = 0; m < 3; ++m) {
         const PackedW& W1 = G.c1[3 * i + j][m];
         const PackedW& W2 = G.c2[3 * i + j][m];
+        const bool fused = single && pair_supported(C);
+        if (fused) {
+          // One kernel per ResBlock step (resblock_pair.cu).  Tiles read a halo of their input, so the step cannot run
+          // in place: lrelu(x) ping-pongs XL -> RL -> C1 -> (branch sum | next stage input).
+          const void* in = m == 0 ? buf(V_XL) : (m == 1 ? buf(V_RL) : buf(V_C1));
+          EpiParams e = epi();
+          e.resid = in; e.resid_ld = C; e.resid_inv = inv_slope;
+          if (m < 2) {
+            e.out0 = m == 0 ? buf(V_RL) : buf(V_C1); e.out0_ld = C; e.out0_slope = 0.1f;
+          } else if (j == 0) {
+            e.out0 = buf(V_SUM); e.out0_ld = C;
+          } else {
+            e.resid2 = buf(V_SUM); e.resid2_ld = C;
+            if (j == 1) { e.out0 = buf(V_SUM); e.out0_ld = C; }
+            else { e.scale = 1.f / 3.f; e.out0 = buf(V_A); e.out0_ld = C; e.out0_slope = i == 3 ? 0.01f : 0.1f; }
+          }
+          add(pair_op(W1, W2, kDils[m], in, C, B, len, e));
+          continue;
+        }
         {  // xt = lrelu(c1(lrelu(r)))   (models.py:92-94)
           EpiParams e = epi();
           e.out0 = buf(V_C1); e.out0_ld = C; e.out0_f32 = f32; e.out0_slope = 0.1f;
