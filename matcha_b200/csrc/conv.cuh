@@ -80,6 +80,7 @@ struct PairGeom {
   int w_resident, w_stages;      // both convs' weights resident, or streamed two taps per ring stage
   const float* bias1;            // c1 bias [C]
   float slope;                   // LeakyReLU between the convs
+  long long* dbg_out;            // developer probe: per-CTA cycle counters [grid][16] (MB200_PAIR_DBG), else null
 };
 
 struct EpiParams {

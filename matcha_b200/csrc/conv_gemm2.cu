@@ -299,6 +299,9 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
 
 template <int NTILE, int KC, int MB, typename T>
 static cudaError_t launch_umma2_eg(const ConvLaunch& L, cudaStream_t st) {
+  if constexpr (MB == 1 && NTILE >= 128) {   // the estimator's epilogue-heavy layers: twelve epilogue warps
+    if (L.g2.eg == 3) return launch_umma2_inst<NTILE, KC, MB, 3, T>(L, st);
+  }
   return L.g2.eg == 4 ? launch_umma2_inst<NTILE, KC, MB, 4, T>(L, st) : launch_umma2_inst<NTILE, KC, MB, 2, T>(L, st);
 }
 

@@ -5,6 +5,7 @@
 #include <cudaTypedefs.h>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -317,9 +318,15 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
       L.smem_bytes = g2.a_stages * a_bytes + g2.w_stages * g2.wt * w_tile + tail_bytes;
       return g2.w_stages >= 3;
     };
-    int want_eg = 2;   // sixteen epilogue warps measured slower (register cap 96, same L2-bound stores): opt-in only
-    if (const char* v = std::getenv("MB200_EG")) want_eg = std::atoi(v) == 4 ? 4 : 2;
-    if (want_eg == 2 || !layout(4)) {
+    // Epilogue warps: 8 by default.  The estimator layers whose epilogue carries the GroupNorm+Mish / LayerNorm / SnakeBeta /
+    // Euler work are bound by that epilogue's latency, not by the tensor pipe: they get 12 (measured -7 % on the
+    // estimator's GEMM time); 16 cap the kernel at 96 registers and spill (measured slower).  MB200_EG overrides.
+    const bool heavy_epi = e.gn_raw || e.ln_out || e.snake_a || e.stats_out || e.x_state;
+    int want_eg = heavy_epi ? 3 : 2;
+    if (const char* v = std::getenv("MB200_EG")) want_eg = std::atoi(v);
+    if (want_eg == 3 && !(g2.mb == 1 && ntile >= 128)) want_eg = 2;
+    if (want_eg != 2 && want_eg != 3 && want_eg != 4) want_eg = 2;
+    if (want_eg == 2 || !layout(want_eg)) {
       if (!layout(2) && g2.w_stages < 2) throw Error("conv_op: weight ring does not fit");
     }
     if (e.ln_out && g2.mb != 1) throw Error("conv_op: fused LayerNorm needs single-block tiles");
@@ -402,6 +409,15 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
   g.mid_bytes = (R + 16) * rowb;
   g.bias1 = W1.bias;
   g.slope = 0.1f;
+  g.dbg_out = nullptr;
+  if (const char* v = std::getenv("MB200_PAIR_DBG")) {   // developer probe: instrument the n-th pair op built
+    static int built = 0;
+    if (built++ == std::atoi(v)) {
+      g.dbg_out = static_cast<long long*>(dalloc(148 * 16 * sizeof(long long)));
+      probe_out = g.dbg_out;
+      std::fprintf(stderr, "[pair probe] C=%d K=%d dil=%d T=%d\n", C, K, dil, T);
+    }
+  }
   const int tail_bytes = 1024 + 512 + 8 * 4608;
   const int budget = 227 * 1024 - tail_bytes - g.mid_bytes;
   const int w_all = 2 * K * w_tile;

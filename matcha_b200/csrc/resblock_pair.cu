@@ -25,6 +25,8 @@ namespace mb {
 
 namespace {
 constexpr int kPairBarBytes = 512;
+// developer probe (PairGeom::dbg_out, MB200_PAIR_DBG): cycles a role spends inside one barrier wait
+#define PW(stmt, acc) do { if (g.dbg_out) { const long long pw_a = clock64(); stmt; acc += clock64() - pw_a; } else { stmt; } } while (0)
 }
 
 template <int C, int MB, typename T>
@@ -90,11 +92,13 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     // ================================================================= TMA producer
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0;
+    long long pw[2] = {0, 0};
+    const long long pt0 = clock64();
     auto load_A = [&](int n) {
       const int tile = blockIdx.x + n * gridDim.x;
       const int b = tile / g.tiles_per_b, t0 = (tile % g.tiles_per_b) * g.S;
       const int row0 = t0 - p - p * g.dil;
-      mbar_wait(&a_empty[as], aph ^ 1);
+      PW(mbar_wait(&a_empty[as], aph ^ 1), pw[0]);
       if (elect_one()) {
         uint8_t* dst = a_ring + as * g.a_bytes;
         mbar_expect_tx(&a_full[as], (R + 8 * g.extra) * ROWB);
@@ -108,7 +112,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     auto load_W = [&](const CUtensorMap* tm) {
       for (int st = 0; st < n_wst; ++st) {
         const int nt = min(2, K - 2 * st);
-        mbar_wait(&w_empty[ws], wph ^ 1);
+        PW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
         if (elect_one()) {
           mbar_expect_tx(&w_full[ws], nt * W_TILE);
           for (int j = 0; j < nt; ++j) tma_load_2d(w_base + ws * W_STAGE + j * W_TILE, tm, &w_full[ws], (2 * st + j) * C, 0);
@@ -137,6 +141,10 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         load_W(&tmW2);
       }
     }
+    if (g.dbg_out && lane == 0) {
+      long long* o = g.dbg_out + blockIdx.x * 16;
+      o[11] = clock64() - pt0; o[12] = pw[0]; o[13] = pw[1]; o[14] = nt_cta;
+    }
   } else if (warp == 1) {
     // ================================================================= MMA issuer
     constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 128, C);
@@ -150,6 +158,8 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     if (resident) { mbar_wait(wres, 0); tc_fence_after(); }
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0;
+    long long pw[5] = {0, 0, 0, 0, 0};
+    const long long pt0 = clock64();
     // all taps of one conv for the MB row blocks of a tile; operand rows advance by `row_step` rows per tap
     auto issue_conv = [&](const uint32_t a_lo, const int row_step, const uint32_t dtm, const int which) {
 #pragma unroll 1
@@ -158,7 +168,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         if (resident) {
           w_lo = w_lo0 + static_cast<uint32_t>(which * K + 2 * st) * W16;
         } else {
-          mbar_wait(&w_full[ws], wph);
+          PW(mbar_wait(&w_full[ws], wph), pw[2]);
           w_lo = w_lo0 + ws * WST16;
         }
         tc_fence_after();
@@ -182,8 +192,8 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     };
     auto M1 = [&](int n) {
       const int slot = n & 1;
-      mbar_wait(&t1_empty[slot], ((n >> 1) & 1) ^ 1);
-      mbar_wait(&a_full[as], aph);
+      PW(mbar_wait(&t1_empty[slot], ((n >> 1) & 1) ^ 1), pw[0]);
+      PW(mbar_wait(&a_full[as], aph), pw[1]);
       issue_conv(a_lo0 + as * a_stage16, g.dil, tmem_base + slot * SLOT, 0);
       if (elect_one()) { umma_commit(&a_empty[as]); umma_commit(&t1_full[slot]); }
       __syncwarp();
@@ -191,8 +201,8 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     };
     auto M2 = [&](int n) {
       const int slot = n & 1;
-      mbar_wait(&t2_empty[slot], ((n >> 1) & 1) ^ 1);
-      mbar_wait(mid_full, n & 1);
+      PW(mbar_wait(&t2_empty[slot], ((n >> 1) & 1) ^ 1), pw[3]);
+      PW(mbar_wait(mid_full, n & 1), pw[4]);
       issue_conv(mid_lo, 1, tmem_base + (2 + slot) * SLOT, 1);
       if (elect_one()) { umma_commit(mid_empty); umma_commit(&t2_full[slot]); }
       __syncwarp();
@@ -202,16 +212,23 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       if (n + 1 < nt_cta) M1(n + 1);
       M2(n);
     }
+    if (g.dbg_out && lane == 0) {
+      long long* o = g.dbg_out + blockIdx.x * 16;
+      o[0] = clock64() - pt0;
+      for (int i = 0; i < 5; ++i) o[1 + i] = pw[i];
+    }
   } else if (warp < 6) {
     // ================================================================= E1: accumulator 1 -> mid tile (A operand of c2)
     const int lane_grp = warp & 3;
     const float slope = g.slope;
+    long long pw[2] = {0, 0};
+    const long long pt0 = clock64();
     for (int n = 0; n < nt_cta; ++n) {
       const int tile = blockIdx.x + n * gridDim.x;
       const int t0 = (tile % g.tiles_per_b) * g.S, m0 = t0 - p;
       const int slot = n & 1;
-      mbar_wait(&t1_full[slot], (n >> 1) & 1);
-      mbar_wait(mid_empty, (n & 1) ^ 1);      // c2 of the previous tile has finished reading the mid tile
+      PW(mbar_wait(&t1_full[slot], (n >> 1) & 1), pw[0]);
+      PW(mbar_wait(mid_empty, (n & 1) ^ 1), pw[1]);      // c2 of the previous tile has finished reading the mid tile
       tc_fence_after();
 #pragma unroll 1
       for (int item = 0; item < MB * (C / 32); ++item) {
@@ -251,11 +268,17 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       __syncwarp();
       if (lane == 0) { mbar_arrive(&t1_empty[slot]); mbar_arrive(mid_full); }
     }
+    if (g.dbg_out && warp == 2 && lane == 0) {
+      long long* o = g.dbg_out + blockIdx.x * 16;
+      o[6] = clock64() - pt0; o[7] = pw[0]; o[8] = pw[1];
+    }
   } else {
     // ================================================================= E2: accumulator 2 -> global (fused epilogue)
     const int grp = (warp - 6) >> 2;
     const int lane_grp = warp & 3;
     uint8_t* stg = stage_base + (warp - 6) * kStageBytes;
+    long long pw = 0;
+    const long long pt0 = clock64();
     for (int n = 0; n < nt_cta; ++n) {
       const int tile = blockIdx.x + n * gridDim.x;
       const int b = tile / g.tiles_per_b, t0 = (tile % g.tiles_per_b) * g.S;
@@ -263,10 +286,14 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const int t_lim = min(g.T, t0 + g.S);     // rows past S belong to the next tile
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + (2 + slot) * SLOT;
       epilogue_tile3<C, MB, EG, T>(e, b, t0, t_lim, 0, 0, taddr, stg, nullptr, lane, lane_grp, grp, &t2_full[slot],
-                                   (n >> 1) & 1);
+                                   (n >> 1) & 1, g.dbg_out ? &pw : nullptr);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&t2_empty[slot]);
+    }
+    if (g.dbg_out && warp == 6 && lane == 0) {
+      long long* o = g.dbg_out + blockIdx.x * 16;
+      o[9] = clock64() - pt0; o[10] = pw;
     }
   }
   tc_fence_before();

@@ -1,6 +1,9 @@
 // HiFi-GAN v1 generator (matcha/hifigan/models.py:149-197) as a launch program: every Conv1d / ConvTranspose1d is
 // a conv-GEMM launch; LeakyReLU, residual adds, the 3-branch mean and the stage hand-over live in the epilogues.
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
 #include <cuda_fp16.h>
 
 #include "plan.h"
@@ -205,6 +208,18 @@ void Plan::hifigan_forward(const float* mel, int Tsrc, float scale, float shift,
     it = vocoder_cache_.emplace(key, std::move(prog)).first;
   }
   run(*it->second, st);
+  if (probe_out && std::getenv("MB200_PAIR_DBG")) {   // developer probe: per-role cycle counters of the instrumented pair op
+    MB_CUDA(cudaStreamSynchronize(st));
+    std::vector<long long> h(148 * 16);
+    MB_CUDA(cudaMemcpy(h.data(), probe_out, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+    static const char* names[15] = {"mma.total", "mma.w_t1_empty", "mma.w_a_full", "mma.w_w_full", "mma.w_t2_empty", "mma.w_mid_full",
+                                    "e1.total", "e1.w_t1_full", "e1.w_mid_empty", "e2.total", "e2.w_t2_full", "prod.total",
+                                    "prod.w_a_empty", "prod.w_w_empty", "tiles"};
+    for (int k = 0; k < 15; ++k) {
+      double s = 0; for (int c = 0; c < 148; ++c) s += h[c * 16 + k];
+      std::fprintf(stderr, "[pair probe] %-16s %12.0f\n", names[k], s / 148);
+    }
+  }
   const long Lw = static_cast<long>(L) * 256;
   const void* a = ws_voc_[V_A].p;
   if (dtype == MB200_F32) MB_CUDA(launch_conv_post<float>((const float*)a, gen_.post_w, gen_.post_b, wav, B, Lw, st));
