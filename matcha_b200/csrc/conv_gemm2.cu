@@ -204,18 +204,20 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
         if (elect_one()) {
           const uint32_t a0 = a_lo + (en0 & 0xffffu), a1 = a_lo + (en1 & 0xffffu);
           const uint32_t acc0 = s != 0;
+          // The weight tile is reused by every 128-row block of the tile; consecutive MMAs go to DIFFERENT accumulators
+          // (k outer, block inner): back-to-back accumulation into one TMEM tile stalls on the previous MMA at narrow N.
 #pragma unroll
-          for (int i = 0; i < MB; ++i) {   // the weight tile is reused by every 128-row block of the tile
+          for (int k = 0; k < KC / 16; ++k) {
 #pragma unroll
-            for (int k = 0; k < KC / 16; ++k)
+            for (int i = 0; i < MB; ++i)
               if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a0 + i * BLK16 + 2 * k, w_lo_0 + 2 * k, desc_hi, idesc, k == 0 ? acc0 : 1u);
           }
           if (!resident && (en0 & kSchedWLast)) umma_commit(&w_empty[ws]);
           if (two) {
 #pragma unroll
-            for (int i = 0; i < MB; ++i) {
+            for (int k = 0; k < KC / 16; ++k) {
 #pragma unroll
-              for (int k = 0; k < KC / 16; ++k)
+              for (int i = 0; i < MB; ++i)
                 if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a1 + i * BLK16 + 2 * k, w_lo_1 + 2 * k, desc_hi, idesc, 1u);
             }
             if (!resident && (en1 & kSchedWLast)) umma_commit(&w_empty[ws1]);
@@ -299,7 +301,7 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
 
 template <int NTILE, int KC, int MB, typename T>
 static cudaError_t launch_umma2_eg(const ConvLaunch& L, cudaStream_t st) {
-  if constexpr (MB == 1 && NTILE >= 128) {   // the estimator's epilogue-heavy layers: twelve epilogue warps
+  if constexpr (NTILE >= 128) {   // epilogue-bound layers: twelve epilogue warps
     if (L.g2.eg == 3) return launch_umma2_inst<NTILE, KC, MB, 3, T>(L, st);
   }
   return L.g2.eg == 4 ? launch_umma2_inst<NTILE, KC, MB, 4, T>(L, st) : launch_umma2_inst<NTILE, KC, MB, 2, T>(L, st);

@@ -324,7 +324,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     const bool heavy_epi = e.gn_raw || e.ln_out || e.snake_a || e.stats_out || e.x_state;
     int want_eg = heavy_epi ? 3 : 2;
     if (const char* v = std::getenv("MB200_EG")) want_eg = std::atoi(v);
-    if (want_eg == 3 && !(g2.mb == 1 && ntile >= 128)) want_eg = 2;
+    if (want_eg == 3 && ntile < 128) want_eg = 2;
     if (want_eg != 2 && want_eg != 3 && want_eg != 4) want_eg = 2;
     if (want_eg == 2 || !layout(want_eg)) {
       if (!layout(2) && g2.w_stages < 2) throw Error("conv_op: weight ring does not fit");

@@ -162,32 +162,38 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const long long pt0 = clock64();
     // all taps of one conv for the MB row blocks of a tile; operand rows advance by `row_step` rows per tap
     auto issue_conv = [&](const uint32_t a_lo, const int row_step, const uint32_t dtm, const int which) {
-#pragma unroll 1
-      for (int st = 0; st < n_wst; ++st) {
-        uint32_t w_lo;
-        if (resident) {
-          w_lo = w_lo0 + static_cast<uint32_t>(which * K + 2 * st) * W16;
-        } else {
-          PW(mbar_wait(&w_full[ws], wph), pw[2]);
-          w_lo = w_lo0 + ws * WST16;
+      // one tap for all MB row blocks; consecutive MMAs go to different accumulators (no back-to-back dependency)
+      auto tap_mmas = [&](const int tap, const uint32_t w) {
+        const uint32_t a = a_lo + static_cast<uint32_t>(tap * row_step) * ROW16;
+#pragma unroll
+        for (int k = 0; k < C / 16; ++k) {
+#pragma unroll
+          for (int i = 0; i < MB; ++i)
+            umma_f16_lohi(dtm + i * C, a + i * BLK16 + 2 * k, w + 2 * k, desc_hi, idesc, (tap | k) != 0 ? 1u : 0u);
         }
+      };
+      if (resident) {   // nothing to wait for: the whole conv is one elected issue block
         tc_fence_after();
         if (elect_one()) {
-          const int nt = min(2, K - 2 * st);
-          for (int j = 0; j < nt; ++j) {
-            const int tap = 2 * st + j;
-            const uint32_t a = a_lo + static_cast<uint32_t>(tap * row_step) * ROW16, w = w_lo + j * W16;
-#pragma unroll
-            for (int i = 0; i < MB; ++i) {
-#pragma unroll
-              for (int k = 0; k < C / 16; ++k)
-                umma_f16_lohi(dtm + i * C, a + i * BLK16 + 2 * k, w + 2 * k, desc_hi, idesc, (tap | k) != 0 ? 1u : 0u);
-            }
-          }
-          if (!resident) umma_commit(&w_empty[ws]);
+          const uint32_t w_lo = w_lo0 + static_cast<uint32_t>(which * K) * W16;
+#pragma unroll 1
+          for (int tap = 0; tap < K; ++tap) tap_mmas(tap, w_lo + tap * W16);
         }
         __syncwarp();
-        if (!resident) { if (++ws == g.w_stages) { ws = 0; wph ^= 1; } }
+        return;
+      }
+#pragma unroll 1
+      for (int st = 0; st < n_wst; ++st) {
+        PW(mbar_wait(&w_full[ws], wph), pw[2]);
+        const uint32_t w_lo = w_lo0 + ws * WST16;
+        tc_fence_after();
+        if (elect_one()) {
+          tap_mmas(2 * st, w_lo);
+          if (2 * st + 1 < K) tap_mmas(2 * st + 1, w_lo + W16);
+          umma_commit(&w_empty[ws]);
+        }
+        __syncwarp();
+        if (++ws == g.w_stages) { ws = 0; wph ^= 1; }
       }
     };
     auto M1 = [&](int n) {

@@ -135,6 +135,27 @@ def test_generator_matches_reference_golden(golden_dir, name, prec):
     check(plan.hifigan_forward(fx["mel"]), fx["wav"], prec)  # graph replay
 
 
+@pytest.mark.parametrize("prec", ["fp16", "bf16"])
+@pytest.mark.parametrize("B,L", [(3, 1), (2, 13), (1, 40)])
+def test_fused_resblock_step_is_bit_identical_to_two_conv_launches(monkeypatch, prec, B, L):
+    """Stages 3-4 run every ResBlock step (hifigan/models.py:90-97) as one kernel that keeps c1's output in shared
+    memory (resblock_pair.cu).  Same arithmetic, same roundings as the two-launch form: the waveforms must be EQUAL.
+    Sizes cover a single partial tile (L=1: 128 / 256 rows), tile edges inside an utterance and several utterances."""
+    sd = weights.generator_state_dict(7, weight_norm=False)
+    mel = torch.randn(B, 80, L, generator=torch.Generator().manual_seed(11)) * 1.5 - 4.0
+    out = {}
+    for fuse in ("1", "0"):
+        monkeypatch.setenv("MB200_FUSE_PAIRS", fuse)
+        plan = Plan(prec, 160, use_graph=False)
+        plan.load_generator(sd)
+        out[fuse] = plan.hifigan_forward(mel).cpu()
+    assert out["1"].shape == (B, 1, 256 * L)
+    assert torch.isfinite(out["1"]).all()
+    assert torch.equal(out["1"], out["0"])
+    if L <= 13 and prec == "fp16":   # and the CPU oracle on the same seeded input (seconds at these sizes)
+        check(out["1"], mo.hifigan_forward(sd, mel), prec)
+
+
 # ------------------------------------------------------------------------------------------ oracle, seeded inputs
 @pytest.mark.parametrize("prec", ["fp32", "fp16"])
 @pytest.mark.parametrize("c_in", [160, 224])
