@@ -251,7 +251,8 @@ def run_ours(args):
             traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
         except (OSError, KeyError, ValueError):
             pass
-        roofline = {"bound": "tensor", "kernel": "conv_gemm_umma2_kernel (all instantiations)", "achieved": achieved,
+        roofline = {"bound": "tensor", "achieved": achieved,
+                    "kernel": "tcgen05 conv-GEMM family: conv_gemm_umma2_kernel + resblock_pair_kernel (all instantiations)",
                     "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": traffic,
                     "traffic_unit": "bytes/launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_src,
                     "peak_source": peaks["source"], "launches_per_step": g_n, "avg_launch_us": g_ms * 1e3 / max(g_n, 1),
