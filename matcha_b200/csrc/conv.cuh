@@ -76,7 +76,7 @@ struct PairGeom {
   int tiles_per_b, total_tiles;
   int extra;                     // 8-row halo boxes after the first 128*mb rows of the input tile
   int a_stages, a_bytes;         // input ring
-  int mid_bytes;                 // intermediate tile (128*mb + 16 rows)
+  int mid_bytes, mid_stages;     // intermediate tile (128*mb + 16 rows), single or double buffered
   int w_resident, w_stages;      // both convs' weights resident, or streamed two taps per ring stage
   const float* bias1;            // c1 bias [C]
   float slope;                   // LeakyReLU between the convs

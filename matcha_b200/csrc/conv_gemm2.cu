@@ -32,7 +32,7 @@ namespace mb {
 constexpr int kMaxRing = 8;
 constexpr int kBarBytes = 512;   // mbarriers + TMEM slot
 
-template <int NTILE, int KC, int MB, int EG, typename T>
+template <int NTILE, int KC, int MB, int EG, typename T, uint32_t F>
 __global__ void __launch_bounds__(64 + 128 * EG, 1)
 conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                        const __grid_constant__ CUtensorMap tmA0x, const __grid_constant__ CUtensorMap tmA1x,
@@ -253,11 +253,11 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       if (MB_DBG(8)) {
         MB_WAIT(mbar_wait(&t_full[slot], tph));
       } else {
-        epilogue_tile3<NTILE, MB, EG, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
+        epilogue_tile3<NTILE, MB, EG, T, F>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
                                  lane_grp, grp, &t_full[slot], tph, &probe_w);
       }
 #else
-      epilogue_tile3<NTILE, MB, EG, T>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
+      epilogue_tile3<NTILE, MB, EG, T, F>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
                                lane_grp, grp, &t_full[slot], tph);
 #endif
       tc_fence_before();
@@ -276,9 +276,9 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-template <int NTILE, int KC, int MB, int EG, typename T>
+template <int NTILE, int KC, int MB, int EG, typename T, uint32_t F>
 static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
-  auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, EG, T>;
+  auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, EG, T, F>;
   static int configured = 0;
   if (configured < L.smem_bytes) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -299,12 +299,24 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
   return cudaLaunchKernelEx(&cfg, kern, L.tmA[0], L.tmA[two ? 1 : 0], L.tmA8[0], L.tmA8[two ? 1 : 0], L.tmW, L.g2, L.e);
 }
 
+// Picks the leanest instantiated epilogue feature class (epilogue3.cuh) that covers what this launch asks for.
+template <int NTILE, int KC, int MB, int EG, typename T>
+static cudaError_t launch_umma2_feat(const ConvLaunch& L, cudaStream_t st) {
+  const uint32_t need = epi_features(L.e);
+#define MB_TRY(CLS) if ((need & ~(CLS)) == 0) return launch_umma2_inst<NTILE, KC, MB, EG, T, (CLS)>(L, st)
+  if constexpr (NTILE == 256 && MB == 1 && EG == 3) { MB_TRY(kFC_STATS); MB_TRY(kFC_SNAKE); MB_TRY(kFC_RESLN); MB_TRY(kFC_GNLN); }
+  if constexpr (EG == 2) { MB_TRY(kFC_VOC); }
+  if constexpr (NTILE == 256 && MB == 1 && EG == 2) { MB_TRY(kFC_RESMASK); }
+#undef MB_TRY
+  return launch_umma2_inst<NTILE, KC, MB, EG, T, kF_ALL>(L, st);
+}
+
 template <int NTILE, int KC, int MB, typename T>
 static cudaError_t launch_umma2_eg(const ConvLaunch& L, cudaStream_t st) {
-  if constexpr (NTILE >= 128) {   // epilogue-bound layers: twelve epilogue warps
-    if (L.g2.eg == 3) return launch_umma2_inst<NTILE, KC, MB, 3, T>(L, st);
+  if constexpr (MB == 1 && NTILE >= 128) {   // epilogue-bound estimator layers: twelve epilogue warps
+    if (L.g2.eg == 3) return launch_umma2_feat<NTILE, KC, MB, 3, T>(L, st);
   }
-  return L.g2.eg == 4 ? launch_umma2_inst<NTILE, KC, MB, 4, T>(L, st) : launch_umma2_inst<NTILE, KC, MB, 2, T>(L, st);
+  return launch_umma2_feat<NTILE, KC, MB, 2, T>(L, st);
 }
 
 template <typename T>

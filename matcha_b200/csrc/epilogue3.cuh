@@ -17,6 +17,38 @@
 
 namespace mb {
 
+// Compile-time feature classes.  The epilogue is one function with every fusion the path needs; a launch only uses a
+// few of them, and the tests on the others (parameter loads, uniform branches, live registers) cost ~40 % of the
+// instructions of this latency-bound code.  F is a SUPERSET of what the launch's EpiParams may ask for: features outside
+// F are compiled out, features inside F are still tested at run time.  kF_ALL is the fully generic epilogue.
+constexpr uint32_t kF_GN = 1u, kF_RESID = 2u, kF_RESID2 = 4u, kF_SNAKE = 8u, kF_MASK = 16u, kF_STATS = 32u, kF_XSTATE = 64u,
+                   kF_LN = 128u, kF_OUT1 = 256u, kF_SCALE = 512u, kF_F32 = 1024u, kF_SLOPE = 2048u;
+constexpr uint32_t kF_NOFAST = 4096u;   // the packed-half path is known not to apply (estimator layers)
+constexpr uint32_t kF_ALL = 0xfffu;
+// classes the launchers instantiate
+constexpr uint32_t kFC_STATS = kF_STATS | kF_NOFAST;                       // Block1D convs: bias + GroupNorm partial sums
+constexpr uint32_t kFC_GNLN = kF_GN | kF_MASK | kF_LN | kF_NOFAST;         // res_conv + mish(GN(raw)) + LayerNorm
+constexpr uint32_t kFC_RESLN = kF_RESID | kF_LN | kF_NOFAST;               // attention out-projection + residual + LayerNorm
+constexpr uint32_t kFC_SNAKE = kF_SNAKE | kF_NOFAST;                       // feed-forward up projection + SnakeBeta
+constexpr uint32_t kFC_RESMASK = kF_RESID | kF_MASK | kF_NOFAST;           // feed-forward down projection, masked convs
+constexpr uint32_t kFC_VOC = kF_RESID | kF_RESID2 | kF_SCALE | kF_SLOPE | kF_OUT1;   // every HiFi-GAN conv (packed-half path in f16)
+__host__ inline uint32_t epi_features(const EpiParams& e) {
+  uint32_t f = 0;
+  if (e.gn_raw) f |= kF_GN;
+  if (e.resid) f |= kF_RESID;
+  if (e.resid2) f |= kF_RESID2;
+  if (e.snake_a) f |= kF_SNAKE;
+  if (e.mask || e.mask_out) f |= kF_MASK;
+  if (e.stats_out) f |= kF_STATS;
+  if (e.x_state) f |= kF_XSTATE;
+  if (e.ln_out) f |= kF_LN;
+  if (e.out1) f |= kF_OUT1 | kF_SLOPE;
+  if (e.scale != 1.f) f |= kF_SCALE;
+  if (e.out0_f32 || e.resid_f32 || e.resid2_f32) f |= kF_F32;
+  if (e.out0_slope != 1.f) f |= kF_SLOPE;
+  return f;
+}
+
 constexpr int kStagePitch = 144;                 // bytes per staged row: 32 fp32 + 16 B pad
 constexpr int kStageBytes = 32 * kStagePitch;    // per epilogue warp
 constexpr int kLnXBytes = 2 * 4 * 128 * 8;        // [tile parity][group <= 4][row] partial LayerNorm sums (float2)
@@ -88,14 +120,28 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 // The profile of this function is flat and latency-bound (two epilogue warps per scheduler), so the code is organised
 // to keep the instruction count per 32x32 item low: options are tested once per item (feature-major, row-minor loops),
 // row offsets are 32-bit element indices computed once, and memory operations are predicated rather than branched.
-template <int NTILE, int MB, int EG, typename T>
-__device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, const int t0, const int T_out,
+template <int NTILE, int MB, int EG, typename T, uint32_t F = kF_ALL>
+__device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b, const int t0, const int T_out,
                                                const int phase, const int nbase, const uint32_t tmem_tile,
                                                uint8_t* stg, float2* lnx, const int lane, const int lane_grp,
                                                const int grp, uint64_t* t_full, const uint32_t t_parity,
                                                long long* probe_wait = nullptr) {
   constexpr int NP = NTILE / 32;            // 32-column blocks per 128-row block
   constexpr int ITEMS = MB * NP;
+  // masked copy of the parameters: everything outside the feature class F is a compile-time constant from here on
+  EpiParams e = ep;
+  if constexpr (!(F & kF_GN)) e.gn_raw = nullptr;
+  if constexpr (!(F & kF_RESID)) e.resid = nullptr;
+  if constexpr (!(F & kF_RESID2)) e.resid2 = nullptr;
+  if constexpr (!(F & kF_SNAKE)) e.snake_a = nullptr;
+  if constexpr (!(F & kF_MASK)) { e.mask = nullptr; e.mask_out = 0; }
+  if constexpr (!(F & kF_STATS)) e.stats_out = nullptr;
+  if constexpr (!(F & kF_XSTATE)) e.x_state = nullptr;
+  if constexpr (!(F & kF_LN)) e.ln_out = nullptr;
+  if constexpr (!(F & kF_OUT1)) e.out1 = nullptr;
+  if constexpr (!(F & kF_SCALE)) e.scale = 1.f;
+  if constexpr (!(F & kF_F32)) { e.out0_f32 = 0; e.resid_f32 = 0; e.resid2_f32 = 0; }
+  if constexpr (!(F & kF_SLOPE)) e.out0_slope = 1.f;
   const int p = lane & 3, rq = lane >> 2;
   const int row_base = b * e.T_o + phase * e.o_phase_step;   // tensors on this path stay below 2^31 elements
   const int tw0 = t0 + lane_grp * 32 + rq;  // this lane's first row of block 0
@@ -132,7 +178,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
   // fp16 layers whose epilogue is only bias / residuals / scale / LeakyReLU (every HiFi-GAN conv) finish in packed half
   // arithmetic: a third of the instructions of the general fp32 path; the extra roundings are fp16 ulps of values that
   // are stored as fp16 anyway.  bf16 keeps the fp32 path.
-  const bool fast = std::is_same<T, __half>::value && !e.gn_raw && !e.snake_a && !e.mask && !e.mask_out && !e.stats_out &&
+  const bool fast = !(F & kF_NOFAST) && std::is_same<T, __half>::value && !e.gn_raw && !e.snake_a && !e.mask && !e.mask_out && !e.stats_out &&
                     !e.x_state && !do_ln && !e.out0_f32 && !e.resid_f32 && !e.resid2_f32;
   float ln_s[4] = {0.f, 0.f, 0.f, 0.f}, ln_ss[4] = {0.f, 0.f, 0.f, 0.f};
 
@@ -247,13 +293,16 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& e, const int b, 
           __half* op = reinterpret_cast<__half*>(e.out0);
           const int ld = e.out0_ld;
           const __half2 sl = __float2half2_rn(e.out0_slope);
+          const bool plain = e.out0_slope == 1.f;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            uint4 ou;
-            __half2* o = reinterpret_cast<__half2*>(&ou);
-            const __half2* h = reinterpret_cast<const __half2*>(&hu[k]);
+            uint4 ou = hu[k];
+            if (!plain) {
+              __half2* o = reinterpret_cast<__half2*>(&ou);
+              const __half2* h = reinterpret_cast<const __half2*>(&hu[k]);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], sl));
+              for (int j = 0; j < 4; ++j) o[j] = __hmax2(h[j], __hmul2(h[j], sl));
+            }
             if (ok[k]) *reinterpret_cast<uint4*>(op + static_cast<size_t>(grow[k]) * ld + n0) = ou;
           }
         }

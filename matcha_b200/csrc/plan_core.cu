@@ -320,12 +320,11 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     };
     // Epilogue warps: 8 by default.  The estimator layers whose epilogue carries the GroupNorm+Mish / LayerNorm / SnakeBeta /
     // Euler work are bound by that epilogue's latency, not by the tensor pipe: they get 12 (measured -7 % on the
-    // estimator's GEMM time); 16 cap the kernel at 96 registers and spill (measured slower).  MB200_EG overrides.
+    // estimator's GEMM time); 16 capped the kernel at 96 registers and spilled (measured slower, removed).  MB200_EG=2|3 overrides.
     const bool heavy_epi = e.gn_raw || e.ln_out || e.snake_a || e.stats_out || e.x_state;
     int want_eg = heavy_epi ? 3 : 2;
-    if (const char* v = std::getenv("MB200_EG")) want_eg = std::atoi(v);
-    if (want_eg == 3 && ntile < 128) want_eg = 2;
-    if (want_eg != 2 && want_eg != 3 && want_eg != 4) want_eg = 2;
+    if (const char* v = std::getenv("MB200_EG")) want_eg = std::atoi(v) == 3 ? 3 : 2;
+    if (want_eg == 3 && !(g2.mb == 1 && ntile >= 128)) want_eg = 2;
     if (want_eg == 2 || !layout(want_eg)) {
       if (!layout(2) && g2.w_stages < 2) throw Error("conv_op: weight ring does not fit");
     }
@@ -405,7 +404,7 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
   g.total_tiles = B * g.tiles_per_b;
   g.extra = ((K - 1) * dil + 7) / 8;
   if (g.extra > 8) throw Error("pair_op: tap span exceeds the halo capacity");
-  g.a_bytes = (R + 64) * rowb;
+  g.a_bytes = ((R + 8 * g.extra) * rowb + 1023) / 1024 * 1024;
   g.mid_bytes = (R + 16) * rowb;
   g.bias1 = W1.bias;
   g.slope = 0.1f;
@@ -418,19 +417,30 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
       std::fprintf(stderr, "[pair probe] C=%d K=%d dil=%d T=%d\n", C, K, dil, T);
     }
   }
+  // shared memory: x ring | mid tile(s) | weights (resident, or a ring of two-tap stages) | barriers + E2 staging.
+  // The mid tile is double-buffered when that still leaves two x stages and a usable weight ring: E1 of tile n+1 then
+  // overlaps c2 of tile n (the short-kernel steps are bound by that chain).
   const int tail_bytes = 1024 + 512 + 8 * 4608;
-  const int budget = 227 * 1024 - tail_bytes - g.mid_bytes;
   const int w_all = 2 * K * w_tile;
-  if ((budget - w_all) / g.a_bytes >= 2) {
-    g.w_resident = 1; g.w_stages = 0;
-    g.a_stages = std::min(4, (budget - w_all) / g.a_bytes);
-    L.smem_bytes = g.a_stages * g.a_bytes + g.mid_bytes + w_all + tail_bytes;
-  } else {
-    g.w_resident = 0; g.a_stages = 2;
-    g.w_stages = std::min(8, (budget - 2 * g.a_bytes) / (2 * w_tile));
-    if (g.w_stages < 3) throw Error("pair_op: weight ring does not fit");
-    L.smem_bytes = 2 * g.a_bytes + g.mid_bytes + g.w_stages * 2 * w_tile + tail_bytes;
+  int want_mid = 2;
+  if (const char* v = std::getenv("MB200_PAIR_MID")) want_mid = std::atoi(v) == 1 ? 1 : 2;
+  bool placed = false;
+  for (int ms = want_mid; ms >= 1 && !placed; --ms) {
+    const int budget = 227 * 1024 - tail_bytes - ms * g.mid_bytes;
+    g.mid_stages = ms;
+    if ((budget - w_all) / g.a_bytes >= 2) {
+      g.w_resident = 1; g.w_stages = 0;
+      g.a_stages = std::min(4, (budget - w_all) / g.a_bytes);
+      L.smem_bytes = g.a_stages * g.a_bytes + ms * g.mid_bytes + w_all + tail_bytes;
+      placed = true;
+    } else {
+      g.w_resident = 0; g.a_stages = 2;
+      g.w_stages = std::min(8, (budget - 2 * g.a_bytes) / (2 * w_tile));
+      L.smem_bytes = 2 * g.a_bytes + ms * g.mid_bytes + g.w_stages * 2 * w_tile + tail_bytes;
+      placed = g.w_stages >= 3;
+    }
   }
+  if (!placed) throw Error("pair_op: weight ring does not fit");
   e.o_mul = 1; e.o_phase_step = 1; e.T_o = T; e.n_valid = C; e.bias = W2.bias;
   L.e = e;
   L.tmA = tmap_act(in, C, T, B, C);

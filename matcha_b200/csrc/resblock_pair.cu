@@ -49,7 +49,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const int n_wst = (K + 1) / 2;          // ring stages per conv when the weights are streamed
   uint8_t* a_ring = smem;
   uint8_t* mid = a_ring + g.a_stages * g.a_bytes;
-  uint8_t* w_base = mid + g.mid_bytes;
+  uint8_t* w_base = mid + g.mid_stages * g.mid_bytes;
   const int w_bytes = g.w_resident ? 2 * K * W_TILE : g.w_stages * W_STAGE;
   uint8_t* tail = w_base + w_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
@@ -61,9 +61,9 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint64_t* t1_empty = t1_full + 2;   // [2]
   uint64_t* t2_full = t1_empty + 2;   // [2]
   uint64_t* t2_empty = t2_full + 2;   // [2]
-  uint64_t* mid_full = t2_empty + 2;
-  uint64_t* mid_empty = mid_full + 1;
-  uint64_t* wres = mid_empty + 1;
+  uint64_t* mid_full = t2_empty + 2;  // [2]
+  uint64_t* mid_empty = mid_full + 2; // [2]
+  uint64_t* wres = mid_empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres + 1);
   uint8_t* stage_base = tail + kPairBarBytes;
 
@@ -79,7 +79,8 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], 4);
       mbar_init(&t2_full[s], 1); mbar_init(&t2_empty[s], 4 * EG);
     }
-    mbar_init(mid_full, 4); mbar_init(mid_empty, 1); mbar_init(wres, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&mid_full[s], 4); mbar_init(&mid_empty[s], 1); }
+    mbar_init(wres, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(tmem_slot);
@@ -208,9 +209,12 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     auto M2 = [&](int n) {
       const int slot = n & 1;
       PW(mbar_wait(&t2_empty[slot], ((n >> 1) & 1) ^ 1), pw[3]);
-      PW(mbar_wait(mid_full, n & 1), pw[4]);
-      issue_conv(mid_lo, 1, tmem_base + (2 + slot) * SLOT, 1);
-      if (elect_one()) { umma_commit(mid_empty); umma_commit(&t2_full[slot]); }
+      // mid tiles: ring of g.mid_stages (2 when shared memory allows: E1 of the next tile then overlaps this c2)
+      const int ms = g.mid_stages == 2 ? slot : 0;
+      const uint32_t mpar = g.mid_stages == 2 ? ((n >> 1) & 1) : (n & 1);
+      PW(mbar_wait(&mid_full[ms], mpar), pw[4]);
+      issue_conv(mid_lo + ms * (static_cast<uint32_t>(g.mid_bytes) >> 4), 1, tmem_base + (2 + slot) * SLOT, 1);
+      if (elect_one()) { umma_commit(&mid_empty[ms]); umma_commit(&t2_full[slot]); }
       __syncwarp();
     };
     if (nt_cta > 0) M1(0);
@@ -229,28 +233,36 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const float slope = g.slope;
     long long pw[2] = {0, 0};
     const long long pt0 = clock64();
+    constexpr int ITEMS = MB * (C / 32);
     for (int n = 0; n < nt_cta; ++n) {
       const int tile = blockIdx.x + n * gridDim.x;
       const int t0 = (tile % g.tiles_per_b) * g.S, m0 = t0 - p;
       const int slot = n & 1;
+      const int ms = g.mid_stages == 2 ? slot : 0;
+      uint8_t* mid_t = mid + ms * g.mid_bytes;
+      const uint32_t tbase = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * SLOT;
       PW(mbar_wait(&t1_full[slot], (n >> 1) & 1), pw[0]);
-      PW(mbar_wait(mid_empty, (n & 1) ^ 1), pw[1]);      // c2 of the previous tile has finished reading the mid tile
       tc_fence_after();
-#pragma unroll 1
-      for (int item = 0; item < MB * (C / 32); ++item) {
+      // accumulator loads run one item ahead of the arithmetic: item+1 is in flight while item is converted and stored
+      float acc[2][32];
+      tmem_ld_32x32(tbase, acc[0]);
+      // the mid tile is free once the c2 that read it has completed
+      PW(mbar_wait(&mid_empty[ms], (g.mid_stages == 2 ? ((n >> 1) & 1) : (n & 1)) ^ 1), pw[1]);
+#pragma unroll
+      for (int item = 0; item < ITEMS; ++item) {
         const int i = item / (C / 32), c = item % (C / 32);
         const int r = i * 128 + lane_grp * 32 + lane;   // row of the mid tile held by this lane
         const int m = m0 + r;
         const bool live = (m >= 0) && (m < g.T);        // c2 zero-pads its INPUT: rows outside the utterance are 0
-        float acc[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * SLOT + i * C + c * 32, acc);
         tmem_ld_wait();
+        if (item + 1 < ITEMS) tmem_ld_32x32(tbase + ((item + 1) / (C / 32)) * C + ((item + 1) % (C / 32)) * 32, acc[(item + 1) & 1]);
+        const float* a = acc[item & 1];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           float bv[8], v[8];
           ldg8f(g.bias1 + c * 32 + 8 * q, bv);
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) v[ch] = acc[8 * q + ch] + bv[ch];
+          for (int ch = 0; ch < 8; ++ch) v[ch] = a[8 * q + ch] + bv[ch];
           uint4 o;
           if constexpr (std::is_same<T, __half>::value) {   // same arithmetic as the unfused fp16 epilogue
             o = pack8<__half>(v);
@@ -266,13 +278,13 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           if (!live) o = make_uint4(0, 0, 0, 0);
           uint32_t off = static_cast<uint32_t>(r * ROWB + (c * 4 + q) * 16);
           off ^= ((off >> 7) & SWZ) << 4;
-          *reinterpret_cast<uint4*>(mid + off) = o;
+          *reinterpret_cast<uint4*>(mid_t + off) = o;
         }
       }
       tc_fence_before();
       fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async-proxy reads
       __syncwarp();
-      if (lane == 0) { mbar_arrive(&t1_empty[slot]); mbar_arrive(mid_full); }
+      if (lane == 0) { mbar_arrive(&t1_empty[slot]); mbar_arrive(&mid_full[ms]); }
     }
     if (g.dbg_out && warp == 2 && lane == 0) {
       long long* o = g.dbg_out + blockIdx.x * 16;
@@ -291,7 +303,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const int slot = n & 1;
       const int t_lim = min(g.T, t0 + g.S);     // rows past S belong to the next tile
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + (2 + slot) * SLOT;
-      epilogue_tile3<C, MB, EG, T>(e, b, t0, t_lim, 0, 0, taddr, stg, nullptr, lane, lane_grp, grp, &t2_full[slot],
+      epilogue_tile3<C, MB, EG, T, kFC_VOC>(e, b, t0, t_lim, 0, 0, taddr, stg, nullptr, lane, lane_grp, grp, &t2_full[slot],
                                    (n >> 1) & 1, g.dbg_out ? &pw : nullptr);
       tc_fence_before();
       __syncwarp();
