@@ -75,6 +75,27 @@ int mb200_synthesise(mb200_plan* plan, const float* mu, const float* mask, const
 int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
                           int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out);
 
+/* One estimator parameter for the training entry point: DEVICE fp32 tensors in the reference layout (SURVEY.md
+ * Appendix A), `grad` may be NULL (that gradient is then not computed). */
+typedef struct {
+  const char* name;
+  const float* param;
+  float* grad;
+} mb200_param;
+
+/* BASECFM.compute_loss(x1, mask, mu, spks) (matcha/models/components/flow_matching.py:87-118) with the random draws
+ * injected: t (B,) ~ U(0,1) and z (B,80,T) ~ N(0,1) are device inputs.  Computes y = (1-(1-sigma_min) t) z + t x1,
+ * u = x1 - (1-sigma_min) z, v = Decoder.forward(y, mask, mu, t, spks) (decoder.py:363-443, per-sample t) and
+ * loss = sum((v-u)^2) / (sum(mask) * 80).  With backward != 0 the whole estimator backward pass runs as well:
+ * d loss / d parameter is ACCUMULATED (+=) into every non-NULL `grad` (zero-fill them for plain gradients),
+ * d loss / d mu -> dmu (B,80,T) and d loss / d spks -> dspks (B, c_in-160), both optional (NULL = skip).
+ * Parameters are read in place (no repacking between optimiser steps).  fp32 FFMA kernels in every plan dtype.
+ * loss: device scalar; y, v: optional (B,80,T) outputs.  `prefix` is stripped from parameter names. */
+int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
+                       const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
+                       float sigma_min, int backward, float* loss, float* y, float* v, float* dmu, float* dspks,
+                       void* stream);
+
 /* Bookkeeping for the benchmark: kernels launched (or replayed inside graphs) by this plan since creation. */
 long long mb200_launch_count(const mb200_plan* plan);
 /* Device-memory footprint of the plan's workspaces and weights, bytes. */

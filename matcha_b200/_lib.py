@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention",
+    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention",
 ]
 
 
@@ -30,6 +30,10 @@ class Cfg(ctypes.Structure):
 class Tensor(ctypes.Structure):
     _fields_ = [("name", ctypes.c_char_p), ("data", ctypes.c_void_p), ("ndim", ctypes.c_int),
                 ("shape", ctypes.c_longlong * 4)]
+
+
+class Param(ctypes.Structure):
+    _fields_ = [("name", ctypes.c_char_p), ("param", ctypes.c_void_p), ("grad", ctypes.c_void_p)]
 
 
 _lib = None
@@ -61,6 +65,8 @@ def load():
         lib.mb200_hifigan_forward.argtypes = [vp, vp, i, i, vp, vp]
         lib.mb200_synthesise.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp, vp, vp]
         lib.mb200_synthesise_host.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp]
+        lib.mb200_compute_loss.argtypes = [vp, ctypes.POINTER(Param), i, ctypes.c_char_p, vp, vp, vp, vp, vp, vp, i, i, f, i,
+                                           vp, vp, vp, vp, vp, vp]
         lib.mb200_launch_count.argtypes = [vp]
         lib.mb200_launch_count.restype = ctypes.c_longlong
         lib.mb200_workspace_bytes.argtypes = [vp]
@@ -215,6 +221,43 @@ class Plan:
                                                  int(n_steps), int(length), float(mel_mean), float(mel_std),
                                                  _ptr(mel_out), _ptr(wav_out)))
         return mel_out, wav_out
+
+    def compute_loss(self, named_params, x1, mask, mu, z, t, spks=None, sigma_min=1e-4, backward=True, want_dmu=False,
+                     want_dspks=False):
+        """BASECFM.compute_loss forward (+ backward) with injected draws t (B,), z (B,80,T).
+
+        named_params: iterable of (name, tensor) -- the estimator's parameters, CUDA fp32 contiguous, reference names
+        (SURVEY.md Appendix A).  Returns dict(loss, y, v, grads {name: tensor}, dmu, dspks); gradients are fresh
+        zero-initialised tensors filled by the CUDA backward pass (flow_matching.py:87-118 under autograd)."""
+        b, c, tt = x1.shape
+        x1, mask, mu, z, spks = (_dev_f32(v, self.device) for v in (x1, mask, mu, z, spks))
+        t = _dev_f32(t, self.device).reshape(-1)
+        if t.numel() != b:
+            raise ValueError("t must have one value per batch element")
+        named = [(k, v) for k, v in named_params]
+        for k, v in named:
+            if not v.is_cuda or v.dtype != torch.float32 or not v.is_contiguous():
+                raise ValueError(f"parameter {k} must be a contiguous fp32 CUDA tensor (the kernels read it in place)")
+        grads = {k: torch.zeros_like(v) for k, v in named} if backward else {}
+        arr = (Param * len(named))()
+        keep = []
+        for j, (k, v) in enumerate(named):
+            name = k.encode()
+            keep.append(name)
+            arr[j].name = name
+            arr[j].param = v.data_ptr()
+            arr[j].grad = grads[k].data_ptr() if backward else None
+        loss = torch.zeros((), device=self.device, dtype=torch.float32)
+        y = torch.empty(b, 80, tt, device=self.device, dtype=torch.float32)
+        v_out = torch.empty(b, 80, tt, device=self.device, dtype=torch.float32)
+        dmu = torch.empty(b, 80, tt, device=self.device, dtype=torch.float32) if backward and want_dmu else None
+        dspks = torch.empty_like(spks) if backward and want_dspks and spks is not None else None
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_compute_loss(self.handle, arr, len(named), b"", _ptr(x1), _ptr(mask), _ptr(mu), _ptr(z),
+                                              _ptr(t), _ptr(spks), b, tt, float(sigma_min), int(backward), _ptr(loss),
+                                              _ptr(y), _ptr(v_out), _ptr(dmu), _ptr(dspks), _stream()))
+        del keep
+        return {"loss": loss, "y": y, "v": v_out, "grads": grads, "dmu": dmu, "dspks": dspks}
 
     def set_profiling(self, on):
         check(self.lib.mb200_set_profiling(self.handle, int(on)))

@@ -159,6 +159,16 @@ class Decoder(nn.Module):
             self._plans[precision] = p
         return self._plans[precision]
 
+    def train_plan(self):
+        """The plan the training path runs on.  compute_loss reads the module's parameters in place (no packed copy), so
+        one plan serves every optimiser step."""
+        if getattr(self, "_train_plan", None) is None:
+            dev = next(self.parameters()).device
+            if dev.type != "cuda":
+                raise RuntimeError("matcha_b200.Decoder runs on CUDA only: move the module to a B200 (no CPU fallback)")
+            self._train_plan = _lib.Plan("fp32", self.in_channels, device=dev)
+        return self._train_plan
+
     @torch.no_grad()
     def forward(self, x, mask, mu, t, spks=None, cond=None):
         """decoder.py:363: x, mu (B,80,T); mask (B,1,T); t () or (B,); spks (B,64) or None -> (B,80,T)."""
@@ -197,17 +207,46 @@ class BASECFM(nn.Module):
                 dt = t_span[step + 1] - t
         return x
 
-    def compute_loss(self, x1, mask, mu, spks=None, cond=None):
-        """flow_matching.py:87-118, forward value only: the estimator backward is not built yet, so the returned
-        loss carries no autograd graph."""
+    def compute_loss(self, x1, mask, mu, spks=None, cond=None, t=None, z=None):
+        """flow_matching.py:87-118.  Same draws as the reference (`torch.rand([b,1,1])` then `torch.randn_like(x1)`, unless
+        t / z are injected for parity tests); y, u, the estimator forward with per-sample t, the loss AND the estimator's
+        whole backward pass run in CUDA (csrc/train.cu).  The returned loss is an autograd node: `loss.backward()`
+        delivers the CUDA-computed gradients to the estimator's parameters, to `mu` (the encoder side) and to `spks`."""
         b = mu.shape[0]
-        t = torch.rand([b, 1, 1], device=mu.device, dtype=mu.dtype)
-        z = torch.randn_like(x1)
-        y = (1 - (1 - self.sigma_min) * t) * z + t * x1
-        u = x1 - (1 - self.sigma_min) * z
-        v = self.estimator(y, mask, mu, t.squeeze(), spks)
-        loss = torch.nn.functional.mse_loss(v, u, reduction="sum") / (torch.sum(mask) * u.shape[1])
+        if t is None:
+            t = torch.rand([b, 1, 1], device=mu.device, dtype=mu.dtype)
+        if z is None:
+            z = torch.randn_like(x1)
+        names = [k for k, _ in self.estimator.named_parameters()]
+        params = [p for _, p in self.estimator.named_parameters()]
+        loss, y = _ComputeLoss.apply(self.estimator, names, float(self.sigma_min), x1, mask, mu, spks, t, z, *params)
         return loss, y
+
+
+class _ComputeLoss(torch.autograd.Function):
+    """Bridges the CUDA forward+backward of compute_loss into autograd: gradients are produced by the kernels during
+    forward() (one fused launch sequence) and handed out, scaled by the incoming gradient, in backward()."""
+
+    @staticmethod
+    def forward(ctx, estimator, names, sigma_min, x1, mask, mu, spks, t, z, *params):
+        nig = ctx.needs_input_grad          # (estimator, names, sigma_min, x1, mask, mu, spks, t, z, *params)
+        need = bool(nig[5] or nig[6] or any(nig[9:]))
+        plan = estimator.train_plan()
+        out = plan.compute_loss(zip(names, (p.detach() for p in params)), x1.detach(), mask, mu.detach(), z, t,
+                                None if spks is None else spks.detach(), sigma_min, backward=need,
+                                want_dmu=bool(nig[5]), want_dspks=bool(nig[6]))
+        ctx.saved = (out["grads"], out["dmu"], out["dspks"], names) if need else None
+        ctx.mark_non_differentiable(out["y"])
+        return out["loss"], out["y"]
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_y):
+        if ctx.saved is None:
+            raise RuntimeError("compute_loss was run without gradients enabled")
+        grads, dmu, dspks, names = ctx.saved
+        scale = lambda g: None if g is None else g * g_loss
+        # inputs: estimator, names, sigma_min, x1, mask, mu, spks, t, z, *params
+        return (None, None, None, None, None, scale(dmu), scale(dspks), None, None, *[scale(grads[k]) for k in names])
 
 
 class CFM(BASECFM):

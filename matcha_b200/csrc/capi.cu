@@ -211,6 +211,26 @@ int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, 
                           int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out) {
   return guarded([&] { P(plan)->synthesise_host(mu, mask, z, spks, B, T, n_steps, L, mel_mean, mel_std, mel_out, wav_out); });
 }
+int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
+                       const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
+                       float sigma_min, int backward, float* loss, float* y, float* v, float* dmu, float* dspks,
+                       void* stream) {
+  return guarded([&] {
+    if (!params || !x1 || !mask || !mu || !z || !t || !loss) throw mb::Error("null argument");
+    std::map<std::string, std::pair<const float*, float*>> m;
+    const std::string pre = prefix ? prefix : "";
+    for (int i = 0; i < n; ++i) {
+      std::string name = params[i].name;
+      if (!pre.empty()) {
+        if (name.compare(0, pre.size(), pre) != 0) continue;
+        name = name.substr(pre.size());
+      }
+      m[name] = {params[i].param, params[i].grad};
+    }
+    P(plan)->compute_loss_grad(m, x1, mask, mu, z, t, spks, B, T, sigma_min, loss, y, v, dmu, dspks, backward != 0,
+                               static_cast<cudaStream_t>(stream));
+  });
+}
 long long mb200_launch_count(const mb200_plan* plan) { return plan ? reinterpret_cast<const Plan*>(plan)->launches : 0; }
 int mb200_set_profiling(mb200_plan* plan, int on) {
   return guarded([&] {

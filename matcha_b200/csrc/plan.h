@@ -125,6 +125,12 @@ class Plan {
                   float mel_mean, float mel_std, float* dec_out, float* mel_out, float* wav_out, cudaStream_t st);
   void synthesise_host(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
                        int L, float mel_mean, float mel_std, float* mel_out, float* wav_out);
+  // BASECFM.compute_loss forward (+ backward) on the fp32 training kernels (train.cu).  params: name -> (parameter, gradient)
+  // device pointers in the reference layout; gradients are ACCUMULATED (+=) into non-null gradient pointers.
+  void compute_loss_grad(const std::map<std::string, std::pair<const float*, float*>>& params, const float* x1,
+                         const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
+                         float sigma_min, float* loss_out, float* y_out, float* v_out, float* dmu, float* dspks, bool backward,
+                         cudaStream_t st);
   void test_conv1d(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T, int K, int dil,
                    int stride, bool transposed, float* y, cudaStream_t st);
   void test_attention(const float* qkv, const float* mask, int B, int T, float* out, cudaStream_t st);
@@ -166,6 +172,8 @@ class Plan {
 
  private:
   std::vector<void*> owned_;
+  void* train_arena_ = nullptr;       // activations saved for the backward pass + gradient scratch (train.cu)
+  size_t train_arena_bytes_ = 0;
   std::recursive_mutex mu_;
   EstimatorW est_;
   GeneratorW gen_;

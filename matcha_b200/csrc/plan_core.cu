@@ -48,6 +48,7 @@ Plan::~Plan() {
   for (auto& kv : decode_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
   for (auto& kv : vocoder_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
   for (void* p : owned_) cudaFree(p);
+  if (train_arena_) cudaFree(train_arena_);
   for (auto* arr : {ws_est_, ws_voc_, ws_io_}) (void)arr;
   for (auto& b : ws_est_) if (b.p) cudaFree(b.p);
   for (auto& b : ws_voc_) if (b.p) cudaFree(b.p);

@@ -1,0 +1,125 @@
+"""BASECFM.compute_loss (flow_matching.py:87-118) forward + backward on the CUDA training path, against the CPU oracle
+under torch autograd (same weights, same injected t and z).  The path is fp32 throughout, so the bar is the fp32 one:
+loss and velocity max-abs <= 1e-3, every parameter gradient within 2e-3 relative L2 of autograd's.  Needs a B200."""
+import os
+import types
+
+import pytest
+import torch
+
+import matcha_b200 as mb
+from matcha_b200._lib import Plan
+from oracle import matcha_oracle as mo
+from oracle import weights
+
+pytestmark = pytest.mark.gpu
+
+DEC = dict(channels=[256, 256], dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=2,
+           act_fn="snakebeta")
+CFM_PARAMS = types.SimpleNamespace(solver="euler", sigma_min=1e-4)
+GRAD_REL_L2 = 2e-3
+
+
+def rel_l2(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+
+
+def _case(b, t, lengths, c_in, seed):
+    g = torch.Generator().manual_seed(seed)
+    x1 = torch.randn(b, 80, t, generator=g)
+    mu = torch.randn(b, 80, t, generator=g)
+    z = torch.randn(b, 80, t, generator=g)
+    tt = torch.rand(b, 1, 1, generator=g)
+    mask = weights.prefix_mask(lengths, t)
+    spks = torch.randn(b, c_in - 160, generator=g) if c_in > 160 else None
+    return x1, mask, mu, z, tt, spks
+
+
+def _oracle(sd, x1, mask, mu, z, tt, spks):
+    sd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    mu = mu.clone().requires_grad_(True)
+    spks = None if spks is None else spks.clone().requires_grad_(True)
+    loss, y = mo.compute_loss(sd, x1, mask, mu, tt, z, spks)
+    loss.backward()
+    return float(loss.detach()), y.detach(), {k: v.grad for k, v in sd.items()}, mu.grad, None if spks is None else spks.grad
+
+
+@pytest.mark.parametrize("b,t,lengths,c_in", [(2, 24, [24, 13], 160), (3, 52, [52, 40, 7], 224), (2, 136, [130, 136], 160)])
+def test_compute_loss_forward_backward_matches_autograd_oracle(b, t, lengths, c_in):
+    sd = weights.estimator_state_dict(c_in, seed=7)
+    x1, mask, mu, z, tt, spks = _case(b, t, lengths, c_in, 11)
+    loss_o, y_o, grads_o, dmu_o, dspk_o = _oracle(sd, x1, mask, mu, z, tt, spks)
+
+    dev = torch.device("cuda")
+    plan = Plan("fp32", c_in, use_graph=False)
+    named = [(k[len("estimator."):], v.to(dev).contiguous()) for k, v in sd.items()]
+    out = plan.compute_loss(named, x1, mask, mu, z, tt, spks, 1e-4, backward=True, want_dmu=True, want_dspks=c_in > 160)
+    torch.cuda.synchronize()
+    assert abs(float(out["loss"]) - loss_o) <= 1e-3 * max(1.0, abs(loss_o)), (float(out["loss"]), loss_o)
+    assert float((out["y"].cpu() - y_o).abs().max()) <= 1e-5
+    with torch.no_grad():
+        v_o = mo.estimator_forward(sd, y_o, mask, mu, tt.reshape(-1), spks)
+    assert float((out["v"].cpu() - v_o).abs().max()) <= 1e-3
+    worst = ("", 0.0)
+    for k, g in out["grads"].items():
+        want = grads_o["estimator." + k]
+        assert torch.isfinite(g).all(), k
+        r = rel_l2(g.cpu(), want)
+        if r > worst[1]:
+            worst = (k, r)
+    assert worst[1] <= GRAD_REL_L2, worst
+    assert rel_l2(out["dmu"].cpu(), dmu_o) <= GRAD_REL_L2
+    if c_in > 160:
+        assert rel_l2(out["dspks"].cpu(), dspk_o) <= GRAD_REL_L2
+
+
+def test_compute_loss_module_is_an_autograd_node():
+    """Drop-in use: CFM.compute_loss(...)[0].backward() fills .grad of the estimator's parameters (and of mu, which the
+    text encoder produced) with the CUDA-computed gradients; an SGD step then lowers the loss."""
+    dev = torch.device("cuda")
+    sd = weights.estimator_state_dict(160, seed=3)
+    cfm = mb.CFM(160, 80, CFM_PARAMS, DEC, n_spks=1, spk_emb_dim=64).to(dev)
+    cfm.load_state_dict(sd, strict=True)
+    x1, mask, mu, z, tt, _ = _case(2, 40, [40, 29], 160, 5)
+    x1, mask, z, tt = x1.to(dev), mask.to(dev), z.to(dev), tt.to(dev)
+    mu = mu.to(dev).requires_grad_(True)
+    loss, y = cfm.compute_loss(x1, mask, mu, t=tt, z=z)
+    assert loss.requires_grad and not y.requires_grad
+    loss.backward()
+    loss_o, _, grads_o, dmu_o, _ = _oracle(sd, x1.cpu(), mask.cpu(), mu.detach().cpu(), z.cpu(), tt.cpu(), None)
+    assert abs(float(loss) - loss_o) <= 1e-3 * max(1.0, abs(loss_o))
+    for k, p in cfm.named_parameters():
+        assert p.grad is not None, k
+        assert rel_l2(p.grad.cpu(), grads_o[k]) <= GRAD_REL_L2, k
+    assert rel_l2(mu.grad.cpu(), dmu_o) <= GRAD_REL_L2
+    with torch.no_grad():
+        for p in cfm.parameters():
+            p -= 1e-3 * p.grad
+    loss2, _ = cfm.compute_loss(x1, mask, mu.detach(), t=tt, z=z)
+    assert float(loss2) < float(loss)
+
+
+def test_compute_loss_property_cfg5_shape():
+    """BASELINE cfg5 shape (B=32, T=512, ragged lengths, per-sample t): gradients are finite, padded frames carry no
+    gradient into mu, and the loss is invariant to what sits in x1's valid region ordering of the batch (permutation
+    of utterances permutes nothing in the summed loss)."""
+    dev = torch.device("cuda")
+    sd = weights.estimator_state_dict(160, seed=9)
+    b, t = 32, 512
+    g = torch.Generator().manual_seed(2)
+    lengths = [int(v) for v in (torch.randint(64, 129, (b,), generator=g) * 4)]
+    x1, mask, mu, z, tt, _ = _case(b, t, lengths, 160, 21)
+    plan = Plan("fp32", 160, use_graph=False)
+    named = [(k[len("estimator."):], v.to(dev).contiguous()) for k, v in sd.items()]
+    out = plan.compute_loss(named, x1, mask, mu, z, tt, None, 1e-4, backward=True, want_dmu=True)
+    perm = torch.randperm(b, generator=g)
+    out2 = plan.compute_loss(named, x1[perm], mask[perm], mu[perm], z[perm], tt[perm], None, 1e-4, backward=True)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out["loss"]).all()
+    assert abs(float(out["loss"]) - float(out2["loss"])) <= 1e-4 * abs(float(out["loss"]))
+    dmu = out["dmu"].cpu()
+    assert torch.isfinite(dmu).all()
+    assert float((dmu * (1 - mask)).abs().max()) == 0.0
+    for k, gr in out["grads"].items():
+        assert torch.isfinite(gr).all(), k
+        assert rel_l2(out2["grads"][k], gr) <= 1e-3, k
