@@ -127,3 +127,52 @@ def synthesise_sharded(fn: Callable[..., torch.Tensor], lengths: Sequence[int], 
         if local.shape[0] == 0:
             local = local.new_zeros(0, max(int(c) for c in chs), 1)
     return gather_padded(local, idx, len(lengths), dst=dst, group=group)
+
+
+def allreduce_gradients(params, bucket_bytes: int = 32 << 20, group: Optional[dist.ProcessGroup] = None,
+                        valid_frames: Optional[torch.Tensor] = None) -> None:
+    """Data-parallel training (BASELINE cfg5): average the estimator's gradients over ranks after CFM.compute_loss's
+    backward.  This is the training path's one real exchange step: gradients are flattened into
+    buckets of at most `bucket_bytes` (11.0 M fp32 parameters = 44 MB -> two 32 MB buckets, sized for launch latency,
+    not link count: NVSwitch reduces in the switch), each bucket is one all-reduce (NCCL on GPUs, gloo in the CPU
+    tests) issued asynchronously so the copies of bucket i+1 overlap the reduction of bucket i.
+
+    The reference trains through Lightning DDP (configs/trainer/ddp.yaml), whose default is the plain mean over ranks;
+    pass `valid_frames` (this rank's sum(mask), a 0-dim tensor) to weight ranks by their valid frames instead, which
+    makes the result equal the single-process gradient of the concatenated batch (the loss is normalised by
+    sum(mask) * 80, flow_matching.py:115-117)."""
+    params = [p for p in params if p.grad is not None]
+    if not params or not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    world = dist.get_world_size(group)
+    weight = None
+    if valid_frames is not None:
+        total = valid_frames.detach().clone().to(params[0].grad.device, torch.float32).reshape(1)
+        mine = total.clone()
+        dist.all_reduce(total, group=group)
+        weight = (mine / total).item()
+    buckets, cur, size = [], [], 0
+    for p in params:
+        n = p.grad.numel() * p.grad.element_size()
+        if cur and size + n > bucket_bytes:
+            buckets.append(cur)
+            cur, size = [], 0
+        cur.append(p)
+        size += n
+    if cur:
+        buckets.append(cur)
+    pending = []
+    for bucket in buckets:
+        flat = torch.cat([p.grad.reshape(-1) for p in bucket])
+        if weight is not None:
+            flat.mul_(weight)
+        pending.append((bucket, flat, dist.all_reduce(flat, group=group, async_op=True)))
+    for bucket, flat, work in pending:
+        work.wait()
+        if weight is None:
+            flat.div_(world)
+        off = 0
+        for p in bucket:
+            n = p.grad.numel()
+            p.grad.copy_(flat[off:off + n].view_as(p.grad))
+            off += n

@@ -70,6 +70,42 @@ def estimator_case(name, c_in, lengths, t_pad, seed, n_steps, t_scalar):
     print(name, "v", float(v_scalar.abs().max()), "dec", float(dec.abs().max()), "loss", float(loss))
 
 
+GRAD_FULL = ("final_proj.weight", "final_block.block.1.weight", "mid_blocks.0.1.0.ff.net.0.alpha",
+             "mid_blocks.0.1.0.ff.net.0.beta", "time_mlp.linear_1.bias", "down_blocks.0.1.0.norm1.weight",
+             "up_blocks.0.0.mlp.1.bias", "down_blocks.0.2.conv.bias", "up_blocks.0.2.conv.bias")
+
+
+def grad_case(name, c_in, lengths, t_pad, seed):
+    """BASECFM.compute_loss under autograd in the UNMODIFIED reference module (flow_matching.py:87-118): the loss, every
+    parameter gradient's L2 norm and sum, a few small gradients in full, and d loss / d mu (the encoder side)."""
+    g = torch.Generator().manual_seed(seed + 1)
+    b = len(lengths)
+    cfm = build_cfm(c_in, seed)             # .eval(): the transformer blocks' Dropout(0.05) (decoder.py:207) is off
+    x1 = torch.randn(b, 80, t_pad, generator=g)
+    mu = torch.randn(b, 80, t_pad, generator=g).requires_grad_(True)
+    mask = weights.prefix_mask(lengths, t_pad)
+    spks = torch.randn(b, c_in - 160, generator=g).requires_grad_(True) if c_in > 160 else None
+    t_draw = torch.rand(b, 1, 1, generator=g)
+    z_draw = torch.randn(b, 80, t_pad, generator=g)
+    orig_rand, orig_randn_like = torch.rand, torch.randn_like
+    torch.rand = lambda *a, **k: t_draw.clone()
+    torch.randn_like = lambda *a, **k: z_draw.clone()
+    try:
+        loss, y = cfm.compute_loss(x1, mask, mu, spks)
+        loss.backward()
+    finally:
+        torch.rand, torch.randn_like = orig_rand, orig_randn_like
+    grads = {k[len("estimator."):]: p.grad.detach().clone() for k, p in cfm.named_parameters()}
+    fx = dict(kind="grads", c_in=c_in, seed=seed, lengths=list(lengths), t_pad=t_pad, x1=x1, mu=mu.detach().clone(), mask=mask,
+              spks=None if spks is None else spks.detach().clone(), t_draw=t_draw, z_draw=z_draw, loss=loss.detach().clone(),
+              grad_norm={k: float(v.double().norm()) for k, v in grads.items()},
+              grad_sum={k: float(v.double().sum()) for k, v in grads.items()},
+              grad_full={k: grads[k] for k in GRAD_FULL}, dmu=mu.grad.detach().clone(),
+              dspks=None if spks is None else spks.grad.detach().clone())
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "loss", float(loss), "params", len(grads), "|dmu|", float(mu.grad.norm()))
+
+
 def generator_case(name, b, t, seed, weight_norm):
     g = torch.Generator().manual_seed(seed + 2)
     gen = build_generator(seed, weight_norm)
@@ -118,9 +154,14 @@ def encoder_case(name, n_spks, lengths, seed, length_scale):
 
 
 def main():
+    import sys
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
     torch.set_num_threads(8)
+    if "grads" in sys.argv[1:]:            # only the compute_loss gradient fixtures (added after the forward ones)
+        grad_case("grad_lj_ragged", 160, (24, 17, 9), 24, seed=41)
+        grad_case("grad_vctk_ragged", 224, (36, 20), 36, seed=42)
+        return
     estimator_case("est_lj_ragged", 160, (24, 17, 9), 24, seed=11, n_steps=3, t_scalar=0.3)
     estimator_case("est_lj_min", 160, (4, 1), 4, seed=12, n_steps=2, t_scalar=0.0)
     estimator_case("est_vctk_ragged", 224, (20, 13), 20, seed=13, n_steps=2, t_scalar=0.75)

@@ -95,3 +95,45 @@ def test_sharded_path_world2_matches_single_process(lengths):
         p.join(120)
         assert p.exitcode == 0
     assert result.get(timeout=5) == "ok"
+
+
+def _grad_worker(rank, world, port, result):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.Generator().manual_seed(5)
+        shapes = [(256, 160, 3), (256,), (1024, 256), (1024,), (80, 256, 1), (7,)]
+        per_rank = [[torch.randn(*s, generator=g) for s in shapes] for _ in range(world)]
+        frames = [torch.tensor(float(100 + 37 * r)) for r in range(world)]
+        for weighted in (False, True):
+            params = [torch.nn.Parameter(torch.zeros(*s)) for s in shapes]
+            for p, gr in zip(params, per_rank[rank]):
+                p.grad = gr.clone()
+            params.append(torch.nn.Parameter(torch.zeros(3)))           # a parameter without a gradient is skipped
+            mdist.allreduce_gradients(params, bucket_bytes=300_000, valid_frames=frames[rank] if weighted else None)
+            tot = sum(float(f) for f in frames)
+            for i, p in enumerate(params[:-1]):
+                if weighted:
+                    want = sum(per_rank[r][i] * (float(frames[r]) / tot) for r in range(world))
+                else:
+                    want = sum(per_rank[r][i] for r in range(world)) / world
+                assert torch.allclose(p.grad, want, atol=1e-6), (weighted, i)
+            assert params[-1].grad is None
+        if rank == 0:
+            result.put("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gradient_allreduce_world2_buckets_and_frame_weighting():
+    ctx = mp.get_context("spawn")
+    result = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_grad_worker, args=(r, 2, port, result)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert result.get(timeout=5) == "ok"

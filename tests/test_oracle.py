@@ -120,3 +120,27 @@ def test_live_reference_generator_both_layouts():
 def test_golden_fixtures_are_small(golden_dir):
     total = sum(os.path.getsize(p) for p in glob.glob(os.path.join(golden_dir, "*.pt")))
     assert 0 < total < 4 << 20
+
+
+@pytest.mark.parametrize("name", ["grad_lj_ragged", "grad_vctk_ragged"])
+def test_compute_loss_gradients_match_reference_golden(golden_dir, name):
+    """The oracle's compute_loss under autograd against gradients the unmodified reference module produced
+    (oracle/make_golden.py grads): loss, every parameter gradient's norm and sum, a few gradients in full, d/d mu."""
+    fx = torch.load(os.path.join(golden_dir, name + ".pt"), weights_only=False)
+    sd = {k: v.clone().requires_grad_(True) for k, v in weights.estimator_state_dict(fx["c_in"], seed=fx["seed"]).items()}
+    mu = fx["mu"].clone().requires_grad_(True)
+    spks = None if fx["spks"] is None else fx["spks"].clone().requires_grad_(True)
+    loss, _ = mo.compute_loss(sd, fx["x1"], fx["mask"], mu, fx["t_draw"], fx["z_draw"], spks)
+    loss.backward()
+    assert abs(float(loss.detach()) - float(fx["loss"])) <= 1e-5 * abs(float(fx["loss"]))
+    assert len(fx["grad_norm"]) == 180
+    for k, n in fx["grad_norm"].items():
+        g = sd["estimator." + k].grad.double()
+        assert abs(float(g.norm()) - n) <= 1e-4 * n + 1e-9, k
+        assert abs(float(g.sum()) - fx["grad_sum"][k]) <= 1e-4 * n * g.numel() ** 0.5 + 1e-9, k
+    for k, g in fx["grad_full"].items():
+        got = sd["estimator." + k].grad
+        assert float((got - g).norm() / g.norm()) <= 1e-4, k
+    assert float((mu.grad - fx["dmu"]).norm() / fx["dmu"].norm()) <= 1e-4
+    if spks is not None:
+        assert float((spks.grad - fx["dspks"]).norm() / fx["dspks"].norm()) <= 1e-4

@@ -123,3 +123,26 @@ def test_compute_loss_property_cfg5_shape():
     for k, gr in out["grads"].items():
         assert torch.isfinite(gr).all(), k
         assert rel_l2(out2["grads"][k], gr) <= 1e-3, k
+
+
+@pytest.mark.parametrize("name", ["grad_lj_ragged", "grad_vctk_ragged"])
+def test_compute_loss_gradients_match_reference_golden(golden_dir, name):
+    """The CUDA backward against gradients produced by the UNMODIFIED reference CFM.compute_loss under autograd
+    (tests/golden/grad_*.pt, generated by oracle/make_golden.py grads in the build container)."""
+    fx = torch.load(os.path.join(golden_dir, name + ".pt"), weights_only=False)
+    sd = weights.estimator_state_dict(fx["c_in"], seed=fx["seed"])
+    dev = torch.device("cuda")
+    plan = Plan("fp32", fx["c_in"], use_graph=False)
+    named = [(k[len("estimator."):], v.to(dev).contiguous()) for k, v in sd.items()]
+    out = plan.compute_loss(named, fx["x1"], fx["mask"], fx["mu"], fx["z_draw"], fx["t_draw"], fx["spks"], 1e-4, backward=True,
+                            want_dmu=True, want_dspks=fx["spks"] is not None)
+    assert abs(float(out["loss"]) - float(fx["loss"])) <= 1e-4 * abs(float(fx["loss"]))
+    assert set(out["grads"]) == set(fx["grad_norm"])
+    for k, n in fx["grad_norm"].items():
+        g = out["grads"][k].double()
+        assert abs(float(g.norm()) - n) <= GRAD_REL_L2 * n + 1e-9, (k, float(g.norm()), n)
+    for k, g in fx["grad_full"].items():
+        assert rel_l2(out["grads"][k].cpu(), g) <= GRAD_REL_L2, k
+    assert rel_l2(out["dmu"].cpu(), fx["dmu"]) <= GRAD_REL_L2
+    if fx["spks"] is not None:
+        assert rel_l2(out["dspks"].cpu(), fx["dspks"]) <= GRAD_REL_L2
