@@ -108,6 +108,10 @@ long long mb200_workspace_bytes(const mb200_plan* plan);
 int mb200_set_profiling(mb200_plan* plan, int on);
 int mb200_get_profile(const mb200_plan* plan, double* out);
 
+/* Developer hook: copies the cycle counters of the last instrumented kernel (MB200_DBG / MB200_PAIR_DBG / MB200_FF_DBG
+ * environment switches) to HOST memory: out[n_ctas * 16] for the first n_ctas CTAs.  Fails if nothing was instrumented. */
+int mb200_debug_probe(mb200_plan* plan, long long* out, int n_ctas);
+
 /* Unit-test hook: one Conv1d / ConvTranspose1d (+ bias) through the conv-GEMM kernel of the plan's mode.
  * x (B,Cin,T) fp32 device, w reference layout HOST fp32 ((Cout,Cin,K) or (Cin,Cout,K) when transposed), bias HOST (Cout)
  * or NULL, y (B,Cout,T_out) fp32 device.  stride applies to Conv1d (1|2) or ConvTranspose1d (K == 2*stride). */

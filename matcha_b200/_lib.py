@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention",
+    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
 
 
@@ -75,6 +75,7 @@ def load():
         lib.mb200_get_profile.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
         lib.mb200_test_conv1d.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, i, i, vp, vp]
         lib.mb200_test_attention.argtypes = [vp, vp, vp, i, i, vp, vp]
+        lib.mb200_debug_probe.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong), i]
         _lib = lib
         return lib
 
@@ -279,6 +280,12 @@ class Plan:
 
     def workspace_bytes(self):
         return int(self.lib.mb200_workspace_bytes(self.handle))
+
+    def debug_probe(self, n_ctas=148):
+        """[n_ctas][16] cycle counters of the last instrumented kernel (developer switches MB200_*_DBG)."""
+        buf = (ctypes.c_longlong * (n_ctas * 16))()
+        check(self.lib.mb200_debug_probe(self.handle, buf, n_ctas))
+        return [list(buf[c * 16:(c + 1) * 16]) for c in range(n_ctas)]
 
     # ---- unit-test hooks
     def test_conv1d(self, x, w, bias, dilation=1, stride=1, transposed=False):

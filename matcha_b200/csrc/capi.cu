@@ -247,6 +247,14 @@ int mb200_get_profile(const mb200_plan* plan, double* out) {
 }
 long long mb200_workspace_bytes(const mb200_plan* plan) { return plan ? reinterpret_cast<const Plan*>(plan)->bytes_allocated : 0; }
 
+int mb200_debug_probe(mb200_plan* plan, long long* out, int n_ctas) {
+  return guarded([&] {
+    Plan* p = P(plan);
+    if (!p->probe_out || !out || n_ctas < 1 || n_ctas > 148) throw mb::Error("no instrumented kernel (or bad arguments)");
+    MB_CUDA(cudaDeviceSynchronize());
+    MB_CUDA(cudaMemcpy(out, p->probe_out, static_cast<size_t>(n_ctas) * 16 * sizeof(long long), cudaMemcpyDeviceToHost));
+  });
+}
 int mb200_test_conv1d(mb200_plan* plan, const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T,
                       int K, int dilation, int stride, int transposed, float* y, void* stream) {
   return guarded([&] { P(plan)->test_conv1d(x, w, bias, B, Cin, Cout, T, K, dilation, stride, transposed != 0, y, static_cast<cudaStream_t>(stream)); });

@@ -83,6 +83,20 @@ struct PairGeom {
   long long* dbg_out;            // developer probe: per-CTA cycle counters [grid][16] (MB200_PAIR_DBG), else null
 };
 
+// Geometry / parameters of the fused feed-forward kernel (ff_fused.cu): rows are the flat [B * L] frame index.
+struct FFGeom {
+  long rows;                     // B * L
+  int total_tiles;               // ceil(rows / 128)
+  const float* bias1;            // [1024]
+  const float* snake_a;          // [1024] exp(alpha)
+  const float* snake_invb;       // [1024] 1 / (exp(beta) + 1e-9)
+  const float* bias2;            // [256]
+  const float* mask;             // [rows]
+  const void* resid;             // [rows][256] operand dtype (the attention sub-block's output)
+  void* out;                     // [rows][256] operand dtype
+  long long* dbg_out;            // developer probe (MB200_FF_DBG): per-CTA cycle counters [grid][16], else null
+};
+
 struct EpiParams {
   int T_o;                 // output rows per batch (T_out * o_mul)
   int o_mul;               // output row = t * o_mul + phase * o_phase_step

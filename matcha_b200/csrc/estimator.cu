@@ -202,6 +202,10 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     if (tc) { e.ln_out = buf(LN); e.ln_ld = 256; e.ln_g = X.ln3_g; e.ln_b = X.ln3_b; }
     add(conv_op(X.out, Src{buf(ATT), 128, 128, Tn}, nullptr, B, Tn, e));
     if (!tc) layernorm(buf(HID), X.ln3_g, X.ln3_b, buf(LN), static_cast<long>(B) * Tn);
+    if (ff_supported()) {   // feed-forward as one kernel: the 1024-wide hidden activation stays in shared memory
+      add(ff_op(X.ff1, X.ff2, X.snake_a, X.snake_invb, buf(LN), buf(HID), mask, out, static_cast<long>(B) * Tn));
+      return;
+    }
     e = epi();
     e.snake_a = X.snake_a; e.snake_invb = X.snake_invb;
     e.out0 = buf(FF); e.out0_ld = 1024; e.out0_f32 = dtype == MB200_F32;

@@ -1,0 +1,312 @@
+// The transformer block's feed-forward (matcha/models/components/transformer.py:131-134 with SnakeBeta :64-80, residual
+// and mask of :311-316 / decoder.py:398-404) as ONE persistent tcgen05 kernel:
+//
+//     out = ( SnakeBeta(x W1^T + b1) W2^T + b2 + resid ) * mask            x = LayerNorm3(hidden) [rows][256]
+//
+// Run as two conv-GEMM launches the 1024-wide hidden activation makes a round trip through HBM (59 MB written and read
+// back per T-level block at cfg2) and each launch has only one or two tiles per CTA, i.e. no steady state.  Here the
+// hidden activation never leaves the SM, and one tile is a 16-step software pipeline: per tile of 128 rows
+//     TMA   x tile [128][256] (4 K chunks)                               -> shared memory (kept for the whole tile)
+//     for j in 0..7 (chunks of 128 hidden channels):
+//       MMA1  x . W1[128j..128j+127]^T            (N = 128, K = 256)      -> TMEM accumulator ring 1 (2 x 128 columns)
+//       E1    + b1, SnakeBeta, -> operand dtype                           -> shared memory "mid" chunk in the UMMA K-major
+//                                                                            128B-swizzled layout (swizzled by hand)
+//       MMA2  mid_j . W2[:, 128j..128j+127]^T     (N = 256, K = 128)      -> TMEM accumulator 2 (256 columns), accumulated over j
+//     E2    + b2 + resid, * mask                                          -> global
+// The issuer interleaves M1(j+1) before M2(j), so E1(j) overlaps M1(j+1) and M2(j-1).  Weights stream through a ring of
+// three 32 KB stages (W1 chunk = 2 stages of two [128 x 64] boxes, W2 chunk = 2 stages of one [256 x 64] box) in exactly
+// the order the issuer consumes them.  Same arithmetic and roundings as the two-launch form: results are bit-identical.
+//
+// Warp roles (320 threads): 0 TMA producer, 1 MMA issuer (converged warps, elected single-thread instructions),
+// 2-9 E1 / E2 (warp % 4 = TMEM lane quarter, (warp - 2) / 4 = column half).
+#include "conv.cuh"
+#include "epilogue3.cuh"
+#include "launch.h"
+#include "ptx.cuh"
+
+namespace mb {
+
+namespace {
+constexpr int kFFXBytes = 4 * 16384;      // x tile: 4 K chunks of [128 rows][64 ch]
+constexpr int kFFMidBytes = 2 * 16384;    // one mid chunk: 2 K chunks of [128 rows][64 ch]
+constexpr int kFFStage = 32768;           // one weight ring stage
+constexpr int kFFStages = 3;
+constexpr int kFFBarBytes = 512;
+// developer probe (FFGeom::dbg_out): cycles a role spends inside one barrier wait
+#define FW(stmt, acc) do { if (g.dbg_out) { const long long fw_a = clock64(); stmt; acc += clock64() - fw_a; } else { stmt; } } while (0)
+}  // namespace
+
+int ff_fused_smem_bytes() { return 1024 + kFFXBytes + 2 * kFFMidBytes + kFFStages * kFFStage + kFFBarBytes; }
+
+template <typename T>
+__global__ void __launch_bounds__(320, 1)
+ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
+                const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ FFGeom g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* x_tile = smem;
+  uint8_t* mid = x_tile + kFFXBytes;
+  uint8_t* w_ring = mid + 2 * kFFMidBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(w_ring + kFFStages * kFFStage);
+  uint64_t* x_full = bars;             // [1]
+  uint64_t* x_empty = bars + 1;        // [1]
+  uint64_t* w_full = bars + 2;         // [3]
+  uint64_t* w_empty = bars + 5;        // [3]
+  uint64_t* t1_full = bars + 8;        // [2]
+  uint64_t* t1_empty = bars + 10;      // [2]
+  uint64_t* mid_full = bars + 12;      // [2]
+  uint64_t* mid_empty = bars + 14;     // [2]
+  uint64_t* t2_full = bars + 16;       // [1]
+  uint64_t* t2_empty = bars + 17;      // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nt_cta = (g.total_tiles > static_cast<int>(blockIdx.x))
+                         ? (g.total_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
+    mbar_init(x_full, 1); mbar_init(x_empty, 1);
+    for (int s = 0; s < kFFStages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], 8);
+      mbar_init(&mid_full[s], 8); mbar_init(&mid_empty[s], 1);
+    }
+    mbar_init(t2_full, 1); mbar_init(t2_empty, 8);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================================================= TMA producer
+    int ws = 0;
+    uint32_t wph = 0;
+    long long pw[2] = {0, 0};
+    const long long pt0 = clock64();
+    auto load_X = [&](int n) {
+      const int tile = blockIdx.x + n * gridDim.x;
+      FW(mbar_wait(x_empty, (n & 1) ^ 1), pw[0]);
+      if (elect_one()) {
+        mbar_expect_tx(x_full, kFFXBytes);
+#pragma unroll
+        for (int kc = 0; kc < 4; ++kc) tma_load_3d(x_tile + kc * 16384, &tmX, x_full, kc * 64, tile * 128, 0);
+      }
+      __syncwarp();
+    };
+    auto load_W1 = [&](int j) {   // hidden channels [128 j, +128): two stages of two [128 n][64 k] boxes
+      for (int s = 0; s < 2; ++s) {
+        FW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
+        if (elect_one()) {
+          mbar_expect_tx(&w_full[ws], kFFStage);
+          tma_load_2d(w_ring + ws * kFFStage, &tmW1, &w_full[ws], (2 * s) * 64, j * 128);
+          tma_load_2d(w_ring + ws * kFFStage + 16384, &tmW1, &w_full[ws], (2 * s + 1) * 64, j * 128);
+        }
+        __syncwarp();
+        if (++ws == kFFStages) { ws = 0; wph ^= 1; }
+      }
+    };
+    auto load_W2 = [&](int j) {   // K slice [128 j, +128) of the down projection: two stages of one [256 n][64 k] box
+      for (int s = 0; s < 2; ++s) {
+        FW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
+        if (elect_one()) {
+          mbar_expect_tx(&w_full[ws], kFFStage);
+          tma_load_2d(w_ring + ws * kFFStage, &tmW2, &w_full[ws], j * 128 + s * 64, 0);
+        }
+        __syncwarp();
+        if (++ws == kFFStages) { ws = 0; wph ^= 1; }
+      }
+    };
+    if (nt_cta > 0) load_X(0);
+    for (int n = 0; n < nt_cta; ++n) {
+      load_W1(0);
+      for (int j = 1; j < 8; ++j) { load_W1(j); load_W2(j - 1); if (j == 7 && n + 1 < nt_cta) load_X(n + 1); }
+      load_W2(7);
+    }
+    if (g.dbg_out && lane == 0) { long long* o = g.dbg_out + blockIdx.x * 16; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; }
+  } else if (warp == 1) {
+    // ================================================================= MMA issuer
+    constexpr int fmt = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+    constexpr uint32_t idesc1 = umma_idesc_f16(fmt, 128, 128), idesc2 = umma_idesc_f16(fmt, 128, 256);
+    const uint32_t desc_hi = static_cast<uint32_t>(umma_smem_desc<128>(0) >> 32);
+    const uint32_t x_lo = static_cast<uint32_t>(umma_smem_desc<128>(smem_u32(x_tile)));
+    const uint32_t mid_lo = static_cast<uint32_t>(umma_smem_desc<128>(smem_u32(mid)));
+    const uint32_t w_lo0 = static_cast<uint32_t>(umma_smem_desc<128>(smem_u32(w_ring)));
+    int ws = 0;
+    uint32_t wph = 0;
+    long long iw[5] = {0, 0, 0, 0, 0};
+    const long long it0 = clock64();
+    for (int n = 0; n < nt_cta; ++n) {
+      FW(mbar_wait(x_full, n & 1), iw[0]);
+#pragma unroll 1
+      for (int j = 0; j <= 8; ++j) {
+        if (j < 8) {            // ---- M1(j): acc1[slot] = x . W1_j^T
+          const int jj = n * 8 + j, slot = jj & 1;
+          FW(mbar_wait(&t1_empty[slot], ((jj >> 1) & 1) ^ 1), iw[1]);
+          const uint32_t dtm = tmem_base + slot * 128;
+          for (int s = 0; s < 2; ++s) {
+            FW(mbar_wait(&w_full[ws], wph), iw[2]);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t w = w_lo0 + ws * (kFFStage >> 4);
+#pragma unroll
+              for (int c = 0; c < 2; ++c) {
+                const uint32_t a = x_lo + (2 * s + c) * 1024u, wc = w + c * 1024u;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_f16_lohi(dtm, a + 2 * k, wc + 2 * k, desc_hi, idesc1, (s | c | k) != 0 ? 1u : 0u);
+              }
+              umma_commit(&w_empty[ws]);
+              if (s == 1) { umma_commit(&t1_full[slot]); if (j == 7) umma_commit(x_empty); }
+            }
+            __syncwarp();
+            if (++ws == kFFStages) { ws = 0; wph ^= 1; }
+          }
+        }
+        if (j >= 1) {           // ---- M2(j-1): acc2 += mid_{j-1} . W2[:, slice j-1]^T
+          const int jm = j - 1, jj = n * 8 + jm, ms = jj & 1;
+          if (jm == 0) FW(mbar_wait(t2_empty, (n & 1) ^ 1), iw[4]);
+          FW(mbar_wait(&mid_full[ms], (jj >> 1) & 1), iw[3]);
+          const uint32_t dtm = tmem_base + 256;
+          for (int s = 0; s < 2; ++s) {
+            FW(mbar_wait(&w_full[ws], wph), iw[2]);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t w = w_lo0 + ws * (kFFStage >> 4);
+              const uint32_t a = mid_lo + ms * (kFFMidBytes >> 4) + s * 1024u;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma_f16_lohi(dtm, a + 2 * k, w + 2 * k, desc_hi, idesc2, (jm | s | k) != 0 ? 1u : 0u);
+              umma_commit(&w_empty[ws]);
+              if (s == 1) { umma_commit(&mid_empty[ms]); if (jm == 7) umma_commit(t2_full); }
+            }
+            __syncwarp();
+            if (++ws == kFFStages) { ws = 0; wph ^= 1; }
+          }
+        }
+      }
+    }
+    if (g.dbg_out && lane == 0) { long long* o = g.dbg_out + blockIdx.x * 16; o[3] = clock64() - it0; for (int i = 0; i < 5; ++i) o[4 + i] = iw[i]; }
+  } else {
+    // ================================================================= E1 (SnakeBeta -> mid) and E2 (-> global)
+    const int lane_grp = warp & 3, half = (warp - 2) >> 2;
+    const int r = lane_grp * 32 + lane;                     // row of the tile held by this lane
+    const uint32_t tlane = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16);
+    long long ew[3] = {0, 0, 0};
+    const long long et0 = clock64();
+    // Warm L1 with the per-channel parameters (13 KB) while the first x tile and weights are in flight: every later
+    // parameter load is then an L1 hit instead of a dependent chain of cold L2 round trips (measured: E1 was 4 000
+    // cycles per chunk against 2 048 cycles of MMA work).
+    {
+      const int tid = threadIdx.x - 64;   // 0..255
+      for (int i = tid; i < 3 * 1024 / 32 + 256 / 32; i += 256) {
+        const float* base = i < 32 ? g.bias1 : (i < 64 ? g.snake_a : (i < 96 ? g.snake_invb : g.bias2));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (i & 31) * 32));
+      }
+    }
+    auto ldp = [&](int col, float4 (&p)[6]) {   // bias, exp(alpha), 1/(exp(beta)+eps) of 8 hidden channels
+      p[0] = __ldg(reinterpret_cast<const float4*>(g.bias1 + col)); p[1] = __ldg(reinterpret_cast<const float4*>(g.bias1 + col) + 1);
+      p[2] = __ldg(reinterpret_cast<const float4*>(g.snake_a + col)); p[3] = __ldg(reinterpret_cast<const float4*>(g.snake_a + col) + 1);
+      p[4] = __ldg(reinterpret_cast<const float4*>(g.snake_invb + col)); p[5] = __ldg(reinterpret_cast<const float4*>(g.snake_invb + col) + 1);
+    };
+    for (int n = 0; n < nt_cta; ++n) {
+      const int tile = blockIdx.x + n * gridDim.x;
+#pragma unroll 1
+      for (int j = 0; j < 8; ++j) {
+        const int jj = n * 8 + j, slot = jj & 1;
+        uint8_t* mid_c = mid + slot * kFFMidBytes + half * 16384;
+        const int nb = j * 128 + half * 64;                 // first hidden channel of this lane's 64 columns
+        float4 prm[2][6];
+        ldp(nb, prm[0]);                                    // in flight while the accumulator is waited for
+        FW(mbar_wait(&t1_full[slot], (jj >> 1) & 1), ew[0]);
+        tc_fence_after();
+        float acc[2][32];
+        tmem_ld_32x32(tlane + slot * 128 + half * 64, acc[0]);
+        tmem_ld_32x32(tlane + slot * 128 + half * 64 + 32, acc[1]);
+        FW(mbar_wait(&mid_empty[slot], ((jj >> 1) & 1) ^ 1), ew[1]);   // the M2 that read this mid buffer two chunks ago is done
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q + 1 < 8) ldp(nb + 8 * (q + 1), prm[(q + 1) & 1]);
+          const float4* pq = prm[q & 1];
+          const float bv[8] = {pq[0].x, pq[0].y, pq[0].z, pq[0].w, pq[1].x, pq[1].y, pq[1].z, pq[1].w};
+          const float pa[8] = {pq[2].x, pq[2].y, pq[2].z, pq[2].w, pq[3].x, pq[3].y, pq[3].z, pq[3].w};
+          const float pb[8] = {pq[4].x, pq[4].y, pq[4].z, pq[4].w, pq[5].x, pq[5].y, pq[5].z, pq[5].w};
+          float v[8];
+          const float* a = acc[q >> 2] + 8 * (q & 3);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            v[ch] = a[ch] + bv[ch];
+            const float sn = __sinf(v[ch] * pa[ch]);
+            v[ch] = fmaf(pb[ch] * sn, sn, v[ch]);
+          }
+          uint32_t off = static_cast<uint32_t>(r * 128 + q * 16);
+          off ^= ((off >> 7) & 7u) << 4;
+          *reinterpret_cast<uint4*>(mid_c + off) = pack8<T>(v);
+        }
+        tc_fence_before();
+        fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async-proxy reads
+        __syncwarp();
+        if (lane == 0) { mbar_arrive(&t1_empty[slot]); mbar_arrive(&mid_full[slot]); }
+      }
+      // ---- E2: this warp's 128 output channels [128 half, +128) of the lane's row.  The residual row segment (256 B)
+      // is requested before the accumulator barrier, so its latency hides behind the last chunk's MMAs.
+      const long row = static_cast<long>(tile) * 128 + r;
+      const bool ok = row < g.rows;
+      const T* rp = reinterpret_cast<const T*>(g.resid) + row * 256 + half * 128;
+      T* op = reinterpret_cast<T*>(g.out) + row * 256 + half * 128;
+      uint4 ru[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { ru[i] = make_uint4(0, 0, 0, 0); if (ok) ru[i] = __ldg(reinterpret_cast<const uint4*>(rp) + i); }
+      const float m = ok ? __ldg(g.mask + row) : 0.f;
+      FW(mbar_wait(t2_full, n & 1), ew[2]);
+      tc_fence_after();
+      float acc[2][32];
+      tmem_ld_32x32(tlane + 256 + half * 128, acc[0]);
+#pragma unroll
+      for (int cb = 0; cb < 4; ++cb) {
+        const int n0 = half * 128 + cb * 32;
+        float4 b2[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) b2[i] = __ldg(reinterpret_cast<const float4*>(g.bias2 + n0) + i);
+        tmem_ld_wait();
+        if (cb + 1 < 4) tmem_ld_32x32(tlane + 256 + n0 + 32, acc[(cb + 1) & 1]);
+        const float* a = acc[cb & 1];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float bv[8] = {b2[2 * q].x, b2[2 * q].y, b2[2 * q].z, b2[2 * q].w, b2[2 * q + 1].x, b2[2 * q + 1].y, b2[2 * q + 1].z, b2[2 * q + 1].w};
+          float rv[8], v[8];
+          unpack8<T>(ru[cb * 4 + q], rv);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) { v[ch] = a[8 * q + ch] + bv[ch]; v[ch] += rv[ch]; v[ch] *= m; }
+          if (ok) *reinterpret_cast<uint4*>(op + cb * 32 + 8 * q) = pack8<T>(v);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(t2_empty);
+    }
+    if (g.dbg_out && warp == 2 && lane == 0) { long long* o = g.dbg_out + blockIdx.x * 16; o[9] = clock64() - et0; for (int i = 0; i < 3; ++i) o[10 + i] = ew[i]; o[13] = nt_cta; }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+template <typename T>
+cudaError_t launch_ff_fused(const FFLaunch& L, cudaStream_t st) {
+  auto kern = ff_fused_kernel<T>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (err != cudaSuccess) return err;
+    configured = true;
+  }
+  kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmX, L.tmW1, L.tmW2, L.g);
+  return cudaGetLastError();
+}
+template cudaError_t launch_ff_fused<__nv_bfloat16>(const FFLaunch&, cudaStream_t);
+template cudaError_t launch_ff_fused<__half>(const FFLaunch&, cudaStream_t);
+
+}  // namespace mb

@@ -29,6 +29,13 @@ struct PairLaunch {
   int C, mb, smem_bytes, grid;
 };
 
+struct FFLaunch {
+  CUtensorMap tmX, tmW1, tmW2;
+  FFGeom g;
+  int smem_bytes, grid;
+};
+int ff_fused_smem_bytes();
+template <typename T> cudaError_t launch_ff_fused(const FFLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_resblock_pair(const PairLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_conv_umma(const ConvLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_conv_simt(const ConvLaunch& L, cudaStream_t st);

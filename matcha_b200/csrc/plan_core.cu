@@ -41,6 +41,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_TILE_POLICY")) tile_policy = std::atoi(v);
   if (const char* v = std::getenv("MB200_KERNEL")) kernel_version = std::atoi(v);
   if (const char* v = std::getenv("MB200_FUSE_PAIRS")) fuse_pairs = std::atoi(v);
+  if (const char* v = std::getenv("MB200_FUSE_FF")) fuse_ff = std::atoi(v);
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -455,6 +456,40 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
   });
   op.kind = 0;
   op.flops = 2.0 * B * T * static_cast<double>(C) * (W1.k_real + W2.k_real);
+  return op;
+}
+
+Launch Plan::ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, const float* snake_invb, const void* x,
+                   const void* resid, const float* mask, void* out, long rows) {
+  if (!ff_supported()) throw Error("ff_op: unsupported configuration");
+  if (W1.N != 1024 || W1.K_total != 256 || W2.N != 256 || W2.K_total != 1024 || W1.kc != 64 || W2.kc != 64 ||
+      W1.n_phases != 1 || W2.n_phases != 1 || !W1.bias || !W2.bias)
+    throw Error("ff_op: packed weights do not match a 256 -> 1024 -> 256 feed-forward");
+  FFLaunch L{};
+  L.g.rows = rows;
+  L.g.total_tiles = static_cast<int>((rows + 127) / 128);
+  L.g.bias1 = W1.bias; L.g.snake_a = snake_a; L.g.snake_invb = snake_invb; L.g.bias2 = W2.bias;
+  L.g.mask = mask; L.g.resid = resid; L.g.out = out;
+  L.g.dbg_out = nullptr;
+  if (const char* v = std::getenv("MB200_FF_DBG")) {   // developer probe: instrument the n-th feed-forward op built
+    static int built = 0;
+    if (built++ == std::atoi(v)) {
+      L.g.dbg_out = static_cast<long long*>(dalloc(148 * 16 * sizeof(long long)));
+      probe_out = L.g.dbg_out;
+      std::fprintf(stderr, "[ff probe] rows=%ld tiles=%d\n", rows, L.g.total_tiles);
+    }
+  }
+  L.tmX = tmap_act(x, 256, static_cast<int>(rows), 1, 64);
+  L.tmW1 = tmap_w(W1.w, 256, 1024, 64, 128);
+  L.tmW2 = tmap_w(W2.w, 1024, 256, 64, 256);
+  L.smem_bytes = ff_fused_smem_bytes();
+  L.grid = std::min(L.g.total_tiles, num_sms);
+  const int dtype = cfg.dtype;
+  Launch op([L, dtype](cudaStream_t st) -> cudaError_t {
+    return dtype == MB200_BF16 ? launch_ff_fused<__nv_bfloat16>(L, st) : launch_ff_fused<__half>(L, st);
+  });
+  op.kind = 0;
+  op.flops = 2.0 * static_cast<double>(rows) * 2.0 * 256.0 * 1024.0;
   return op;
 }
 

@@ -156,6 +156,41 @@ def test_fused_resblock_step_is_bit_identical_to_two_conv_launches(monkeypatch, 
         check(out["1"], mo.hifigan_forward(sd, mel), prec)
 
 
+@pytest.mark.parametrize("prec", ["fp16", "bf16"])
+@pytest.mark.parametrize("b,t,lengths", [(1, 4, [3]), (2, 136, [136, 77]), (5, 452, [451, 452, 300, 9, 200])])
+def test_fused_feed_forward_matches_two_conv_launches(monkeypatch, prec, b, t, lengths):
+    """The transformer feed-forward (transformer.py:131-134, SnakeBeta :64-80) runs as one kernel that keeps the 1024-wide
+    hidden activation in shared memory (ff_fused.cu): same MMA order, arithmetic and roundings as the ff1 / ff2 conv-GEMM
+    launches.  With one warp per GroupNorm group (T = 4) the estimator is deterministic and the outputs must be EQUAL.
+    At larger sizes the estimator's GroupNorm partial sums are accumulated with atomics, so two runs of the SAME path
+    already differ by half-precision ulps amplified through the network; there the fused path must be no further from the
+    two-launch path than that path is from itself, and as close to the fp32 path.  Sizes: a single partial tile, tiles
+    that straddle two utterances (the fused kernel tiles the flat B*L rows), several row tiles per CTA at cfg2's length."""
+    sd = weights.estimator_state_dict(160, seed=5)
+    g = torch.Generator().manual_seed(3)
+    x, mu = torch.randn(b, 80, t, generator=g), torch.randn(b, 80, t, generator=g)
+    mask = weights.prefix_mask(lengths, t)
+
+    def run(precision, fuse):
+        monkeypatch.setenv("MB200_FUSE_FF", fuse)
+        plan = Plan(precision, 160, use_graph=False)
+        plan.load_estimator(sd)
+        n0 = plan.launch_count()
+        return plan.estimator_forward(x, mask, mu, torch.tensor(0.4)).cpu(), plan.launch_count() - n0
+
+    (fused, n_f), (plain, n_p), (plain2, _), (plain3, _) = run(prec, "1"), run(prec, "0"), run(prec, "0"), run(prec, "0")
+    assert n_p - n_f == 6          # six feed-forwards: two launches became one
+    assert torch.isfinite(fused).all()
+    if t == 4:
+        assert torch.equal(fused, plain)
+        return
+    ref, _ = run("fp32", "0")
+    noise = max(rel_l2(plain2, plain), rel_l2(plain3, plain), rel_l2(plain3, plain2))
+    assert rel_l2(fused, plain) <= 2.0 * noise + 1e-4, (rel_l2(fused, plain), noise)
+    far = max(rel_l2(plain, ref), rel_l2(plain2, ref), rel_l2(plain3, ref))
+    assert rel_l2(fused, ref) <= 1.25 * far + 1e-4, (rel_l2(fused, ref), far)
+
+
 # ------------------------------------------------------------------------------------------ oracle, seeded inputs
 @pytest.mark.parametrize("prec", ["fp32", "fp16"])
 @pytest.mark.parametrize("c_in", [160, 224])
