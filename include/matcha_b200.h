@@ -75,6 +75,14 @@ int mb200_synthesise(mb200_plan* plan, const float* mu, const float* mask, const
 int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
                           int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out);
 
+/* Denoiser.__init__ (matcha/hifigan/denoiser.py:53-57): bias (513,) = |STFT(bias_audio (L,))|[:, frame 0] with
+ * n_fft = win = 1024, hop 256, periodic Hann, center / reflect padding (denoiser.py:26-44).  L > 512. */
+int mb200_denoiser_bias(mb200_plan* plan, const float* bias_audio, int L, float* bias, void* stream);
+/* Denoiser.forward(audio (B, L), strength) (denoiser.py:59-64; called on the vocoder output by cli.py:119-120):
+ * STFT -> max(|S| - strength * bias, 0) with the phase kept -> iSTFT.  out (B, 256 * (L / 256)).  L > 512. */
+int mb200_denoise(mb200_plan* plan, const float* audio, int B, int L, const float* bias, float strength, float* out,
+                  void* stream);
+
 /* One estimator parameter for the training entry point: DEVICE fp32 tensors in the reference layout (SURVEY.md
  * Appendix A), `grad` may be NULL (that gradient is then not computed). */
 typedef struct {

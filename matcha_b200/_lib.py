@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
+    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
 
 
@@ -67,6 +67,8 @@ def load():
         lib.mb200_synthesise_host.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp]
         lib.mb200_compute_loss.argtypes = [vp, ctypes.POINTER(Param), i, ctypes.c_char_p, vp, vp, vp, vp, vp, vp, i, i, f, i,
                                            vp, vp, vp, vp, vp, vp]
+        lib.mb200_denoiser_bias.argtypes = [vp, vp, i, vp, vp]
+        lib.mb200_denoise.argtypes = [vp, vp, i, i, vp, f, vp, vp]
         lib.mb200_launch_count.argtypes = [vp]
         lib.mb200_launch_count.restype = ctypes.c_longlong
         lib.mb200_workspace_bytes.argtypes = [vp]
@@ -259,6 +261,26 @@ class Plan:
                                               _ptr(y), _ptr(v_out), _ptr(dmu), _ptr(dspks), _stream()))
         del keep
         return {"loss": loss, "y": y, "v": v_out, "grads": grads, "dmu": dmu, "dspks": dspks}
+
+    def denoiser_bias(self, bias_audio):
+        """|STFT(bias_audio (L,))|[:, 0] -> (513,)  (hifigan/denoiser.py:53-57)."""
+        a = _dev_f32(bias_audio, self.device).reshape(-1)
+        bias = torch.empty(513, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_denoiser_bias(self.handle, _ptr(a), a.numel(), _ptr(bias), _stream()))
+        return bias
+
+    def denoise(self, audio, bias, strength):
+        """audio (B, L) -> (B, 256 * (L // 256))  (hifigan/denoiser.py:59-64)."""
+        a = _dev_f32(audio, self.device)
+        b, l = a.shape
+        bias = _dev_f32(bias, self.device).reshape(-1)
+        if bias.numel() != 513:
+            raise ValueError("bias must hold 513 bins")
+        out = torch.empty(b, 256 * (l // 256), device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_denoise(self.handle, _ptr(a), b, l, _ptr(bias), float(strength), _ptr(out), _stream()))
+        return out
 
     def set_profiling(self, on):
         check(self.lib.mb200_set_profiling(self.handle, int(on)))

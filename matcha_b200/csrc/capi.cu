@@ -211,6 +211,19 @@ int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, 
                           int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out) {
   return guarded([&] { P(plan)->synthesise_host(mu, mask, z, spks, B, T, n_steps, L, mel_mean, mel_std, mel_out, wav_out); });
 }
+int mb200_denoiser_bias(mb200_plan* plan, const float* bias_audio, int L, float* bias, void* stream) {
+  return guarded([&] {
+    if (!bias_audio || !bias) throw mb::Error("null argument");
+    P(plan)->denoiser_bias(bias_audio, L, bias, static_cast<cudaStream_t>(stream));
+  });
+}
+int mb200_denoise(mb200_plan* plan, const float* audio, int B, int L, const float* bias, float strength, float* out,
+                  void* stream) {
+  return guarded([&] {
+    if (!audio || !bias || !out) throw mb::Error("null argument");
+    P(plan)->denoise(audio, B, L, bias, strength, out, static_cast<cudaStream_t>(stream));
+  });
+}
 int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
                        const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
                        float sigma_min, int backward, float* loss, float* y, float* v, float* dmu, float* dspks,

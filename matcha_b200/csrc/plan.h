@@ -131,6 +131,9 @@ class Plan {
                          const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
                          float sigma_min, float* loss_out, float* y_out, float* v_out, float* dmu, float* dspks, bool backward,
                          cudaStream_t st);
+  // HiFi-GAN bias denoiser (hifigan/denoiser.py:53-64): bias = |STFT(audio)|[:, 0] (513 bins); out (B, 256*(L/256))
+  void denoiser_bias(const float* audio, int L, float* bias, cudaStream_t st);
+  void denoise(const float* audio, int B, int L, const float* bias, float strength, float* out, cudaStream_t st);
   void test_conv1d(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int T, int K, int dil,
                    int stride, bool transposed, float* y, cudaStream_t st);
   void test_attention(const float* qkv, const float* mask, int B, int T, float* out, cudaStream_t st);

@@ -106,3 +106,40 @@ class Generator(nn.Module):
     @torch.no_grad()
     def forward(self, x):
         return self.plan().hifigan_forward(x)
+
+
+class Denoiser(nn.Module):
+    """Drop-in for matcha/hifigan/denoiser.py:10-64 ("removes model bias from audio"): same constructor
+    (`Denoiser(vocoder, filter_length=1024, n_overlap=4, win_length=1024, mode="zeros")`), same `bias_spec` buffer
+    (1, 513, 1) and `forward(audio, strength=0.0005)`.  The bias audio comes from the vocoder passed in (the CUDA
+    Generator above, or anything callable on a (1, 80, 88) mel); STFT, spectral subtraction and iSTFT are one CUDA
+    kernel (csrc/denoiser.cu).  Only the shipped STFT geometry (1024 / hop 256 / 1024) has a kernel."""
+
+    def __init__(self, vocoder, filter_length=1024, n_overlap=4, win_length=1024, mode="zeros"):
+        super().__init__()
+        if (filter_length, n_overlap, win_length) != (1024, 4, 1024):
+            raise NotImplementedError("matcha_b200.Denoiser has a kernel for filter_length = win_length = 1024, n_overlap = 4 only")
+        self.filter_length, self.hop_length, self.win_length = filter_length, filter_length // n_overlap, win_length
+        p = next(vocoder.parameters())
+        dtype, device = p.dtype, p.device
+        if device.type != "cuda":
+            raise RuntimeError("matcha_b200.Denoiser runs on CUDA only (no CPU fallback)")
+        self.device = device
+        if mode == "zeros":
+            mel_input = torch.zeros((1, 80, 88), dtype=dtype, device=device)
+        elif mode == "normal":
+            mel_input = torch.randn((1, 80, 88), dtype=dtype, device=device)
+        else:
+            raise Exception(f"Mode {mode} if not supported")   # message as in denoiser.py:24
+        self._plan = _lib.Plan("fp32", 160, device=device, use_graph=False)
+        with torch.no_grad():
+            bias_audio = vocoder(mel_input).float().squeeze(0)                     # (1, 22528)
+            bias = self._plan.denoiser_bias(bias_audio.reshape(-1))
+        self.register_buffer("bias_spec", bias.reshape(1, 513, 1))
+
+    @torch.inference_mode()
+    def forward(self, audio, strength=0.0005):
+        a = audio.reshape(1, -1) if audio.dim() == 1 else audio    # (L,) comes back as (1, L'): bias_spec broadcasts a batch axis
+        if a.dim() != 2:
+            raise ValueError("audio must be (L,) or (B, L)")
+        return self._plan.denoise(a, self.bias_spec.reshape(-1), strength)

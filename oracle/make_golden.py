@@ -106,6 +106,23 @@ def grad_case(name, c_in, lengths, t_pad, seed):
     print(name, "loss", float(loss), "params", len(grads), "|dmu|", float(mu.grad.norm()))
 
 
+def denoiser_case(name, seed, lengths, strength):
+    """The UNMODIFIED reference Denoiser (hifigan/denoiser.py) over the reference Generator: bias_spec and the denoised
+    audio for a ragged set of seeded waveforms (each its own call: the reference takes (L,) or equal-length (B, L))."""
+    ref_shims.install()
+    from matcha.hifigan.denoiser import Denoiser
+    gen = build_generator(seed, weight_norm=False)
+    den = Denoiser(gen, mode="zeros")
+    g = torch.Generator().manual_seed(seed + 3)
+    audios = [torch.tanh(torch.randn(n, generator=g) * 0.3) for n in lengths]
+    outs = [den(a, strength=strength).clone() for a in audios]
+    batch = torch.stack([torch.tanh(torch.randn(3000, generator=g) * 0.3) for _ in range(3)])
+    fx = dict(kind="denoiser", seed=seed, strength=strength, bias_spec=den.bias_spec.clone(), audios=audios, outs=outs,
+              batch=batch, batch_out=den(batch, strength=strength).clone())
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "bias max", float(den.bias_spec.max()), "out", [tuple(o.shape) for o in outs], tuple(fx["batch_out"].shape))
+
+
 def generator_case(name, b, t, seed, weight_norm):
     g = torch.Generator().manual_seed(seed + 2)
     gen = build_generator(seed, weight_norm)
@@ -158,6 +175,9 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
     torch.set_num_threads(8)
+    if "denoiser" in sys.argv[1:]:
+        denoiser_case("denoiser_ragged", 51, (513, 1024, 2303, 5000), strength=0.05)
+        return
     if "grads" in sys.argv[1:]:            # only the compute_loss gradient fixtures (added after the forward ones)
         grad_case("grad_lj_ragged", 160, (24, 17, 9), 24, seed=41)
         grad_case("grad_vctk_ragged", 224, (36, 20), 36, seed=42)

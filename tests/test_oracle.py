@@ -144,3 +144,18 @@ def test_compute_loss_gradients_match_reference_golden(golden_dir, name):
     assert float((mu.grad - fx["dmu"]).norm() / fx["dmu"].norm()) <= 1e-4
     if spks is not None:
         assert float((spks.grad - fx["dspks"]).norm() / fx["dspks"].norm()) <= 1e-4
+
+
+def test_denoiser_matches_reference_golden(golden_dir):
+    """oracle denoiser (hifigan/denoiser.py restated) against the unmodified reference Denoiser over the reference
+    Generator (oracle/make_golden.py denoiser): bias spectrum and denoised audio, ragged lengths and a batch."""
+    fx = torch.load(os.path.join(golden_dir, "denoiser_ragged.pt"), weights_only=False)
+    sd = weights.generator_state_dict(fx["seed"], weight_norm=False)
+    bias = mo.denoiser_bias(sd)
+    assert bias.shape == (1, 513, 1)
+    assert float((bias - fx["bias_spec"]).abs().max()) <= 1e-4 * float(fx["bias_spec"].abs().max())
+    for a, want in zip(fx["audios"], fx["outs"]):
+        got = mo.denoise(a, fx["bias_spec"], fx["strength"])
+        assert got.shape == want.shape and float((got - want).abs().max()) <= 1e-6
+    got = mo.denoise(fx["batch"], fx["bias_spec"], fx["strength"])
+    assert float((got - fx["batch_out"]).abs().max()) <= 1e-6
