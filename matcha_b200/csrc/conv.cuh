@@ -95,6 +95,14 @@ struct FFGeom {
   const void* resid;             // [rows][256] operand dtype (the attention sub-block's output)
   void* out;                     // [rows][256] operand dtype
   long long* dbg_out;            // developer probe (MB200_FF_DBG): per-CTA cycle counters [grid][16], else null
+  // Optional pre-stage (pre != 0): the attention out-projection, residual and LayerNorm that feed the feed-forward
+  // (transformer.py:266-296): hid = att Wo^T + bo + res_in -> hid_out (= resid above); x = LayerNorm(hid) stays on chip.
+  int pre;
+  const float* bias_o;           // [256]
+  const void* res_in;            // [rows][256] operand dtype (the block's input, transformer.py:276)
+  void* hid_out;                 // [rows][256] operand dtype
+  const float* ln_g;             // [256] norm3 weight / bias
+  const float* ln_b;
 };
 
 struct EpiParams {

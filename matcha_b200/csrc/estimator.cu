@@ -196,6 +196,11 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     e.out0 = buf(QKV); e.out0_ld = 384; e.out0_f32 = dtype == MB200_F32;
     add(conv_op(X.qkv, Src{buf(LN), 256, 256, Tn}, nullptr, B, Tn, e));
     attention(buf(QKV), mask, buf(ATT), Tn);
+    if (ff_supported() && fuse_ff >= 2) {   // out-projection + residual + LayerNorm + feed-forward + residual + mask: one kernel
+      add(ff_op(X.ff1, X.ff2, X.snake_a, X.snake_invb, buf(ATT), buf(HID), mask, out, static_cast<long>(B) * Tn, &X.out, buf(RES),
+                X.ln3_g, X.ln3_b));
+      return;
+    }
     e = epi();
     e.resid = buf(RES); e.resid_ld = 256; e.resid_f32 = dtype == MB200_F32;
     e.out0 = buf(HID); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;

@@ -41,7 +41,8 @@ int ff_fused_smem_bytes() { return 1024 + kFFXBytes + 2 * kFFMidBytes + kFFStage
 template <typename T>
 __global__ void __launch_bounds__(320, 1)
 ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
-                const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ FFGeom g) {
+                const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmWo,
+                const __grid_constant__ FFGeom g) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* x_tile = smem;
@@ -58,7 +59,11 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   uint64_t* mid_empty = bars + 14;     // [2]
   uint64_t* t2_full = bars + 16;       // [1]
   uint64_t* t2_empty = bars + 17;      // [1]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+  uint64_t* att_full = bars + 18;      // [1] pre-stage: attention tile landed in mid[0]
+  uint64_t* att_empty = bars + 19;     // [1] mid[0] no longer read by this tile's M2 (chunk 6)
+  uint64_t* t0_full = bars + 20;       // [1] pre-stage accumulator (TMEM columns 0..255) complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
+  const bool pre = g.pre != 0;         // tmX then maps the attention output [rows][128] instead of the LayerNorm output
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nt_cta = (g.total_tiles > static_cast<int>(blockIdx.x))
@@ -66,7 +71,9 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
-    mbar_init(x_full, 1); mbar_init(x_empty, 1);
+    tma_prefetch_desc(&tmWo);
+    mbar_init(x_full, pre ? 8 : 1); mbar_init(x_empty, 1);
+    mbar_init(att_full, 1); mbar_init(att_empty, 1); mbar_init(t0_full, 1);
     for (int s = 0; s < kFFStages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], 8);
@@ -120,10 +127,30 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         if (++ws == kFFStages) { ws = 0; wph ^= 1; }
       }
     };
-    if (nt_cta > 0) load_X(0);
+    auto load_pre = [&](int n) {   // attention tile [128][128] -> mid[0] (two K chunks), Wo [256][128] -> two ring stages
+      const int tile = blockIdx.x + n * gridDim.x;
+      FW(mbar_wait(att_empty, (n & 1) ^ 1), pw[0]);
+      if (elect_one()) {
+        mbar_expect_tx(att_full, kFFMidBytes);
+        tma_load_3d(mid, &tmX, att_full, 0, tile * 128, 0);
+        tma_load_3d(mid + 16384, &tmX, att_full, 64, tile * 128, 0);
+      }
+      __syncwarp();
+      for (int s = 0; s < 2; ++s) {
+        FW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
+        if (elect_one()) {
+          mbar_expect_tx(&w_full[ws], kFFStage);
+          tma_load_2d(w_ring + ws * kFFStage, &tmWo, &w_full[ws], s * 64, 0);
+        }
+        __syncwarp();
+        if (++ws == kFFStages) { ws = 0; wph ^= 1; }
+      }
+    };
+    if (nt_cta > 0 && !pre) load_X(0);
     for (int n = 0; n < nt_cta; ++n) {
+      if (pre) load_pre(n);
       load_W1(0);
-      for (int j = 1; j < 8; ++j) { load_W1(j); load_W2(j - 1); if (j == 7 && n + 1 < nt_cta) load_X(n + 1); }
+      for (int j = 1; j < 8; ++j) { load_W1(j); load_W2(j - 1); if (j == 7 && n + 1 < nt_cta && !pre) load_X(n + 1); }
       load_W2(7);
     }
     if (g.dbg_out && lane == 0) { long long* o = g.dbg_out + blockIdx.x * 16; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; }
@@ -139,13 +166,32 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
     uint32_t wph = 0;
     long long iw[5] = {0, 0, 0, 0, 0};
     const long long it0 = clock64();
+    uint32_t pe[2] = {0, 0};   // uses of each acc1 slot so far (parity): the pre-stage adds one use per tile
     for (int n = 0; n < nt_cta; ++n) {
+      if (pre) {                // ---- M0: TMEM[0..255] = att . Wo^T   (N = 256, K = 128)
+        FW(mbar_wait(att_full, n & 1), iw[0]);
+        FW(mbar_wait(&t1_empty[0], pe[0] ^ 1), iw[1]); pe[0] ^= 1;
+        FW(mbar_wait(&t1_empty[1], pe[1] ^ 1), iw[1]); pe[1] ^= 1;
+        for (int s = 0; s < 2; ++s) {
+          FW(mbar_wait(&w_full[ws], wph), iw[2]);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t w = w_lo0 + ws * (kFFStage >> 4), a = mid_lo + s * 1024u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_f16_lohi(tmem_base, a + 2 * k, w + 2 * k, desc_hi, idesc2, (s | k) != 0 ? 1u : 0u);
+            umma_commit(&w_empty[ws]);
+            if (s == 1) umma_commit(t0_full);
+          }
+          __syncwarp();
+          if (++ws == kFFStages) { ws = 0; wph ^= 1; }
+        }
+      }
       FW(mbar_wait(x_full, n & 1), iw[0]);
 #pragma unroll 1
       for (int j = 0; j <= 8; ++j) {
         if (j < 8) {            // ---- M1(j): acc1[slot] = x . W1_j^T
           const int jj = n * 8 + j, slot = jj & 1;
-          FW(mbar_wait(&t1_empty[slot], ((jj >> 1) & 1) ^ 1), iw[1]);
+          FW(mbar_wait(&t1_empty[slot], pe[slot] ^ 1), iw[1]); pe[slot] ^= 1;
           const uint32_t dtm = tmem_base + slot * 128;
           for (int s = 0; s < 2; ++s) {
             FW(mbar_wait(&w_full[ws], wph), iw[2]);
@@ -179,7 +225,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 #pragma unroll
               for (int k = 0; k < 4; ++k) umma_f16_lohi(dtm, a + 2 * k, w + 2 * k, desc_hi, idesc2, (jm | s | k) != 0 ? 1u : 0u);
               umma_commit(&w_empty[ws]);
-              if (s == 1) { umma_commit(&mid_empty[ms]); if (jm == 7) umma_commit(t2_full); }
+              if (s == 1) { umma_commit(&mid_empty[ms]); if (jm == 6) umma_commit(att_empty); if (jm == 7) umma_commit(t2_full); }
             }
             __syncwarp();
             if (++ws == kFFStages) { ws = 0; wph ^= 1; }
@@ -204,6 +250,10 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         const float* base = i < 32 ? g.bias1 : (i < 64 ? g.snake_a : (i < 96 ? g.snake_invb : g.bias2));
         asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (i & 31) * 32));
       }
+      if (pre && tid < 24) {
+        const float* base = tid < 8 ? g.bias_o : (tid < 16 ? g.ln_g : g.ln_b);
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (tid & 7) * 32));
+      }
     }
     auto ldp = [&](int col, float4 (&p)[6]) {   // bias, exp(alpha), 1/(exp(beta)+eps) of 8 hidden channels
       p[0] = __ldg(reinterpret_cast<const float4*>(g.bias1 + col)); p[1] = __ldg(reinterpret_cast<const float4*>(g.bias1 + col) + 1);
@@ -212,6 +262,72 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
     };
     for (int n = 0; n < nt_cta; ++n) {
       const int tile = blockIdx.x + n * gridDim.x;
+      if (pre) {
+        // ---- E0: hid = att Wo^T + bo + res -> global; x = LayerNorm(hid) -> x tile (A operand of M1).  Same arithmetic as
+        // the unfused out-projection epilogue: row sums from the fp32 values, normalisation of the ROUNDED stored values.
+        const long row = static_cast<long>(tile) * 128 + r;
+        const bool ok = row < g.rows;
+        const T* rp = reinterpret_cast<const T*>(g.res_in) + row * 256 + half * 128;
+        T* hp = reinterpret_cast<T*>(g.hid_out) + row * 256 + half * 128;
+        uint4 hu[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { hu[i] = make_uint4(0, 0, 0, 0); if (ok) hu[i] = __ldg(reinterpret_cast<const uint4*>(rp) + i); }
+        FW(mbar_wait(t0_full, n & 1), ew[0]);
+        tc_fence_after();
+        FW(mbar_wait(x_empty, (n & 1) ^ 1), ew[1]);          // the previous tile's M1s no longer read the x tile
+        float sm = 0.f, sq = 0.f;
+        {
+          float acc[2][32];
+          tmem_ld_32x32(tlane + half * 128, acc[0]);
+#pragma unroll
+          for (int cb = 0; cb < 4; ++cb) {
+            const int n0 = half * 128 + cb * 32;
+            float4 b2[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) b2[i] = __ldg(reinterpret_cast<const float4*>(g.bias_o + n0) + i);
+            tmem_ld_wait();
+            if (cb + 1 < 4) tmem_ld_32x32(tlane + n0 + 32, acc[(cb + 1) & 1]);
+            const float* a = acc[cb & 1];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float bv[8] = {b2[2 * q].x, b2[2 * q].y, b2[2 * q].z, b2[2 * q].w, b2[2 * q + 1].x, b2[2 * q + 1].y, b2[2 * q + 1].z, b2[2 * q + 1].w};
+              float rv[8], v[8];
+              unpack8<T>(hu[cb * 4 + q], rv);
+#pragma unroll
+              for (int ch = 0; ch < 8; ++ch) { v[ch] = a[8 * q + ch] + bv[ch]; v[ch] += rv[ch]; sm += v[ch]; sq = fmaf(v[ch], v[ch], sq); }
+              hu[cb * 4 + q] = pack8<T>(v);
+              if (ok) *reinterpret_cast<uint4*>(hp + cb * 32 + 8 * q) = hu[cb * 4 + q];
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) { mbar_arrive(&t1_empty[0]); mbar_arrive(&t1_empty[1]); }   // TMEM columns 0..255 are free again
+        // row statistics: the other half of the row belongs to the partner warp (same TMEM lane quarter); mid[0] (the
+        // attention tile, dead once M0 completed) carries the exchange
+        float2* xch = reinterpret_cast<float2*>(mid);
+        xch[half * 128 + r] = make_float2(sm, sq);
+        named_bar_sync(1 + lane_grp, 64);
+        const float2 s0 = xch[r], s1 = xch[128 + r];
+        named_bar_sync(1 + lane_grp, 64);                     // both warps have read before E1 overwrites mid[0]
+        const float mean = (s0.x + s1.x) * (1.f / 256.f);
+        const float rstd = rsqrtf(fmaxf((s0.y + s1.y) * (1.f / 256.f) - mean * mean, 0.f) + 1e-5f);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float ga[8], be[8], xv[8];
+          ldg8f(g.ln_g + half * 128 + 8 * i, ga);
+          ldg8f(g.ln_b + half * 128 + 8 * i, be);
+          unpack8<T>(hu[i], xv);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) xv[ch] = fmaf((xv[ch] - mean) * rstd, ga[ch], be[ch]);
+          uint32_t off = static_cast<uint32_t>(r * 128 + (i & 7) * 16);
+          off ^= ((off >> 7) & 7u) << 4;
+          *reinterpret_cast<uint4*>(x_tile + (half * 2 + (i >> 3)) * 16384 + off) = pack8<T>(xv);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(x_full);
+      }
 #pragma unroll 1
       for (int j = 0; j < 8; ++j) {
         const int jj = n * 8 + j, slot = jj & 1;
@@ -258,7 +374,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       T* op = reinterpret_cast<T*>(g.out) + row * 256 + half * 128;
       uint4 ru[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) { ru[i] = make_uint4(0, 0, 0, 0); if (ok) ru[i] = __ldg(reinterpret_cast<const uint4*>(rp) + i); }
+      for (int i = 0; i < 16; ++i) { ru[i] = make_uint4(0, 0, 0, 0); if (ok) ru[i] = *(reinterpret_cast<const uint4*>(rp) + i); }   // plain loads: with the pre-stage this thread wrote the row itself
       const float m = ok ? __ldg(g.mask + row) : 0.f;
       FW(mbar_wait(t2_full, n & 1), ew[2]);
       tc_fence_after();
@@ -303,7 +419,7 @@ cudaError_t launch_ff_fused(const FFLaunch& L, cudaStream_t st) {
     if (err != cudaSuccess) return err;
     configured = true;
   }
-  kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmX, L.tmW1, L.tmW2, L.g);
+  kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmX, L.tmW1, L.tmW2, L.tmWo, L.g);
   return cudaGetLastError();
 }
 template cudaError_t launch_ff_fused<__nv_bfloat16>(const FFLaunch&, cudaStream_t);

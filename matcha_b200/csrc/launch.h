@@ -30,7 +30,7 @@ struct PairLaunch {
 };
 
 struct FFLaunch {
-  CUtensorMap tmX, tmW1, tmW2;
+  CUtensorMap tmX, tmW1, tmW2, tmWo;   // tmX: LayerNorm output [rows][256], or the attention output [rows][128] with the pre-stage
   FFGeom g;
   int smem_bytes, grid;
 };

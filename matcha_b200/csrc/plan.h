@@ -146,7 +146,8 @@ class Plan {
   int num_sms = 148;
   int tile_policy = 0;      // 1: 256-row x 128-channel tiles for wide layers (halves the weight stream; measured neutral at cfg2); 0: 128 x 256 (MB200_TILE_POLICY)
   int use_pdl = 0;          // programmatic dependent launch for the persistent conv kernel (MB200_PDL=1 enables; measured neutral inside CUDA graphs)
-  int fuse_ff = 1;          // transformer feed-forward as one kernel, hidden activation kept on chip (MB200_FUSE_FF=0: two conv launches)
+  int fuse_ff = 2;          // transformer feed-forward as one kernel, hidden activation kept on chip; 2 = also the attention
+                            // out-projection + residual + LayerNorm as its pre-stage (MB200_FUSE_FF=1: FF only, 0: conv launches)
   int fuse_pairs = 1;       // HiFi-GAN stages 3-4: one kernel per ResBlock step (MB200_FUSE_PAIRS=0: two conv launches)
   bool profiling = false;
   double prof[kProfRegions][kProfKinds][3] = {};   // [region][kind] = {launches, milliseconds, flops}
@@ -172,8 +173,11 @@ class Plan {
   // x + c2(lrelu(c1(in))) as one kernel (resblock_pair.cu); `in` is [B][T][C] dense, e carries c2's residual / outputs
   Launch pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* in, int C, int B, int T, EpiParams e);
   // (SnakeBeta(x W1^T + b1) W2^T + b2 + resid) * mask as one kernel (ff_fused.cu); x, resid, out are [B*L][256] dense
+  // With Wo != nullptr the attention out-projection, its residual and LayerNorm3 run as the kernel's pre-stage:
+  // x is then the attention output [B*L][128], res_in the block input, resid (written here) the post-attention hidden.
   Launch ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, const float* snake_invb, const void* x,
-               const void* resid, const float* mask, void* out, long rows);
+               void* resid, const float* mask, void* out, long rows, const PackedW* Wo = nullptr,
+               const void* res_in = nullptr, const float* ln_g = nullptr, const float* ln_b = nullptr);
   bool ff_supported() const { return fuse_ff && tensor_core() && kernel_version >= 2; }
   bool pair_supported(int C) const { return fuse_pairs && tensor_core() && kernel_version >= 2 && (C == 64 || C == 32); }
   void run(Program& prog, cudaStream_t st);

@@ -460,7 +460,8 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
 }
 
 Launch Plan::ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, const float* snake_invb, const void* x,
-                   const void* resid, const float* mask, void* out, long rows) {
+                   void* resid, const float* mask, void* out, long rows, const PackedW* Wo, const void* res_in,
+                   const float* ln_g, const float* ln_b) {
   if (!ff_supported()) throw Error("ff_op: unsupported configuration");
   if (W1.N != 1024 || W1.K_total != 256 || W2.N != 256 || W2.K_total != 1024 || W1.kc != 64 || W2.kc != 64 ||
       W1.n_phases != 1 || W2.n_phases != 1 || !W1.bias || !W2.bias)
@@ -479,9 +480,19 @@ Launch Plan::ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, c
       std::fprintf(stderr, "[ff probe] rows=%ld tiles=%d\n", rows, L.g.total_tiles);
     }
   }
-  L.tmX = tmap_act(x, 256, static_cast<int>(rows), 1, 64);
   L.tmW1 = tmap_w(W1.w, 256, 1024, 64, 128);
   L.tmW2 = tmap_w(W2.w, 1024, 256, 64, 256);
+  if (Wo) {
+    if (Wo->N != 256 || Wo->K_total != 128 || Wo->kc != 64 || Wo->n_phases != 1 || !Wo->bias || !res_in || !ln_g || !ln_b)
+      throw Error("ff_op: the pre-stage needs a packed 128 -> 256 projection with bias, its residual and LayerNorm parameters");
+    L.g.pre = 1; L.g.bias_o = Wo->bias; L.g.res_in = res_in; L.g.hid_out = resid; L.g.ln_g = ln_g; L.g.ln_b = ln_b;
+    L.tmX = tmap_act(x, 128, static_cast<int>(rows), 1, 64);
+    L.tmWo = tmap_w(Wo->w, 128, 256, 64, 256);
+  } else {
+    L.g.pre = 0;
+    L.tmX = tmap_act(x, 256, static_cast<int>(rows), 1, 64);
+    L.tmWo = L.tmW2;
+  }
   L.smem_bytes = ff_fused_smem_bytes();
   L.grid = std::min(L.g.total_tiles, num_sms);
   const int dtype = cfg.dtype;
@@ -489,7 +500,7 @@ Launch Plan::ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, c
     return dtype == MB200_BF16 ? launch_ff_fused<__nv_bfloat16>(L, st) : launch_ff_fused<__half>(L, st);
   });
   op.kind = 0;
-  op.flops = 2.0 * static_cast<double>(rows) * 2.0 * 256.0 * 1024.0;
+  op.flops = 2.0 * static_cast<double>(rows) * (2.0 * 256.0 * 1024.0 + (Wo ? 256.0 * 128.0 : 0.0));
   return op;
 }
 

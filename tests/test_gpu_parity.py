@@ -157,15 +157,18 @@ def test_fused_resblock_step_is_bit_identical_to_two_conv_launches(monkeypatch, 
 
 
 @pytest.mark.parametrize("prec", ["fp16", "bf16"])
+@pytest.mark.parametrize("mode", ["1", "2"])
 @pytest.mark.parametrize("b,t,lengths", [(1, 4, [3]), (2, 136, [136, 77]), (5, 452, [451, 452, 300, 9, 200])])
-def test_fused_feed_forward_matches_two_conv_launches(monkeypatch, prec, b, t, lengths):
+def test_fused_feed_forward_matches_two_conv_launches(monkeypatch, prec, b, t, lengths, mode):
     """The transformer feed-forward (transformer.py:131-134, SnakeBeta :64-80) runs as one kernel that keeps the 1024-wide
     hidden activation in shared memory (ff_fused.cu): same MMA order, arithmetic and roundings as the ff1 / ff2 conv-GEMM
     launches.  With one warp per GroupNorm group (T = 4) the estimator is deterministic and the outputs must be EQUAL.
     At larger sizes the estimator's GroupNorm partial sums are accumulated with atomics, so two runs of the SAME path
     already differ by half-precision ulps amplified through the network; there the fused path must be no further from the
     two-launch path than that path is from itself, and as close to the fp32 path.  Sizes: a single partial tile, tiles
-    that straddle two utterances (the fused kernel tiles the flat B*L rows), several row tiles per CTA at cfg2's length."""
+    that straddle two utterances (the fused kernel tiles the flat B*L rows), several row tiles per CTA at cfg2's length.
+    mode 2 (the default) also runs the attention out-projection + residual + LayerNorm3 as the kernel's pre-stage: the
+    LayerNorm row sums are then added in another order, so that mode is held to the closeness bar at every size."""
     sd = weights.estimator_state_dict(160, seed=5)
     g = torch.Generator().manual_seed(3)
     x, mu = torch.randn(b, 80, t, generator=g), torch.randn(b, 80, t, generator=g)
@@ -178,11 +181,14 @@ def test_fused_feed_forward_matches_two_conv_launches(monkeypatch, prec, b, t, l
         n0 = plan.launch_count()
         return plan.estimator_forward(x, mask, mu, torch.tensor(0.4)).cpu(), plan.launch_count() - n0
 
-    (fused, n_f), (plain, n_p), (plain2, _), (plain3, _) = run(prec, "1"), run(prec, "0"), run(prec, "0"), run(prec, "0")
-    assert n_p - n_f == 6          # six feed-forwards: two launches became one
+    (fused, n_f), (plain, n_p), (plain2, _), (plain3, _) = run(prec, mode), run(prec, "0"), run(prec, "0"), run(prec, "0")
+    assert n_p - n_f == (6 if mode == "1" else 12)   # six transformer blocks: two (three) launches became one
     assert torch.isfinite(fused).all()
     if t == 4:
-        assert torch.equal(fused, plain)
+        if mode == "1":
+            assert torch.equal(fused, plain)
+        else:
+            assert rel_l2(fused, plain) <= (3e-3 if prec == "fp16" else 2e-2), rel_l2(fused, plain)
         return
     ref, _ = run("fp32", "0")
     noise = max(rel_l2(plain2, plain), rel_l2(plain3, plain), rel_l2(plain3, plain2))
