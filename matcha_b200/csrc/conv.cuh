@@ -105,6 +105,26 @@ struct FFGeom {
   const float* ln_b;
 };
 
+// Geometry / parameters of the fused res_conv + GroupNorm/Mish + LayerNorm1 + QKV kernel (resqkv_fused.cu).
+struct RQGeom {
+  long rows;                     // B * L (flat frame index)
+  int L;                         // frames per utterance (GroupNorm statistics are per utterance)
+  int total_tiles;               // ceil(rows / 128)
+  int nk0, nk1;                  // 64-channel K chunks of the first / second (channel-concat) source
+  const float* bias;             // res_conv bias [256]
+  const void* gn_raw;            // block2 conv output [rows][256], operand dtype
+  const float* gn_stats;         // [B][8][2] sum, sum of squares
+  const float* gn_gamma;         // [256]
+  const float* gn_beta;
+  float gn_inv_count;            // 1 / (32 L)
+  const float* mask;             // [rows]
+  void* res_out;                 // [rows][256] operand dtype
+  const float* ln_g;             // norm1 weight / bias [256]
+  const float* ln_b;
+  void* qkv_out;                 // [rows][384] operand dtype
+  long long* dbg_out;            // developer probe (MB200_RQ_DBG): per-CTA timestamps of the epilogue's phases, else null
+};
+
 struct EpiParams {
   int T_o;                 // output rows per batch (T_out * o_mul)
   int o_mul;               // output row = t * o_mul + phase * o_phase_step

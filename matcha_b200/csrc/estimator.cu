@@ -181,6 +181,10 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     e = epi();
     e.out0 = buf(RAW2); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32; e.stats_out = st2;
     add(conv_op(R.conv2, Src{buf(H1), 256, 256, Tn}, nullptr, B, Tn, e));
+    if (rq_supported()) {   // res_conv + GroupNorm/Mish + LayerNorm1 + QKV projection: one kernel (RES and QKV written)
+      add(resqkv_op(R.res, X.qkv, s0, s1, buf(RAW2), st2, R.gn2_g, R.gn2_b, mask, buf(RES), X.ln1_g, X.ln1_b, buf(QKV), B, Tn));
+      return;
+    }
     e = epi();
     e.gn_raw = buf(RAW2); e.gn_ld = 256; e.gn_stats = st2; e.gn_gamma = R.gn2_g; e.gn_beta = R.gn2_b;
     e.gn_inv_count = 1.f / (32.f * Tn); e.mask = mask;
@@ -193,8 +197,10 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   auto transformer = [&](int x, int Tn, const float* mask, void* out) {
     const TransformerW& X = est_.tr[x];
     EpiParams e = epi();
-    e.out0 = buf(QKV); e.out0_ld = 384; e.out0_f32 = dtype == MB200_F32;
-    add(conv_op(X.qkv, Src{buf(LN), 256, 256, Tn}, nullptr, B, Tn, e));
+    if (!rq_supported()) {   // otherwise the ResNet block's fused kernel has already written QKV
+      e.out0 = buf(QKV); e.out0_ld = 384; e.out0_f32 = dtype == MB200_F32;
+      add(conv_op(X.qkv, Src{buf(LN), 256, 256, Tn}, nullptr, B, Tn, e));
+    }
     attention(buf(QKV), mask, buf(ATT), Tn);
     if (ff_supported() && fuse_ff >= 2) {   // out-projection + residual + LayerNorm + feed-forward + residual + mask: one kernel
       add(ff_op(X.ff1, X.ff2, X.snake_a, X.snake_invb, buf(ATT), buf(HID), mask, out, static_cast<long>(B) * Tn, &X.out, buf(RES),

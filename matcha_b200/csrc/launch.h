@@ -34,6 +34,13 @@ struct FFLaunch {
   FFGeom g;
   int smem_bytes, grid;
 };
+struct RQLaunch {
+  CUtensorMap tmA0, tmA1, tmWres, tmWqkv;
+  RQGeom g;
+  int smem_bytes, grid;
+};
+int resqkv_fused_smem_bytes();
+template <typename T> cudaError_t launch_resqkv_fused(const RQLaunch& L, cudaStream_t st);
 int ff_fused_smem_bytes();
 template <typename T> cudaError_t launch_ff_fused(const FFLaunch& L, cudaStream_t st);
 template <typename T> cudaError_t launch_resblock_pair(const PairLaunch& L, cudaStream_t st);

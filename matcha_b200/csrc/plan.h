@@ -148,6 +148,7 @@ class Plan {
   int use_pdl = 0;          // programmatic dependent launch for the persistent conv kernel (MB200_PDL=1 enables; measured neutral inside CUDA graphs)
   int fuse_ff = 2;          // transformer feed-forward as one kernel, hidden activation kept on chip; 2 = also the attention
                             // out-projection + residual + LayerNorm as its pre-stage (MB200_FUSE_FF=1: FF only, 0: conv launches)
+  int fuse_rq = 1;          // res_conv + GroupNorm/Mish + LayerNorm1 + QKV as one kernel (MB200_FUSE_RQ=0: two conv launches)
   int fuse_pairs = 1;       // HiFi-GAN stages 3-4: one kernel per ResBlock step (MB200_FUSE_PAIRS=0: two conv launches)
   bool profiling = false;
   double prof[kProfRegions][kProfKinds][3] = {};   // [region][kind] = {launches, milliseconds, flops}
@@ -178,6 +179,12 @@ class Plan {
   Launch ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, const float* snake_invb, const void* x,
                void* resid, const float* mask, void* out, long rows, const PackedW* Wo = nullptr,
                const void* res_in = nullptr, const float* ln_g = nullptr, const float* ln_b = nullptr);
+  // res = x Wres^T + b + mish(GN(raw2)) * mask ; qkv = LayerNorm1(res) Wqkv^T as one kernel (resqkv_fused.cu);
+  // sources are dense [B][L][ld] buffers tiled over the flat B*L rows
+  Launch resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const Src* s1, const void* gn_raw, const float* gn_stats,
+                   const float* gn_gamma, const float* gn_beta, const float* mask, void* res_out, const float* ln_g,
+                   const float* ln_b, void* qkv_out, int B, int L);
+  bool rq_supported() const { return fuse_rq && tensor_core() && kernel_version >= 2; }
   bool ff_supported() const { return fuse_ff && tensor_core() && kernel_version >= 2; }
   bool pair_supported(int C) const { return fuse_pairs && tensor_core() && kernel_version >= 2 && (C == 64 || C == 32); }
   void run(Program& prog, cudaStream_t st);

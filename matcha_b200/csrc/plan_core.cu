@@ -42,6 +42,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_KERNEL")) kernel_version = std::atoi(v);
   if (const char* v = std::getenv("MB200_FUSE_PAIRS")) fuse_pairs = std::atoi(v);
   if (const char* v = std::getenv("MB200_FUSE_FF")) fuse_ff = std::atoi(v);
+  if (const char* v = std::getenv("MB200_FUSE_RQ")) fuse_rq = std::atoi(v);
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -501,6 +502,47 @@ Launch Plan::ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, c
   });
   op.kind = 0;
   op.flops = 2.0 * static_cast<double>(rows) * (2.0 * 256.0 * 1024.0 + (Wo ? 256.0 * 128.0 : 0.0));
+  return op;
+}
+
+Launch Plan::resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const Src* s1, const void* gn_raw,
+                       const float* gn_stats, const float* gn_gamma, const float* gn_beta, const float* mask, void* res_out,
+                       const float* ln_g, const float* ln_b, void* qkv_out, int B, int L) {
+  if (!rq_supported()) throw Error("resqkv_op: unsupported configuration");
+  const int kres = s0.ch + (s1 ? s1->ch : 0);
+  if (Wres.N != 256 || Wres.K_total != kres || Wres.n_taps != 1 || Wres.kc != 64 || Wres.ntile != 256 || !Wres.bias ||
+      Wqkv.N != 384 || Wqkv.K_total != 256 || Wqkv.kc != 64 || Wqkv.bias || s0.ch % 64 || (s1 && s1->ch % 64) || kres > 512)
+    throw Error("resqkv_op: packed weights do not match a 1x1 res_conv (K <= 512) followed by a 256 -> 384 projection");
+  if (s0.rows != L || (s1 && s1->rows != L)) throw Error("resqkv_op: sources must be dense [B][L][ld] buffers");
+  RQLaunch Lq{};
+  RQGeom& g = Lq.g;
+  g.rows = static_cast<long>(B) * L; g.L = L;
+  g.total_tiles = static_cast<int>((g.rows + 127) / 128);
+  g.nk0 = s0.ch / 64; g.nk1 = s1 ? s1->ch / 64 : 0;
+  g.bias = Wres.bias; g.gn_raw = gn_raw; g.gn_stats = gn_stats; g.gn_gamma = gn_gamma; g.gn_beta = gn_beta;
+  g.gn_inv_count = 1.f / (32.f * L);
+  g.mask = mask; g.res_out = res_out; g.ln_g = ln_g; g.ln_b = ln_b; g.qkv_out = qkv_out;
+  g.dbg_out = nullptr;
+  if (const char* v = std::getenv("MB200_RQ_DBG")) {   // developer probe: instrument the n-th op built
+    static int built = 0;
+    if (built++ == std::atoi(v)) {
+      g.dbg_out = static_cast<long long*>(dalloc(148 * 16 * sizeof(long long)));
+      probe_out = g.dbg_out;
+      std::fprintf(stderr, "[rq probe] rows=%ld tiles=%d nk=%d\n", g.rows, g.total_tiles, g.nk0 + g.nk1);
+    }
+  }
+  Lq.tmA0 = tmap_act(s0.p, s0.ld, static_cast<int>(g.rows), 1, 64);
+  Lq.tmA1 = s1 ? tmap_act(s1->p, s1->ld, static_cast<int>(g.rows), 1, 64) : Lq.tmA0;
+  Lq.tmWres = Wres.tm;
+  Lq.tmWqkv = tmap_w(Wqkv.w, 256, 384, 64, 128);
+  Lq.smem_bytes = resqkv_fused_smem_bytes();
+  Lq.grid = std::min(g.total_tiles, num_sms);
+  const int dtype = cfg.dtype;
+  Launch op([Lq, dtype](cudaStream_t st) -> cudaError_t {
+    return dtype == MB200_BF16 ? launch_resqkv_fused<__nv_bfloat16>(Lq, st) : launch_resqkv_fused<__half>(Lq, st);
+  });
+  op.kind = 0;
+  op.flops = 2.0 * static_cast<double>(g.rows) * (256.0 * Wres.k_real + 384.0 * 256.0);
   return op;
 }
 
