@@ -23,6 +23,7 @@
 #include "epilogue3.cuh"
 #include "launch.h"
 #include "ptx.cuh"
+#include "rowio.cuh"
 
 namespace mb {
 
@@ -267,39 +268,46 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         // the unfused out-projection epilogue: row sums from the fp32 values, normalisation of the ROUNDED stored values.
         const long row = static_cast<long>(tile) * 128 + r;
         const bool ok = row < g.rows;
-        const T* rp = reinterpret_cast<const T*>(g.res_in) + row * 256 + half * 128;
-        T* hp = reinterpret_cast<T*>(g.hid_out) + row * 256 + half * 128;
-        uint4 hu[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) { hu[i] = make_uint4(0, 0, 0, 0); if (ok) hu[i] = __ldg(reinterpret_cast<const uint4*>(rp) + i); }
+        // Rolled loops on purpose: as straight-line code this once-per-tile stage is bound by instruction fetch
+        // (resqkv_fused.cu's epilogue, measured).  The rounded hidden values go to HBM and, un-normalised, into the x tile,
+        // where the LayerNorm pass normalises them in place (same thread, same addresses).
+        // Global traffic is staged through the x tile (rowio.cuh): coalesced loads of the residual rows, coalesced stores
+        // of the hidden rows; row-per-lane global accesses touch 32 lines per instruction and were the bottleneck.
+        const long row0 = static_cast<long>(tile) * 128;
+        const int r0 = lane_grp * 32;
+        FW(mbar_wait(x_empty, (n & 1) ^ 1), ew[1]);          // the previous tile's M1s no longer read the x tile
+        warp_rows_g2s<T>(x_tile, reinterpret_cast<const T*>(g.res_in), row0, g.rows, r0, half, lane);
+        __syncwarp();
         FW(mbar_wait(t0_full, n & 1), ew[0]);
         tc_fence_after();
-        FW(mbar_wait(x_empty, (n & 1) ^ 1), ew[1]);          // the previous tile's M1s no longer read the x tile
         float sm = 0.f, sq = 0.f;
-        {
-          float acc[2][32];
-          tmem_ld_32x32(tlane + half * 128, acc[0]);
+#pragma unroll 1
+        for (int cb = 0; cb < 4; ++cb) {
+          const int n0 = half * 128 + cb * 32;
+          float acc[32];
+          tmem_ld_32x32(tlane + n0, acc);
+          uint4* xp[4];
+          uint4 cur[4];
 #pragma unroll
-          for (int cb = 0; cb < 4; ++cb) {
-            const int n0 = half * 128 + cb * 32;
-            float4 b2[8];
+          for (int q = 0; q < 4; ++q) {
+            const int i = cb * 4 + q;
+            xp[q] = reinterpret_cast<uint4*>(x_tile + (half * 2 + (i >> 3)) * 16384 + xtile_off(r, i & 7));
+            cur[q] = *xp[q];
+          }
+          tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 8; ++i) b2[i] = __ldg(reinterpret_cast<const float4*>(g.bias_o + n0) + i);
-            tmem_ld_wait();
-            if (cb + 1 < 4) tmem_ld_32x32(tlane + n0 + 32, acc[(cb + 1) & 1]);
-            const float* a = acc[cb & 1];
+          for (int q = 0; q < 4; ++q) {
+            float bv[8], rv[8], v[8];
+            ldg8f(g.bias_o + n0 + 8 * q, bv);
+            unpack8<T>(cur[q], rv);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const float bv[8] = {b2[2 * q].x, b2[2 * q].y, b2[2 * q].z, b2[2 * q].w, b2[2 * q + 1].x, b2[2 * q + 1].y, b2[2 * q + 1].z, b2[2 * q + 1].w};
-              float rv[8], v[8];
-              unpack8<T>(hu[cb * 4 + q], rv);
-#pragma unroll
-              for (int ch = 0; ch < 8; ++ch) { v[ch] = a[8 * q + ch] + bv[ch]; v[ch] += rv[ch]; sm += v[ch]; sq = fmaf(v[ch], v[ch], sq); }
-              hu[cb * 4 + q] = pack8<T>(v);
-              if (ok) *reinterpret_cast<uint4*>(hp + cb * 32 + 8 * q) = hu[cb * 4 + q];
-            }
+            for (int ch = 0; ch < 8; ++ch) { v[ch] = acc[8 * q + ch] + bv[ch]; v[ch] += rv[ch]; sm += v[ch]; sq = fmaf(v[ch], v[ch], sq); }
+            *xp[q] = pack8<T>(v);
           }
         }
+        __syncwarp();
+        warp_rows_s2g<T>(x_tile, reinterpret_cast<T*>(g.hid_out), row0, g.rows, r0, half, lane);
+        __syncwarp();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) { mbar_arrive(&t1_empty[0]); mbar_arrive(&t1_empty[1]); }   // TMEM columns 0..255 are free again
@@ -312,17 +320,18 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         named_bar_sync(1 + lane_grp, 64);                     // both warps have read before E1 overwrites mid[0]
         const float mean = (s0.x + s1.x) * (1.f / 256.f);
         const float rstd = rsqrtf(fmaxf((s0.y + s1.y) * (1.f / 256.f) - mean * mean, 0.f) + 1e-5f);
-#pragma unroll
+#pragma unroll 2
         for (int i = 0; i < 16; ++i) {
           float ga[8], be[8], xv[8];
           ldg8f(g.ln_g + half * 128 + 8 * i, ga);
           ldg8f(g.ln_b + half * 128 + 8 * i, be);
-          unpack8<T>(hu[i], xv);
-#pragma unroll
-          for (int ch = 0; ch < 8; ++ch) xv[ch] = fmaf((xv[ch] - mean) * rstd, ga[ch], be[ch]);
           uint32_t off = static_cast<uint32_t>(r * 128 + (i & 7) * 16);
           off ^= ((off >> 7) & 7u) << 4;
-          *reinterpret_cast<uint4*>(x_tile + (half * 2 + (i >> 3)) * 16384 + off) = pack8<T>(xv);
+          uint4* xp = reinterpret_cast<uint4*>(x_tile + (half * 2 + (i >> 3)) * 16384 + off);
+          unpack8<T>(*xp, xv);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) xv[ch] = fmaf((xv[ch] - mean) * rstd, ga[ch], be[ch]);
+          *xp = pack8<T>(xv);
         }
         fence_proxy_async();
         __syncwarp();
@@ -370,32 +379,76 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       // is requested before the accumulator barrier, so its latency hides behind the last chunk's MMAs.
       const long row = static_cast<long>(tile) * 128 + r;
       const bool ok = row < g.rows;
+      const float m = ok ? __ldg(g.mask + row) : 0.f;
+      if (pre) {
+        // The x tile is idle once the last M1 has completed (nothing refills it before the next tile's E0), so the residual
+        // rows and the output rows are staged through it for coalesced global traffic (rowio.cuh).  The residual is the
+        // hidden tensor E0 stored with the same lane -> address mapping, hence plain (coherent) loads.
+        const long row0 = static_cast<long>(tile) * 128;
+        const int r0 = lane_grp * 32;
+        FW(mbar_wait(x_empty, n & 1), ew[1]);
+        warp_rows_g2s<T, false>(x_tile, reinterpret_cast<const T*>(g.resid), row0, g.rows, r0, half, lane);
+        __syncwarp();
+        FW(mbar_wait(t2_full, n & 1), ew[2]);
+        tc_fence_after();
+#pragma unroll 1
+        for (int cb = 0; cb < 4; ++cb) {
+          const int n0 = half * 128 + cb * 32;
+          float acc[32];
+          tmem_ld_32x32(tlane + 256 + n0, acc);
+          uint4* xp[4];
+          uint4 cur[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int i = cb * 4 + q;
+            xp[q] = reinterpret_cast<uint4*>(x_tile + (half * 2 + (i >> 3)) * 16384 + xtile_off(r, i & 7));
+            cur[q] = *xp[q];
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float bv[8], rv[8], v[8];
+            ldg8f(g.bias2 + n0 + 8 * q, bv);
+            unpack8<T>(cur[q], rv);
+#pragma unroll
+            for (int ch = 0; ch < 8; ++ch) { v[ch] = acc[8 * q + ch] + bv[ch]; v[ch] += rv[ch]; v[ch] *= m; }
+            *xp[q] = pack8<T>(v);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(t2_empty);     // the accumulators are read: the next tile's MMAs may start
+        warp_rows_s2g<T>(x_tile, reinterpret_cast<T*>(g.out), row0, g.rows, r0, half, lane);
+        __syncwarp();
+        continue;
+      }
       const T* rp = reinterpret_cast<const T*>(g.resid) + row * 256 + half * 128;
       T* op = reinterpret_cast<T*>(g.out) + row * 256 + half * 128;
-      uint4 ru[16];
+      uint4 ru[4];   // plain loads: with the pre-stage this thread wrote the row itself
 #pragma unroll
-      for (int i = 0; i < 16; ++i) { ru[i] = make_uint4(0, 0, 0, 0); if (ok) ru[i] = *(reinterpret_cast<const uint4*>(rp) + i); }   // plain loads: with the pre-stage this thread wrote the row itself
-      const float m = ok ? __ldg(g.mask + row) : 0.f;
+      for (int q = 0; q < 4; ++q) { ru[q] = make_uint4(0, 0, 0, 0); if (ok) ru[q] = *(reinterpret_cast<const uint4*>(rp) + q); }
       FW(mbar_wait(t2_full, n & 1), ew[2]);
       tc_fence_after();
-      float acc[2][32];
-      tmem_ld_32x32(tlane + 256 + half * 128, acc[0]);
-#pragma unroll
-      for (int cb = 0; cb < 4; ++cb) {
+#pragma unroll 1
+      for (int cb = 0; cb < 4; ++cb) {      // rolled: see E0
         const int n0 = half * 128 + cb * 32;
-        float4 b2[8];
+        float acc[32];
+        tmem_ld_32x32(tlane + 256 + n0, acc);
+        uint4 cur[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) b2[i] = __ldg(reinterpret_cast<const float4*>(g.bias2 + n0) + i);
+        for (int q = 0; q < 4; ++q) cur[q] = ru[q];
+        if (cb + 1 < 4) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) { ru[q] = make_uint4(0, 0, 0, 0); if (ok) ru[q] = *(reinterpret_cast<const uint4*>(rp) + (cb + 1) * 4 + q); }
+        }
         tmem_ld_wait();
-        if (cb + 1 < 4) tmem_ld_32x32(tlane + 256 + n0 + 32, acc[(cb + 1) & 1]);
-        const float* a = acc[cb & 1];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const float bv[8] = {b2[2 * q].x, b2[2 * q].y, b2[2 * q].z, b2[2 * q].w, b2[2 * q + 1].x, b2[2 * q + 1].y, b2[2 * q + 1].z, b2[2 * q + 1].w};
-          float rv[8], v[8];
-          unpack8<T>(ru[cb * 4 + q], rv);
+          float bv[8], rv[8], v[8];
+          ldg8f(g.bias2 + n0 + 8 * q, bv);
+          unpack8<T>(cur[q], rv);
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) { v[ch] = a[8 * q + ch] + bv[ch]; v[ch] += rv[ch]; v[ch] *= m; }
+          for (int ch = 0; ch < 8; ++ch) { v[ch] = acc[8 * q + ch] + bv[ch]; v[ch] += rv[ch]; v[ch] *= m; }
           if (ok) *reinterpret_cast<uint4*>(op + cb * 32 + 8 * q) = pack8<T>(v);
         }
       }

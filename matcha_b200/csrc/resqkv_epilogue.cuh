@@ -4,6 +4,7 @@
 #include "conv.cuh"
 #include "epilogue3.cuh"
 #include "ptx.cuh"
+#include "rowio.cuh"
 
 namespace mb {
 
@@ -29,14 +30,15 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
     // executed once per tile, and the warps ran at 4.8 cycles per instruction on instruction fetch (ncu source view: samples
     // spread evenly over every line).  One 32-channel GroupNorm group per iteration; the rounded values go to HBM (res) and,
     // un-normalised, into the x tile, where the LayerNorm pass picks them up again (same thread, same addresses).
-    const T* rawp = reinterpret_cast<const T*>(g.gn_raw) + row * 256 + half * 128;
-    T* resp = reinterpret_cast<T*>(g.res_out) + row * 256 + half * 128;
+    // Global traffic is staged through the x tile (rowio.cuh): the block2 conv output arrives there with coalesced loads,
+    // the rounded result leaves from there with coalesced stores, and the LayerNorm pass then normalises it in place.
+    const long row0 = static_cast<long>(tile) * 128;
+    const int r0 = lane_grp * 32;
+    warp_rows_g2s<T>(x_tile, reinterpret_cast<const T*>(g.gn_raw), row0, g.rows, r0, half, lane);
     const float m = ok ? __ldg(g.mask + row) : 0.f;
     const int b = ok ? static_cast<int>(row / g.L) : 0;
     const float* st = g.gn_stats + (b * 8 + half * 4) * 2;
-    uint4 ru[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) { ru[q] = make_uint4(0, 0, 0, 0); if (ok) ru[q] = __ldg(reinterpret_cast<const uint4*>(rawp) + q); }
+    __syncwarp();
     if (probe && n == 0) po[0] = clock64() - pt0;
     mbar_wait(t0_full, n & 1);
     tc_fence_after();
@@ -50,12 +52,13 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
       const float gsum = __ldg(st + 2 * cb), gsq = __ldg(st + 2 * cb + 1);
       const float gmean = gsum * g.gn_inv_count;
       const float grstd = rsqrtf(fmaxf(gsq * g.gn_inv_count - gmean * gmean, 0.f) + 1e-5f);
+      uint4* xp[4];
       uint4 cur[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) cur[q] = ru[q];
-      if (cb + 1 < 4) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) { ru[q] = make_uint4(0, 0, 0, 0); if (ok) ru[q] = __ldg(reinterpret_cast<const uint4*>(rawp) + (cb + 1) * 4 + q); }
+      for (int q = 0; q < 4; ++q) {
+        const int i = cb * 4 + q;                            // 16-byte unit of this half-row
+        xp[q] = reinterpret_cast<uint4*>(x_tile + (half * 2 + (i >> 3)) * 16384 + xtile_off(r, i & 7));
+        cur[q] = *xp[q];
       }
       tmem_ld_wait();
 #pragma unroll
@@ -74,14 +77,12 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
           sm += v[ch];
           sq = fmaf(v[ch], v[ch], sq);
         }
-        const uint4 hv = pack8<T>(v);
-        if (ok) *reinterpret_cast<uint4*>(resp + cb * 32 + 8 * q) = hv;
-        const int i = cb * 4 + q;                            // 16-byte unit of this half-row
-        uint32_t off = static_cast<uint32_t>(r * 128 + (i & 7) * 16);
-        off ^= ((off >> 7) & 7u) << 4;
-        *reinterpret_cast<uint4*>(x_tile + (half * 2 + (i >> 3)) * 16384 + off) = hv;
+        *xp[q] = pack8<T>(v);
       }
     }
+    __syncwarp();
+    warp_rows_s2g<T>(x_tile, reinterpret_cast<T*>(g.res_out), row0, g.rows, r0, half, lane);
+    __syncwarp();
     if (probe && n == 0) po[2] = clock64() - pt0;
     // LayerNorm1 row statistics: the other half of the row belongs to the partner warp (same TMEM lane quarter)
     xch[half * 128 + r] = make_float2(sm, sq);
@@ -109,22 +110,36 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
     if (lane == 0) mbar_arrive(x_full);
     if (probe && n == 0) po[3] = clock64() - pt0;
     // ---- E1: q | k | v columns [192 half, +192) of this lane's row
-    T* qp = reinterpret_cast<T*>(g.qkv_out) + row * 384 + half * 192;
+    // q | k | v columns [192 half, +192) of this warp's 32 rows, in two rounds of 96 columns staged through a warp-private
+    // slice of the x tile (free once M1 has completed; pitch 208 B keeps the row-per-lane writes conflict-free)
     mbar_wait(t1_full, n & 1);
     tc_fence_after();
     if (probe && n == 0) po[4] = clock64() - pt0;
+    uint8_t* stg = x_tile + (warp - 2) * 8192;
 #pragma unroll 1
-    for (int cb = 0; cb < 6; ++cb) {
-      float acc[32];
-      tmem_ld_32x32(tlane + half * 192 + cb * 32, acc);
-      tmem_ld_wait();
+    for (int rd = 0; rd < 2; ++rd) {
+#pragma unroll 1
+      for (int cb = 0; cb < 3; ++cb) {
+        float acc[32];
+        tmem_ld_32x32(tlane + half * 192 + rd * 96 + cb * 32, acc);
+        tmem_ld_wait();
 #pragma unroll
-      for (int q = 0; q < 4; ++q)
-        if (ok) *reinterpret_cast<uint4*>(qp + cb * 32 + 8 * q) = pack8<T>(acc + 8 * q);
+        for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(stg + lane * 208 + (cb * 4 + q) * 16) = pack8<T>(acc + 8 * q);
+      }
+      __syncwarp();
+#pragma unroll
+      for (int it = 0; it < 12; ++it) {
+        const int idx = it * 32 + lane, rr = idx / 12, u = idx % 12;
+        const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 208 + u * 16);
+        const long grow = row0 + r0 + rr;
+        if (grow < g.rows) *(reinterpret_cast<uint4*>(reinterpret_cast<T*>(g.qkv_out) + grow * 384 + half * 192 + rd * 96) + u) = v;
+      }
+      __syncwarp();
     }
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(t_free);
+    if (n + 1 < nt_cta) named_bar_sync(5, 256);   // every warp's staging slice is drained before the next tile's rows land in the x tile
     if (probe && n == 0) po[5] = clock64() - pt0;
   }
   if (probe) po[6] = clock64() - pt0;
