@@ -252,7 +252,7 @@ def run_ours(args):
         except (OSError, KeyError, ValueError):
             pass
         roofline = {"bound": "tensor", "achieved": achieved,
-                    "kernel": "tcgen05 conv-GEMM family: conv_gemm_umma2_kernel + resblock_pair_kernel + ff_fused_kernel (all instantiations)",
+                    "kernel": "tcgen05 conv-GEMM family: conv_gemm_umma2_kernel + resblock_pair_kernel + ff_fused_kernel + resqkv_fused_kernel (all instantiations)",
                     "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": traffic,
                     "traffic_unit": "bytes/launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_src,
                     "peak_source": peaks["source"], "launches_per_step": g_n, "avg_launch_us": g_ms * 1e3 / max(g_n, 1),

@@ -13,7 +13,7 @@ import re
 import sys
 
 TENSOR = "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"
-GEMM_FAMILY = ("conv_gemm_umma2_kernel", "resblock_pair_kernel", "ff_fused_kernel")
+GEMM_FAMILY = ("conv_gemm_umma2_kernel", "resblock_pair_kernel", "ff_fused_kernel", "resqkv_fused_kernel")
 
 
 def short(name):
@@ -57,11 +57,11 @@ def main():
     n = sum(a["n"] for a in fam)
     ns = sum(a["ns"] for a in fam)
     dram = sum(a["dram"] for a in fam)
-    lines += ["", "tcgen05 conv-GEMM family (conv_gemm_umma2_kernel + resblock_pair_kernel + ff_fused_kernel, all instantiations): %d launches, %.3f ms = %.1f%% of "
+    lines += ["", "tcgen05 conv-GEMM family (conv_gemm_umma2_kernel + resblock_pair_kernel + ff_fused_kernel + resqkv_fused_kernel, all instantiations): %d launches, %.3f ms = %.1f%% of "
               "the step, DRAM traffic %.2f MB per launch (%.2f GB per step)" % (n, ns / 1e6, 100 * ns / total, dram / n / 1e6, dram / 1e9)]
     open(out + "_summary.txt", "w").write("\n".join(lines) + "\n")
     json.dump({"source": out + "_summary.txt (ncu dram__bytes_read.sum + dram__bytes_write.sum, one eager cfg2 pass)",
-               "kernel": "conv_gemm_umma2_kernel + resblock_pair_kernel + ff_fused_kernel (all instantiations)", "launches_per_step": n,
+               "kernel": "conv_gemm_umma2_kernel + resblock_pair_kernel + ff_fused_kernel + resqkv_fused_kernel (all instantiations)", "launches_per_step": n,
                "dram_bytes_per_launch": dram / n, "dram_bytes_per_step": dram, "share_of_step_time": ns / total},
               open("profiles/r01_dram_traffic.json", "w"), indent=1)
     print("\n".join(lines))
