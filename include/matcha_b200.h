@@ -83,6 +83,15 @@ int mb200_denoiser_bias(mb200_plan* plan, const float* bias_audio, int L, float*
 int mb200_denoise(mb200_plan* plan, const float* audio, int B, int L, const float* bias, float strength, float* out,
                   void* stream);
 
+/* Length regulation on the synthesis path (matcha/models/matcha_tts.py:118-131): replaces
+ * `attn = generate_path(w_ceil, x_mask (x) y_mask)` (matcha/utils/model.py:29-41) and the dense
+ * `mu_y = matmul(attn^T, mu_x^T)^T` by a prefix sum + gather.  All DEVICE pointers, fp32, reference layouts:
+ * mu_x (B, C, Lx), w (B, Lx) frames per token (w_ceil * length_scale), x_mask (B, Lx) 0/1, y_lengths (B,) int64,
+ * outputs mu_y (B, C, T), attn (B, Lx, T) (may be NULL), y_mask (B, T) (may be NULL); cum (B, Lx) is workspace that
+ * returns the fp32 prefix sums.  Frames at or past y_lengths[b] and frames no token owns are zero.  No plan needed. */
+int mb200_length_regulate(const float* mu_x, const float* w, const float* x_mask, const long long* y_lengths, int B, int C,
+                          int Lx, int T, float* cum, float* mu_y, float* attn, float* y_mask, void* stream);
+
 /* One estimator parameter for the training entry point: DEVICE fp32 tensors in the reference layout (SURVEY.md
  * Appendix A), `grad` may be NULL (that gradient is then not computed). */
 typedef struct {

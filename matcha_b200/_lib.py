@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
+    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
 
 
@@ -69,6 +69,7 @@ def load():
                                            vp, vp, vp, vp, vp, vp]
         lib.mb200_denoiser_bias.argtypes = [vp, vp, i, vp, vp]
         lib.mb200_denoise.argtypes = [vp, vp, i, i, vp, f, vp, vp]
+        lib.mb200_length_regulate.argtypes = [vp, vp, vp, vp, i, i, i, i, vp, vp, vp, vp, vp]
         lib.mb200_launch_count.argtypes = [vp]
         lib.mb200_launch_count.restype = ctypes.c_longlong
         lib.mb200_workspace_bytes.argtypes = [vp]
@@ -108,6 +109,31 @@ def _dev_f32(t, device):
 
 def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def length_regulate(mu_x, w, x_mask, y_lengths, t_pad, want_attn=True):
+    """CUDA length regulation (matcha_tts.py:118-131): mu_x (B, C, Lx), w (B, Lx) frames per token, x_mask (B, Lx),
+    y_lengths (B,) int64 -> mu_y (B, C, t_pad), attn (B, Lx, t_pad) or None, y_mask (B, t_pad).  No plan needed."""
+    lib = load()
+    if not mu_x.is_cuda:
+        raise RuntimeError("matcha_b200.length_regulate runs on CUDA tensors only (no CPU fallback)")
+    dev = mu_x.device
+    mu_x, w, x_mask = _dev_f32(mu_x, dev), _dev_f32(w, dev), _dev_f32(x_mask, dev)
+    b, c, lx = mu_x.shape
+    if tuple(w.shape) != (b, lx) or tuple(x_mask.shape) != (b, lx):
+        raise ValueError("w and x_mask must be (B, Lx)")
+    yl = y_lengths.to(device=dev, dtype=torch.int64).contiguous()
+    if tuple(yl.shape) != (b,):
+        raise ValueError("y_lengths must be (B,)")
+    t_pad = int(t_pad)
+    cum = torch.empty(b, lx, device=dev, dtype=torch.float32)
+    mu_y = torch.empty(b, c, t_pad, device=dev, dtype=torch.float32)
+    attn = torch.empty(b, lx, t_pad, device=dev, dtype=torch.float32) if want_attn else None
+    y_mask = torch.empty(b, t_pad, device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev):
+        check(lib.mb200_length_regulate(_ptr(mu_x), _ptr(w), _ptr(x_mask), _ptr(yl), b, c, lx, t_pad, _ptr(cum), _ptr(mu_y),
+                                        _ptr(attn), _ptr(y_mask), _stream()))
+    return mu_y, attn, y_mask
 
 
 class Plan:

@@ -224,6 +224,13 @@ int mb200_denoise(mb200_plan* plan, const float* audio, int B, int L, const floa
     P(plan)->denoise(audio, B, L, bias, strength, out, static_cast<cudaStream_t>(stream));
   });
 }
+int mb200_length_regulate(const float* mu_x, const float* w, const float* x_mask, const long long* y_lengths, int B, int C,
+                          int Lx, int T, float* cum, float* mu_y, float* attn, float* y_mask, void* stream) {
+  return guarded([&] {
+    if (!mu_x || !w || !x_mask || !y_lengths || !cum || !mu_y) throw mb::Error("null argument");
+    mb::length_regulate(mu_x, w, x_mask, y_lengths, B, C, Lx, T, cum, mu_y, attn, y_mask, static_cast<cudaStream_t>(stream));
+  });
+}
 int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
                        const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
                        float sigma_min, int backward, float* loss, float* y, float* v, float* dmu, float* dspks,

@@ -212,4 +212,8 @@ class Plan {
   friend struct PlanAccess;
 };
 
+// Length regulation (matcha_tts.py:118-131, utils/model.py:29-41), length_regulate.cu.  Plan-independent.
+void length_regulate(const float* mu_x, const float* w, const float* x_mask, const long long* y_len, int B, int C, int Lx,
+                     int T, float* cum, float* mu_y, float* attn, float* y_mask, cudaStream_t st);
+
 }  // namespace mb

@@ -190,12 +190,22 @@ class TextEncoder(nn.Module):
 
 
 def length_regulate(mu_x, w_ceil, x_mask, y_lengths, t_pad):
-    """mu_y (B, n_feats, t_pad) and attn (B, Lx, t_pad) from per-token frame counts.
+    """mu_y (B, n_feats, t_pad), attn (B, Lx, t_pad) and y_mask (B, 1, t_pad) from per-token frame counts.
 
     Same result as `attn = generate_path(...)`, `mu_y = attn^T @ mu_x` (matcha_tts.py:126-131) without the dense matmul:
-    frame j of utterance b copies token `searchsorted(cumsum(w), j, right=True)`, and frames at or beyond
-    y_lengths[b] are zero.
+    frame j of utterance b copies the first token whose duration prefix sum exceeds j, and frames at or beyond
+    y_lengths[b] are zero.  CUDA tensors go through the `mb200_length_regulate` kernels (csrc/length_regulate.cu, prefix
+    sum + gather, bit-exact against the reference-generated fixtures); tensors on the CPU - where the rest of `synthesise`
+    cannot run anyway - take the torch formulation below, which is what the CPU unit tests pin to the same fixtures.
     """
+    if mu_x.is_cuda:
+        from . import _lib
+        mu_y, attn, y_mask = _lib.length_regulate(mu_x, w_ceil.squeeze(1), x_mask.squeeze(1), y_lengths, t_pad)
+        return mu_y.to(mu_x.dtype), attn.to(x_mask.dtype), y_mask.unsqueeze(1).to(x_mask.dtype)
+    return _length_regulate_host(mu_x, w_ceil, x_mask, y_lengths, t_pad)
+
+
+def _length_regulate_host(mu_x, w_ceil, x_mask, y_lengths, t_pad):
     b, c, lx = mu_x.shape
     y_mask = sequence_mask(y_lengths, t_pad).unsqueeze(1).to(x_mask.dtype)           # (B, 1, T)
     attn_mask = x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)                            # (B, 1, Lx, T)

@@ -115,3 +115,53 @@ def test_synthesise_end_to_end_against_oracle(n_spks):
     ref = mo.solve_euler(est_sd, torch.zeros_like(mu_y), mu_y, mask, 3, spks=spk_vec)[:, :, :y_max]
     assert float((out["decoder_outputs"].cpu() - ref).abs().max()) <= 1e-3
     assert torch.allclose(out["mel"].cpu(), out["decoder_outputs"].cpu() * 2.1 - 5.5, atol=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["enc_lj_ragged", "enc_vctk_scaled"])
+def test_cuda_length_regulation_matches_reference_golden(name):
+    """`mb200_length_regulate` (prefix sum + gather) against the unmodified reference's generate_path + matmul: bit-exact."""
+    fx = _fx(name)
+    w_ceil = torch.ceil(torch.exp(fx["logw"]) * fx["x_mask"]) * fx["length_scale"]
+    mu_y, attn, y_mask = mt.length_regulate(fx["mu_x"].cuda(), w_ceil.cuda(), fx["x_mask"].cuda(), fx["y_lengths"].cuda(),
+                                            fx["t_pad"])
+    assert mu_y.is_cuda and attn.shape == (fx["mu_x"].shape[0], fx["mu_x"].shape[2], fx["t_pad"])
+    assert torch.equal(attn.cpu().to(torch.uint8), fx["attn"].squeeze(1))
+    assert torch.equal(mu_y.cpu(), fx["mu_y"])
+    assert y_mask.shape == (fx["mu_x"].shape[0], 1, fx["t_pad"])
+    assert torch.equal(y_mask.cpu().squeeze(1).sum(1).long(), fx["y_lengths"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("b,lx,scale", [(4, 2001, 1.5), (64, 301, 1.5), (3, 57, 0.37), (2, 1, 1.0), (5, 130, 0.9)])
+def test_cuda_length_regulation_matches_oracle(b, lx, scale):
+    """Seeded cases up to BASELINE cfg4's size (Lx 2001 -> 3001 frames) and the edges: tokens with zero frames, an
+    utterance whose durations are all zero (y_length clamps to 1 and its only frame has no owner), a non-dyadic
+    length_scale (prefix sums inexact in fp32), Lx = 1, ragged token counts."""
+    from oracle import matcha_oracle as mo
+    g = torch.Generator().manual_seed(100 * b + lx)
+    x_len = torch.randint(max(1, lx // 3), lx + 1, (b,), generator=g)
+    x_len[0] = lx
+    x_mask = (torch.arange(lx)[None, :] < x_len[:, None]).float()
+    dur = torch.randint(0, 4, (b, lx), generator=g).float() if scale != 1.5 else torch.full((b, lx), 1.0)
+    if b > 1:
+        dur[1] = 0.0                                  # an utterance with no frames at all
+    w = dur * x_mask * scale
+    y_len = torch.clamp_min(w.sum(1), 1).long()
+    t_pad = mt.fix_len_compatibility(int(y_len.max()))
+    mu_x = torch.randn(b, 80, lx, generator=g)
+    ref_mu, ref_attn, ref_ym = mo.length_regulate(mu_x, w, x_mask, y_len, t_pad)
+    mu_y, attn, y_mask = mt.length_regulate(mu_x.cuda(), w.unsqueeze(1).cuda(), x_mask.unsqueeze(1).cuda(), y_len.cuda(), t_pad)
+    assert torch.equal(attn.cpu(), ref_attn)
+    assert torch.equal(mu_y.cpu(), ref_mu)
+    assert torch.equal(y_mask.cpu().squeeze(1), ref_ym)
+    # size-independent properties: every frame below y_length of an utterance with frames has exactly one owner,
+    # owners are monotone in the frame index, padded frames have none
+    own = attn.cpu().sum(1)
+    for i in range(b):
+        n = int(y_len[i])
+        if float(w[i].sum()) >= 1:
+            assert torch.equal(own[i, :n], torch.ones(n))
+            tok = attn.cpu()[i, :, :n].argmax(0)
+            assert bool((tok[1:] >= tok[:-1]).all())
+        assert float(own[i, n:].abs().sum()) == 0.0

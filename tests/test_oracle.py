@@ -159,3 +159,14 @@ def test_denoiser_matches_reference_golden(golden_dir):
         assert got.shape == want.shape and float((got - want).abs().max()) <= 1e-6
     got = mo.denoise(fx["batch"], fx["bias_spec"], fx["strength"])
     assert float((got - fx["batch_out"]).abs().max()) <= 1e-6
+
+
+@pytest.mark.parametrize("name", ["enc_lj_ragged", "enc_vctk_scaled"])
+def test_length_regulate_matches_reference_golden(golden_dir, name):
+    """The oracle's alignment + matmul restatement against the unmodified reference's generate_path / matmul."""
+    fx = torch.load(os.path.join(golden_dir, name + ".pt"), weights_only=False)
+    w = (torch.ceil(torch.exp(fx["logw"]) * fx["x_mask"]) * fx["length_scale"]).squeeze(1)
+    mu_y, attn, y_mask = mo.length_regulate(fx["mu_x"], w, fx["x_mask"].squeeze(1), fx["y_lengths"], fx["t_pad"])
+    assert torch.equal(attn.to(torch.uint8), fx["attn"].squeeze(1))
+    assert torch.equal(mu_y, fx["mu_y"])
+    assert torch.equal(y_mask.sum(1).long(), fx["y_lengths"])
