@@ -92,6 +92,15 @@ int mb200_denoise(mb200_plan* plan, const float* audio, int B, int L, const floa
 int mb200_length_regulate(const float* mu_x, const float* w, const float* x_mask, const long long* y_lengths, int B, int C,
                           int Lx, int T, float* cum, float* mu_y, float* attn, float* y_mask, void* stream);
 
+/* Monotonic alignment search: `maximum_path(value, mask)` of matcha/utils/monotonic_align/__init__.py:7-22, i.e. the
+ * Cython `maximum_path_c` (monotonic_align/core.pyx:11-47) without the device -> host -> device round trip.  DEVICE
+ * pointers, fp32: value (B, Tx, Ty) log-prior, mask (B, Tx, Ty) 0/1 (token count = nonzeros of mask[b, :, 0], frame count
+ * = nonzeros of mask[b, 0, :], as the reference derives them); path (B, Tx, Ty) receives 0/1.  workspace: at least
+ * mb200_maximum_path_workspace_bytes(B, Tx, Ty) bytes.  Defined for 1 <= tokens <= frames per utterance. */
+long long mb200_maximum_path_workspace_bytes(int B, int Tx, int Ty);
+int mb200_maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* workspace,
+                       void* stream);
+
 /* One estimator parameter for the training entry point: DEVICE fp32 tensors in the reference layout (SURVEY.md
  * Appendix A), `grad` may be NULL (that gradient is then not computed). */
 typedef struct {

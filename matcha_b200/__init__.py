@@ -8,6 +8,7 @@ from ._lib import Plan, euler_schedule  # noqa: F401
 from .cfm import BASECFM, CFM, Decoder  # noqa: F401
 from .hifigan import AttrDict, Denoiser, Generator, V1 as HIFIGAN_V1  # noqa: F401
 from .matcha_tts import MatchaTTS, TextEncoder  # noqa: F401
+from . import monotonic_align  # noqa: F401
 
 __all__ = ["Plan", "euler_schedule", "BASECFM", "CFM", "Decoder", "Generator", "Denoiser", "AttrDict", "HIFIGAN_V1", "MatchaTTS",
-           "TextEncoder"]
+           "TextEncoder", "monotonic_align"]

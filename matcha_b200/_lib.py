@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
+    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_maximum_path", "mb200_maximum_path_workspace_bytes", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
 
 
@@ -70,6 +70,9 @@ def load():
         lib.mb200_denoiser_bias.argtypes = [vp, vp, i, vp, vp]
         lib.mb200_denoise.argtypes = [vp, vp, i, i, vp, f, vp, vp]
         lib.mb200_length_regulate.argtypes = [vp, vp, vp, vp, i, i, i, i, vp, vp, vp, vp, vp]
+        lib.mb200_maximum_path.argtypes = [vp, vp, i, i, i, vp, vp, vp]
+        lib.mb200_maximum_path_workspace_bytes.argtypes = [i, i, i]
+        lib.mb200_maximum_path_workspace_bytes.restype = ctypes.c_longlong
         lib.mb200_launch_count.argtypes = [vp]
         lib.mb200_launch_count.restype = ctypes.c_longlong
         lib.mb200_workspace_bytes.argtypes = [vp]
@@ -134,6 +137,24 @@ def length_regulate(mu_x, w, x_mask, y_lengths, t_pad, want_attn=True):
         check(lib.mb200_length_regulate(_ptr(mu_x), _ptr(w), _ptr(x_mask), _ptr(yl), b, c, lx, t_pad, _ptr(cum), _ptr(mu_y),
                                         _ptr(attn), _ptr(y_mask), _stream()))
     return mu_y, attn, y_mask
+
+
+def maximum_path(value, mask):
+    """CUDA monotonic alignment search: value, mask (B, Tx, Ty) -> 0/1 path (B, Tx, Ty) in value's dtype
+    (monotonic_align/__init__.py:7-22).  No plan needed, no host round trip."""
+    lib = load()
+    if not value.is_cuda:
+        raise RuntimeError("matcha_b200.maximum_path runs on CUDA tensors only (no CPU fallback)")
+    dev = value.device
+    if value.dim() != 3 or tuple(mask.shape) != tuple(value.shape):
+        raise ValueError("value and mask must both be (B, Tx, Ty)")
+    v, m = _dev_f32(value, dev), _dev_f32(mask, dev)
+    b, tx, ty = v.shape
+    path = torch.empty(b, tx, ty, device=dev, dtype=torch.float32)
+    ws = torch.empty(max(1, int(lib.mb200_maximum_path_workspace_bytes(b, tx, ty))), device=dev, dtype=torch.uint8)
+    with torch.cuda.device(dev):
+        check(lib.mb200_maximum_path(_ptr(v), _ptr(m), b, tx, ty, _ptr(path), _ptr(ws), _stream()))
+    return path.to(value.dtype)
 
 
 class Plan:

@@ -231,6 +231,17 @@ int mb200_length_regulate(const float* mu_x, const float* w, const float* x_mask
     mb::length_regulate(mu_x, w, x_mask, y_lengths, B, C, Lx, T, cum, mu_y, attn, y_mask, static_cast<cudaStream_t>(stream));
   });
 }
+long long mb200_maximum_path_workspace_bytes(int B, int Tx, int Ty) {
+  if (B <= 0 || Tx <= 0 || Ty <= 0) return 0;
+  return static_cast<long long>(mb::maximum_path_workspace_bytes(B, Tx, Ty));
+}
+int mb200_maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* workspace,
+                       void* stream) {
+  return guarded([&] {
+    if (!value || !mask || !path || !workspace) throw mb::Error("null argument");
+    mb::maximum_path(value, mask, B, Tx, Ty, path, workspace, static_cast<cudaStream_t>(stream));
+  });
+}
 int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
                        const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
                        float sigma_min, int backward, float* loss, float* y, float* v, float* dmu, float* dspks,

@@ -1,0 +1,123 @@
+// Monotonic alignment search on the GPU: the most likely monotonic path through the (tokens x frames)
+// log-prior matrix, one CTA per utterance.  Replaces the reference's only native component, the Cython/OpenMP
+// `maximum_path_c` (matcha/utils/monotonic_align/core.pyx:11-47) and its device -> host -> device round trip
+// (matcha/utils/monotonic_align/__init__.py:7-22, called from matcha_tts.py:192 every training step).
+//
+// Reference recurrence, per utterance with t_x tokens and t_y frames (value = log_prior * mask, updated in place):
+//     for y in 0..t_y-1, x in [max(0, t_x + y - t_y), min(t_x, y + 1)):
+//         V[x, y] = max(x == y ? -1e9 : V[x, y-1],  x == 0 ? (y == 0 ? 0 : -1e9) : V[x-1, y-1]) + value[x, y]
+//     index = t_x - 1; for y = t_y-1 .. 0:  path[index, y] = 1;
+//         if index != 0 and (index == y or V[index, y-1] < V[index-1, y-1]): index -= 1
+// Column y depends on column y-1 only, so the tokens of a column are computed in parallel (one __syncthreads per frame)
+// from the previous column kept in shared memory; the input arrives in tiles of TC frames x all tokens with coalesced
+// row-segment loads; the back-tracking comparison `V[x, y-1] < V[x-1, y-1]` is evaluated while column y is computed (both
+// operands are the previous column) and kept as one bit per (frame, token) - 1/32 of the DP matrix - which a single thread
+// then walks backwards.  Same fp32 operations in the same order per cell as the reference: the path is bit-identical.
+// Defined, as the reference is, for 1 <= t_x <= t_y (with more tokens than frames the reference reads out of bounds).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "plan.h"
+
+namespace mb {
+
+namespace {
+
+constexpr float kMasNeg = -1e9f;
+
+__global__ void __launch_bounds__(256)
+mas_kernel(const float* __restrict__ value, const float* __restrict__ mask, int Tx, int Ty, int TC, float* __restrict__ path,
+           uint32_t* __restrict__ dec) {
+  extern __shared__ float sm[];
+  float* colA = sm;                    // [Tx] previous column of V
+  float* colB = colA + Tx;             // [Tx] current column
+  float* tile = colB + Tx;             // [Tx][TC + 1] masked input values of TC frames
+  __shared__ int s_cnt[2];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+  const long base = static_cast<long>(b) * Tx * Ty;
+  const int W = (Tx + 31) >> 5;
+
+  // t_x = mask.sum(1)[:, 0], t_y = mask.sum(2)[:, 0]   (monotonic_align/__init__.py:19-20)
+  if (tid < 2) s_cnt[tid] = 0;
+  __syncthreads();
+  int cx = 0, cy = 0;
+  for (int x = tid; x < Tx; x += 256) cx += mask[base + static_cast<long>(x) * Ty] != 0.f;
+  for (int y = tid; y < Ty; y += 256) cy += mask[base + y] != 0.f;
+  atomicAdd(&s_cnt[0], cx);
+  atomicAdd(&s_cnt[1], cy);
+  // path = 0 everywhere; the back-tracking thread sets the ones afterwards
+  for (long i = tid; i < static_cast<long>(Tx) * Ty; i += 256) path[base + i] = 0.f;
+  for (int x = tid; x < Tx; x += 256) colA[x] = 0.f;
+  __syncthreads();
+  const int t_x = s_cnt[0], t_y = s_cnt[1];
+  if (t_x <= 0 || t_y <= 0) return;
+
+  float* prev = colA;
+  float* cur = colB;
+  const int x_round = ((t_x + 31) >> 5) << 5;
+  for (int y0 = 0; y0 < t_y; y0 += TC) {
+    for (int idx = tid; idx < t_x * TC; idx += 256) {
+      const int x = idx / TC, c = idx - x * TC, y = y0 + c;
+      float v = 0.f;
+      if (y < t_y) v = value[base + static_cast<long>(x) * Ty + y] * mask[base + static_cast<long>(x) * Ty + y];
+      tile[x * (TC + 1) + c] = v;
+    }
+    __syncthreads();
+    const int nc = min(TC, t_y - y0);
+    for (int c = 0; c < nc; ++c) {
+      const int y = y0 + c;
+      const int lo = max(0, t_x + y - t_y), hi = min(t_x, y + 1);
+      for (int x = tid; x < x_round; x += 256) {
+        bool step = false;
+        if (x < t_x) {
+          const float in = tile[x * (TC + 1) + c];
+          float nv = in;                               // cells outside the band keep their input value
+          if (x >= lo && x < hi) {
+            const float v_cur = (x == y) ? kMasNeg : prev[x];
+            const float v_prev = (x == 0) ? (y == 0 ? 0.f : kMasNeg) : prev[x - 1];
+            nv = fmaxf(v_cur, v_prev) + in;
+          }
+          cur[x] = nv;
+          if (x != 0 && y != 0) step = (x == y) || (prev[x] < prev[x - 1]);
+        }
+        const uint32_t bits = __ballot_sync(0xffffffffu, step);
+        if (lane == 0) dec[(static_cast<long>(b) * Ty + y) * W + (x >> 5)] = bits;
+      }
+      __syncthreads();
+      float* t = prev; prev = cur; cur = t;
+    }
+  }
+  if (tid == 0) {
+    int index = t_x - 1;
+    for (int y = t_y - 1; y >= 0; --y) {
+      path[base + static_cast<long>(index) * Ty + y] = 1.f;
+      if (index != 0) {
+        const uint32_t w = dec[(static_cast<long>(b) * Ty + y) * W + (index >> 5)];
+        if ((w >> (index & 31)) & 1u) --index;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+size_t maximum_path_workspace_bytes(int B, int Tx, int Ty) {
+  return static_cast<size_t>(B) * Ty * ((Tx + 31) / 32) * sizeof(uint32_t);
+}
+
+void maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* workspace, cudaStream_t st) {
+  if (B <= 0 || Tx <= 0 || Ty <= 0) throw Error("maximum_path: empty shape");
+  int TC = 32;
+  auto bytes = [&](int tc) { return (2 * static_cast<size_t>(Tx) + static_cast<size_t>(Tx) * (tc + 1)) * sizeof(float); };
+  while (TC > 1 && bytes(TC) > 200 * 1024) TC >>= 1;
+  if (bytes(TC) > 200 * 1024) throw Error("maximum_path: too many tokens for one CTA's shared memory");
+  static bool configured = false;
+  if (!configured) {
+    MB_CUDA(cudaFuncSetAttribute(mas_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = true;
+  }
+  mas_kernel<<<B, 256, bytes(TC), st>>>(value, mask, Tx, Ty, TC, path, static_cast<uint32_t*>(workspace));
+  MB_CUDA(cudaGetLastError());
+}
+
+}  // namespace mb

@@ -216,4 +216,8 @@ class Plan {
 void length_regulate(const float* mu_x, const float* w, const float* x_mask, const long long* y_len, int B, int C, int Lx,
                      int T, float* cum, float* mu_y, float* attn, float* y_mask, cudaStream_t st);
 
+// Monotonic alignment search (monotonic_align/core.pyx:11-47), mas.cu.  Plan-independent.
+size_t maximum_path_workspace_bytes(int B, int Tx, int Ty);
+void maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* workspace, cudaStream_t st);
+
 }  // namespace mb

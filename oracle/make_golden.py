@@ -170,11 +170,38 @@ def encoder_case(name, n_spks, lengths, seed, length_scale):
     print(name, "Lx", lx, "y_lengths", y_lengths.tolist(), "t_pad", int(t_pad))
 
 
+def mas_case(name, x_lengths, y_lengths, seed):
+    """Monotonic alignment search through the reference's own Cython code (compiled by oracle/build_ref.py), called the
+    way matcha/utils/monotonic_align/__init__.py:7-22 calls it."""
+    import numpy as np
+    from oracle.build_ref import build, load_ref_mas
+    build()
+    core = load_ref_mas()
+    rng = np.random.default_rng(seed)
+    b, tx, ty = len(x_lengths), max(x_lengths), max(y_lengths)
+    value = (rng.standard_normal((b, tx, ty)) * 40.0 - 120.0).astype(np.float32)      # log-prior-like magnitudes
+    mask = np.zeros((b, tx, ty), dtype=np.float32)
+    for i, (nx, ny) in enumerate(zip(x_lengths, y_lengths)):
+        mask[i, :nx, :ny] = 1.0
+    v = (value * mask).astype(np.float32)
+    path = np.zeros_like(v).astype(np.int32)
+    t_x_max = mask.sum(1)[:, 0].astype(np.int32)
+    t_y_max = mask.sum(2)[:, 0].astype(np.int32)
+    core.maximum_path_c(path, v, t_x_max, t_y_max)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), value=value, x_lengths=np.array(x_lengths), y_lengths=np.array(y_lengths),
+                        path=path.astype(np.uint8))
+    print(name, "Tx", tx, "Ty", ty, "ones per utterance", path.sum((1, 2)).tolist())
+
+
 def main():
     import sys
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
     torch.set_num_threads(8)
+    if "mas" in sys.argv[1:]:              # SURVEY.md section 8(f) row 4
+        mas_case("mas_ragged", (23, 9, 1, 17), (61, 40, 5, 17), seed=71)
+        mas_case("mas_long", (60, 41), (181, 120), seed=72)
+        return
     if "denoiser" in sys.argv[1:]:         # SURVEY.md section 8(f) row 1
         denoiser_case("denoiser_ragged", 51, (513, 1024, 2303, 5000), strength=0.05)
         return

@@ -165,3 +165,22 @@ def test_cuda_length_regulation_matches_oracle(b, lx, scale):
             tok = attn.cpu()[i, :, :n].argmax(0)
             assert bool((tok[1:] >= tok[:-1]).all())
         assert float(own[i, n:].abs().sum()) == 0.0
+
+
+@pytest.mark.gpu
+def test_cuda_length_regulation_unaligned_frame_count():
+    """t_pad that is not a multiple of 4 (rows of the alignment lose their 16-byte alignment: scalar store path)."""
+    from matcha_b200 import _lib
+    from oracle import matcha_oracle as mo
+    g = torch.Generator().manual_seed(9)
+    b, lx = 3, 41
+    x_mask = torch.ones(b, lx)
+    w = torch.randint(0, 5, (b, lx), generator=g).float() * 0.77
+    y_len = torch.clamp_min(w.sum(1), 1).long()
+    mu_x = torch.randn(b, 80, lx, generator=g)
+    for t_pad in (int(y_len.max()) + 1, int(y_len.max()) + 2, int(y_len.max()) + 3):
+        ref_mu, ref_attn, ref_ym = mo.length_regulate(mu_x, w, x_mask, y_len, t_pad)
+        mu_y, attn, y_mask = _lib.length_regulate(mu_x.cuda(), w.cuda(), x_mask.cuda(), y_len.cuda(), t_pad)
+        assert torch.equal(attn.cpu(), ref_attn) and torch.equal(mu_y.cpu(), ref_mu) and torch.equal(y_mask.cpu(), ref_ym)
+        mu_only, none, _ = _lib.length_regulate(mu_x.cuda(), w.cuda(), x_mask.cuda(), y_len.cuda(), t_pad, want_attn=False)
+        assert none is None and torch.equal(mu_only.cpu(), ref_mu)
