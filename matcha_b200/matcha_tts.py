@@ -3,26 +3,29 @@
 What runs where:
   * the hot path -- `self.decoder(mu_y, y_mask, n_timesteps, temperature, spks)` (matcha_tts.py:135) -- is the CUDA path of
     this package (`matcha_b200.cfm.CFM` -> libmatcha_b200.so);
-  * the upstream of the path (text encoder, duration predictor, length regulation) is host-side PyTorch written for
-    this package: it is SURVEY §8(f) rows 2-3 ("next"), not yet CUDA kernels.  It keeps the reference's parameter names
+  * the text encoder and duration predictor are PyTorch written for this package (not yet CUDA
+    kernels); length regulation is CUDA (`mb200_length_regulate`, §8(f) row 2).  The encoder keeps the reference's parameter names
     (`encoder.emb`, `encoder.prenet.*`, `encoder.encoder.attn_layers.N.conv_q ...`, `encoder.proj_m`, `encoder.proj_w.*`,
     `spk_emb`, `decoder.estimator.*`) so `load_state_dict(strict=True)` of a reference checkpoint's `state_dict` works;
   * length regulation does not form the dense (B, Lx, T) alignment matmul (matcha_tts.py:129-131): `mu_y` is a gather
     of `mu_x` by the token index of each frame, which is what the 0/1 alignment computes; `attn` is still returned for
     API compatibility.
 
-Training (`forward`, MAS, losses) is out of scope for this round.
+Training: `forward` returns the reference's three losses with the monotonic alignment search (§8(f) row 4) and the
+decoder loss + backward (§8(a) row a15) in CUDA; the optimiser / Lightning loop stays outside.
 """
 from __future__ import annotations
 
 import datetime as dt
 import math
+import random
 from types import SimpleNamespace
 
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from . import monotonic_align
 from .cfm import CFM
 
 
@@ -264,9 +267,54 @@ class MatchaTTS(nn.Module):
             "rtf": seconds * 22050 / (decoder_outputs.shape[-1] * 256),
         }
 
-    def forward(self, *args, **kwargs):
-        raise NotImplementedError("matcha_b200.MatchaTTS covers synthesis; training (MAS, losses, estimator backward) "
-                                  "is not built in this round")
+    def forward(self, x, x_lengths, y, y_lengths, spks=None, out_size=None, cond=None):
+        """The three training losses `(dur_loss, prior_loss, diff_loss)` (reference matcha_tts.py:150-245).
+
+        Encoder and the scalar losses are torch; the alignment between tokens and mel frames is found on the GPU
+        (`monotonic_align.maximum_path`, csrc/mas.cu - the reference round-trips through the host here) and the decoder
+        loss with its whole backward pass runs in CUDA (`CFM.compute_loss`, csrc/train.cu).  Gradients reach the encoder
+        through `mu_y` (prior and flow-matching loss) and `logw` (duration loss), as upstream.
+        """
+        if self.n_spks > 1:
+            spks = self.spk_emb(spks)
+        mu_x, logw, x_mask = self.encoder(x, x_lengths, spks)
+        y_max_length = y.shape[-1]
+        y_mask = sequence_mask(y_lengths, y_max_length).unsqueeze(1).to(x_mask)
+        attn_mask = x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)
+        with torch.no_grad():
+            # log N(y_j; mu_x_i, I) for every (token, frame) pair, expanded into three terms as upstream
+            const = -0.5 * math.log(2 * math.pi) * self.n_feats
+            factor = -0.5 * torch.ones(mu_x.shape, dtype=mu_x.dtype, device=mu_x.device)
+            y_square = torch.matmul(factor.transpose(1, 2), y ** 2)
+            y_mu_double = torch.matmul(2.0 * (factor * mu_x).transpose(1, 2), y)
+            mu_square = torch.sum(factor * (mu_x ** 2), 1).unsqueeze(-1)
+            log_prior = y_square - y_mu_double + mu_square + const
+            attn = monotonic_align.maximum_path(log_prior, attn_mask.squeeze(1)).detach()
+        logw_ = torch.log(1e-8 + torch.sum(attn.unsqueeze(1), -1)) * x_mask
+        dur_loss = torch.sum((logw - logw_) ** 2) / torch.sum(x_lengths)        # utils/model.py:44-46
+        if out_size is not None:
+            # random segment of `out_size` frames per utterance (the Grad-TTS memory hack, matcha_tts.py:203-225)
+            max_offset = (y_lengths - out_size).clamp(0).tolist()
+            offsets = [random.choice(range(0, end)) if end > 0 else 0 for end in max_offset]
+            attn_cut = torch.zeros(attn.shape[0], attn.shape[1], out_size, dtype=attn.dtype, device=attn.device)
+            y_cut = torch.zeros(y.shape[0], self.n_feats, out_size, dtype=y.dtype, device=y.device)
+            cut_lengths = []
+            for i, off in enumerate(offsets):
+                n = out_size + min(int(y_lengths[i]) - out_size, 0)
+                cut_lengths.append(n)
+                y_cut[i, :, :n] = y[i, :, off:off + n]
+                attn_cut[i, :, :n] = attn[i, :, off:off + n]
+            y_cut_lengths = torch.tensor(cut_lengths, dtype=torch.long, device=y.device)
+            attn, y = attn_cut, y_cut
+            y_mask = sequence_mask(y_cut_lengths).unsqueeze(1).to(y_mask)
+        mu_y = torch.matmul(attn.squeeze(1).transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
+        diff_loss, _ = self.decoder.compute_loss(x1=y, mask=y_mask, mu=mu_y, spks=spks, cond=cond)
+        if self.prior_loss:
+            prior_loss = torch.sum(0.5 * ((y - mu_y) ** 2 + math.log(2 * math.pi)) * y_mask)
+            prior_loss = prior_loss / (torch.sum(y_mask) * self.n_feats)
+        else:
+            prior_loss = 0
+        return dur_loss, prior_loss, diff_loss
 
 
 def default_config(n_spks=1):

@@ -193,11 +193,72 @@ def mas_case(name, x_lengths, y_lengths, seed):
     print(name, "Tx", tx, "Ty", ty, "ones per utterance", path.sum((1, 2)).tolist())
 
 
+def forward_case(name, n_spks, x_lengths, y_lengths, seed):
+    """The reference MatchaTTS.forward (matcha_tts.py:150-245) - encoder, log-prior, its own Cython MAS (oracle/_ref),
+    duration / prior / flow-matching losses - run unmodified, with the draws of compute_loss recorded."""
+    from oracle.build_ref import build
+    build()
+    from matcha_b200 import matcha_tts as mt       # only for the shipped hyper-parameters (default_config)
+    _, _, _, _, MatchaTTS = ref_shims.load_reference()
+    cfg = mt.default_config(n_spks=n_spks)
+    model = MatchaTTS(n_vocab=178, n_spks=n_spks, spk_emb_dim=64, n_feats=80, encoder=cfg["encoder"],
+                      decoder=dict(cfg["decoder"]), cfm=cfg["cfm"], data_statistics=cfg["data_statistics"], out_size=None).eval()
+    c_in = 160 if n_spks == 1 else 224
+    enc_sd = weights.text_encoder_state_dict(n_spks=n_spks, seed=seed)
+    est_sd = weights.estimator_state_dict(c_in, seed=seed + 1)
+    sd = {"encoder." + k: v for k, v in enc_sd.items()}
+    sd.update({"decoder." + k: v for k, v in est_sd.items()})
+    sd["mel_mean"], sd["mel_std"] = torch.tensor(-5.536622), torch.tensor(2.116101)
+    g = torch.Generator().manual_seed(seed)
+    if n_spks > 1:
+        sd["spk_emb.weight"] = torch.randn(n_spks, 64, generator=g)
+    model.load_state_dict(sd, strict=True)
+    b, lx, ty = len(x_lengths), max(x_lengths), max(y_lengths)
+    x = torch.randint(1, 178, (b, lx), generator=g)
+    for i, n in enumerate(x_lengths):
+        x[i, n:] = 0
+    y = torch.randn(b, 80, ty, generator=g)
+    for i, n in enumerate(y_lengths):
+        y[i, :, n:] = 0
+    spks = torch.randint(0, n_spks, (b,), generator=g) if n_spks > 1 else None
+    draws = {}
+    real_rand, real_randn_like = torch.rand, torch.randn_like
+
+    def rand(*a, **k):
+        draws["t"] = real_rand(*a, **k)
+        return draws["t"]
+
+    def randn_like(*a, **k):
+        draws["z"] = real_randn_like(*a, **k)
+        return draws["z"]
+
+    torch.manual_seed(seed)
+    torch.rand, torch.randn_like = rand, randn_like
+    try:
+        dur_loss, prior_loss, diff_loss = model(x, torch.tensor(x_lengths), y, torch.tensor(y_lengths), spks=spks)
+        (dur_loss + prior_loss + diff_loss).backward()
+    finally:
+        torch.rand, torch.randn_like = real_rand, real_randn_like
+    named = dict(model.named_parameters())
+    keep = ["encoder.proj_m.weight", "encoder.proj_w.proj.weight", "encoder.encoder.norm_layers_2.5.gamma",
+            "encoder.prenet.proj.bias", "decoder.estimator.final_proj.weight", "decoder.estimator.mid_blocks.0.0.mlp.1.bias"]
+    fx = dict(n_spks=n_spks, seed=seed, x=x, x_lengths=torch.tensor(x_lengths), y=y, y_lengths=torch.tensor(y_lengths), spks=spks,
+              spk_emb=sd.get("spk_emb.weight"), t=draws["t"].clone(), z=draws["z"].clone(),
+              dur_loss=dur_loss.detach().clone(), prior_loss=prior_loss.detach().clone(), diff_loss=diff_loss.detach().clone(),
+              grads={k: named[k].grad.clone() for k in keep})
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "losses", float(dur_loss), float(prior_loss), float(diff_loss))
+
+
 def main():
     import sys
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
     torch.set_num_threads(8)
+    if "forward" in sys.argv[1:]:          # MatchaTTS.forward (training losses), the caller of 8(f) row 4 and 8(a) a15
+        forward_case("fwd_lj_ragged", 1, (13, 7, 10), (40, 24, 33), seed=81)
+        forward_case("fwd_vctk_ragged", 109, (9, 12), (28, 36), seed=82)
+        return
     if "mas" in sys.argv[1:]:              # SURVEY.md section 8(f) row 4
         mas_case("mas_ragged", (23, 9, 1, 17), (61, 40, 5, 17), seed=71)
         mas_case("mas_long", (60, 41), (181, 120), seed=72)

@@ -128,8 +128,14 @@ def install():
         if isinstance(m, types.ModuleType) and not getattr(m, "__file__", None):
             m.__dict__.update(attrs)
     del d
-    # Cython MAS (matcha/utils/monotonic_align/core.pyx) is training-only and not built here.
-    _mod("matcha.utils.monotonic_align.core", maximum_path_c=_Anything())
+    # Cython MAS (matcha/utils/monotonic_align/core.pyx): the reference's own code compiled into oracle/_ref by
+    # oracle/build_ref.py when that has been run, else a stub (synthesis never calls it).
+    from oracle.build_ref import load_ref_mas
+    core = load_ref_mas()
+    if core is not None:
+        sys.modules["matcha.utils.monotonic_align.core"] = core
+    else:
+        _mod("matcha.utils.monotonic_align.core", maximum_path_c=_Anything())
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
 
