@@ -19,20 +19,27 @@ namespace mb {
 
 namespace {
 
-// one thread per utterance: 2 000 dependent adds at most (T = 3 004 configs), a few microseconds
-__global__ void lr_cumsum_kernel(const float* __restrict__ w, int B, int Lx, float* __restrict__ cum) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
+// one warp per utterance: coalesced loads of 32 durations, then every lane performs the SAME sequential additions (the
+// value of lane k arrives by shuffle) and lane k keeps the k-th partial sum - the order of a scalar loop, without its
+// chain of dependent global loads
+__global__ void __launch_bounds__(32) lr_cumsum_kernel(const float* __restrict__ w, int Lx, float* __restrict__ cum) {
+  const int b = blockIdx.x, lane = threadIdx.x;
   const float* wr = w + static_cast<long>(b) * Lx;
   float* cr = cum + static_cast<long>(b) * Lx;
   double s = 0.0;
-  for (int i = 0; i < Lx; ++i) {
-    s += static_cast<double>(wr[i]);
-    cr[i] = static_cast<float>(s);
+  for (int i0 = 0; i0 < Lx; i0 += 32) {
+    const float x = (i0 + lane < Lx) ? wr[i0 + lane] : 0.f;
+    float mine = 0.f;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+      s += static_cast<double>(__shfl_sync(0xffffffffu, x, k));
+      if (lane == k) mine = static_cast<float>(s);
+    }
+    if (i0 + lane < Lx) cr[i0 + lane] = mine;
   }
 }
 
-// grid (frame blocks of 128, B); 128 threads, one frame each.  The owner of frame j is the first token with cum > j
+// grid (frame blocks of 128, channel groups of 16, B); 128 threads, one frame each.  The owner of frame j is the first token with cum > j
 // (binary search over the utterance's prefix sums in shared memory); tokens that own no frame (w = 0) are skipped by the
 // search exactly as they get an all-zero row from the reference's difference of prefix masks.
 __global__ void __launch_bounds__(128)
@@ -41,7 +48,8 @@ lr_fill_kernel(const float* __restrict__ mu_x, const float* __restrict__ cum, co
                float* __restrict__ y_mask) {
   extern __shared__ float s_cum[];   // [Lx] prefix sums, then [Lx] token mask
   float* s_xm = s_cum + Lx;
-  const int b = blockIdx.y, j0 = blockIdx.x * 128, j = j0 + threadIdx.x;
+  const int b = blockIdx.z, j0 = blockIdx.x * 128, j = j0 + threadIdx.x;
+  const int c0 = blockIdx.y * 16, c1 = min(C, c0 + 16);
   for (int i = threadIdx.x; i < Lx; i += 128) {
     s_cum[i] = cum[static_cast<long>(b) * Lx + i];
     s_xm[i] = x_mask[static_cast<long>(b) * Lx + i];
@@ -58,14 +66,14 @@ lr_fill_kernel(const float* __restrict__ mu_x, const float* __restrict__ cum, co
       if (s_cum[mid] > fj) hi = mid; else lo = mid + 1;
     }
     if (lo < Lx && j < yl) { tok = lo; own = s_xm[lo]; }
-    if (y_mask) y_mask[static_cast<long>(b) * T + j] = j < yl ? 1.f : 0.f;
+    if (y_mask && blockIdx.y == 0) y_mask[static_cast<long>(b) * T + j] = j < yl ? 1.f : 0.f;
     // frame-rate encoder output: channel rows are contiguous along T -> coalesced stores, gathered loads (L2-resident)
     const float* mx = mu_x + static_cast<long>(b) * C * Lx;
     float* my = mu_y + static_cast<long>(b) * C * T + j;
     if (tok >= 0 && own != 0.f) {
-      for (int c = 0; c < C; ++c) my[static_cast<long>(c) * T] = __ldg(mx + static_cast<long>(c) * Lx + tok) * own;
+      for (int c = c0; c < c1; ++c) my[static_cast<long>(c) * T] = __ldg(mx + static_cast<long>(c) * Lx + tok) * own;
     } else {
-      for (int c = 0; c < C; ++c) my[static_cast<long>(c) * T] = 0.f;
+      for (int c = c0; c < c1; ++c) my[static_cast<long>(c) * T] = 0.f;
     }
   }
 }
@@ -113,9 +121,9 @@ void length_regulate(const float* mu_x, const float* w, const float* x_mask, con
                      int T, float* cum, float* mu_y, float* attn, float* y_mask, cudaStream_t st) {
   if (B <= 0 || C <= 0 || Lx <= 0 || T <= 0) throw Error("length_regulate: empty shape");
   if (2 * Lx * sizeof(float) > 48 * 1024) throw Error("length_regulate: Lx > 6144 tokens is not supported");
-  lr_cumsum_kernel<<<(B + 31) / 32, 32, 0, st>>>(w, B, Lx, cum);
+  lr_cumsum_kernel<<<B, 32, 0, st>>>(w, Lx, cum);
   MB_CUDA(cudaGetLastError());
-  lr_fill_kernel<<<dim3((T + 127) / 128, B), 128, 2 * Lx * sizeof(float), st>>>(mu_x, cum, x_mask, y_len, C, Lx, T, mu_y, y_mask);
+  lr_fill_kernel<<<dim3((T + 127) / 128, (C + 15) / 16, B), 128, 2 * Lx * sizeof(float), st>>>(mu_x, cum, x_mask, y_len, C, Lx, T, mu_y, y_mask);
   MB_CUDA(cudaGetLastError());
   if (attn) {
     const int vec = (T & 3) == 0 && (reinterpret_cast<uintptr_t>(attn) & 15) == 0;   // rows stay 16-byte aligned
