@@ -20,11 +20,32 @@ struct Ctx {
 };
 inline unsigned blocks256(long n) { return static_cast<unsigned>((n + 255) / 256); }
 
+// MB200_TRAIN_GEMM = tf32x3 (default: tensor cores, error-compensated, fp32-level accuracy) | tf32 | ffma
+int train_gemm_mode() {
+  static const int mode = [] {
+    const char* e = std::getenv("MB200_TRAIN_GEMM");
+    if (!e) return 3;
+    const std::string v = e;
+    if (v == "ffma") return 0;
+    if (v == "tf32") return 1;
+    if (v == "tf32x3") return 3;
+    throw Error("MB200_TRAIN_GEMM must be ffma, tf32 or tf32x3");
+  }();
+  return mode;
+}
+
 void gemm(Ctx& c, Gemm p, int nz) {
   if (p.M <= 0 || p.N <= 0 || p.K <= 0 || nz <= 0) return;
   if (p.nz2 <= 0) p.nz2 = 1;
-  dim3 grid((p.M + trn::BM - 1) / trn::BM, (p.N + trn::BN - 1) / trn::BN, nz);
-  trn::sgemm_kernel<<<grid, 256, 0, c.st>>>(p);
+  const int mode = train_gemm_mode();
+  if (mode != 0 && p.M >= 32 && p.N >= 32) {
+    dim3 grid((p.M + trn::TM - 1) / trn::TM, (p.N + trn::TN - 1) / trn::TN, nz);
+    if (mode == 3) trn::tgemm_kernel<3><<<grid, 256, 0, c.st>>>(p);
+    else trn::tgemm_kernel<1><<<grid, 256, 0, c.st>>>(p);
+  } else {
+    dim3 grid((p.M + trn::BM - 1) / trn::BM, (p.N + trn::BN - 1) / trn::BN, nz);
+    trn::sgemm_kernel<<<grid, 256, 0, c.st>>>(p);
+  }
   c.check();
   c.launches++;
 }

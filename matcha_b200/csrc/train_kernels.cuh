@@ -88,6 +88,144 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const Gemm p) {
   }
 }
 
+// The same contract on the tensor cores: 128 x 128 x 16 tiles, 8 warps of 64 x 32, mma.sync.m16n8k8 TF32 with fp32
+// accumulation, register-staged double buffering (the next tile's global loads are in flight while this one is
+// multiplied; one __syncthreads per k step).  SPLIT = 3 is the error-compensated "3xTF32" product
+//     a b ~= a_hi b_hi + a_lo b_hi + a_hi b_lo,   x_hi = tf32(x), x_lo = tf32(x - x_hi)
+// which keeps fp32-level accuracy (the dropped a_lo b_lo term is 2^-22 relative) at three MMAs per product - still far
+// above the FFMA rate; SPLIT = 1 is plain TF32 (10-bit mantissa operands).
+constexpr int TM = 128, TN = 128, TK = 16, TPAD = 8;
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <int SPLIT>
+__global__ void __launch_bounds__(256) tgemm_kernel(const Gemm p) {
+  __shared__ float As[2][TK][TM + TPAD];
+  __shared__ float Bs[2][TK][TN + TPAD];
+  const int z1 = blockIdx.z / p.nz2, z2 = blockIdx.z % p.nz2;
+  const float* __restrict__ A = p.A + z1 * p.bA1 + z2 * p.bA2;
+  const float* __restrict__ B = p.B + z1 * p.bB1 + z2 * p.bB2;
+  float* C = p.C + z1 * p.bC1 + z2 * p.bC2;
+  const int m0 = blockIdx.x * TM, n0 = blockIdx.y * TN;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;
+  const bool a_kfast = p.sAk == 1, b_kfast = p.sBk == 1;
+  float acc[4][4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int r = 0; r < 4; ++r) acc[i][j][r] = 0.f;
+  // Operand addressing hoisted out of the k loop: element r of this thread differs from element 0 by a constant (m, k)
+  // step, so one base pointer per operand, one 64-bit step and a pointer bump per k tile replace sixteen
+  // multiply-add address computations per tile (measured: with them the kernel spent more time forming addresses than
+  // in the MMAs, 21 TFLOP/s).
+  float ra[8], rb[8];
+  int am, ak, a_dm, a_dk, bn, bk, b_dn, b_dk;
+  if (a_kfast) { ak = threadIdx.x % TK; am = threadIdx.x / TK; a_dm = 256 / TK; a_dk = 0; }
+  else { am = threadIdx.x % TM; ak = threadIdx.x / TM; a_dm = 0; a_dk = 256 / TM; }
+  if (b_kfast) { bk = threadIdx.x % TK; bn = threadIdx.x / TK; b_dn = 256 / TK; b_dk = 0; }
+  else { bn = threadIdx.x % TN; bk = threadIdx.x / TN; b_dn = 0; b_dk = 256 / TN; }
+  const float* pa = A + static_cast<long>(m0 + am) * p.sAm + static_cast<long>(ak) * p.sAk;
+  const float* pb = B + static_cast<long>(n0 + bn) * p.sBn + static_cast<long>(bk) * p.sBk;
+  const long a_step = static_cast<long>(a_dm) * p.sAm + static_cast<long>(a_dk) * p.sAk;
+  const long b_step = static_cast<long>(b_dn) * p.sBn + static_cast<long>(b_dk) * p.sBk;
+  const long a_tile = static_cast<long>(TK) * p.sAk, b_tile = static_cast<long>(TK) * p.sBk;
+  auto gload = [&](int k0) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      ra[r] = (m0 + am + r * a_dm < p.M && k0 + ak + r * a_dk < p.K) ? pa[r * a_step] : 0.f;
+      rb[r] = (n0 + bn + r * b_dn < p.N && k0 + bk + r * b_dk < p.K) ? pb[r * b_step] : 0.f;
+    }
+    pa += a_tile;
+    pb += b_tile;
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      As[buf][ak + r * a_dk][am + r * a_dm] = ra[r];
+      Bs[buf][bk + r * b_dk][bn + r * b_dn] = rb[r];
+    }
+  };
+  gload(0);
+  sstore(0);
+  __syncthreads();
+  int buf = 0;
+  for (int k0 = 0; k0 < p.K; k0 += TK) {
+    const bool more = k0 + TK < p.K;
+    if (more) gload(k0 + TK);
+#pragma unroll
+    for (int ks = 0; ks < TK; ks += 8) {
+      uint32_t bh[4][2], bl[4][2];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float b0 = Bs[buf][ks + t][wn + j * 8 + g], b1 = Bs[buf][ks + t + 4][wn + j * 8 + g];
+        bh[j][0] = to_tf32(b0); bh[j][1] = to_tf32(b1);
+        if (SPLIT == 3) { bl[j][0] = to_tf32(b0 - __uint_as_float(bh[j][0])); bl[j][1] = to_tf32(b1 - __uint_as_float(bh[j][1])); }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float a[4] = {As[buf][ks + t][wm + i * 16 + g], As[buf][ks + t][wm + i * 16 + g + 8],
+                            As[buf][ks + t + 4][wm + i * 16 + g], As[buf][ks + t + 4][wm + i * 16 + g + 8]};
+        uint32_t ah[4], al[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          ah[r] = to_tf32(a[r]);
+          if (SPLIT == 3) al[r] = to_tf32(a[r] - __uint_as_float(ah[r]));
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (SPLIT == 3) {          // small terms first
+            mma_tf32(acc[i][j], al, bh[j]);
+            mma_tf32(acc[i][j], ah, bl[j]);
+          }
+          mma_tf32(acc[i][j], ah, bh[j]);
+        }
+      }
+    }
+    if (more) sstore(buf ^ 1);
+    __syncthreads();
+    buf ^= 1;
+  }
+  // Epilogue.  `C += v` (conv taps after the first, residual gradients) is done 16 values at a time: all the old
+  // values are requested first, then added and stored.  One read-modify-write at a time, each waiting out a full memory
+  // round trip, was half of this kernel's run time (64 dependent round trips per thread).
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float* cp[16];
+    float old[16];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int m = m0 + wm + i * 16 + g + (r >> 1) * 8, n = n0 + wn + j * 8 + 2 * t + (r & 1);
+        cp[j * 4 + r] = (m < p.M && n < p.N) ? C + m * p.sCm + n * p.sCn : nullptr;
+      }
+    if (p.mode == 1) {
+#pragma unroll
+      for (int q = 0; q < 16; ++q) old[q] = cp[q] ? *cp[q] : 0.f;
+    }
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      if (!cp[q]) continue;
+      const float v = p.alpha * acc[i][q >> 2][q & 3];
+      if (p.mode == 0) *cp[q] = v;
+      else if (p.mode == 1) *cp[q] = old[q] + v;
+      else atomicAdd(cp[q], v);
+    }
+  }
+}
+
 __device__ __forceinline__ float warp_sum_f(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
