@@ -39,9 +39,26 @@ void gemm(Ctx& c, Gemm p, int nz) {
   if (p.nz2 <= 0) p.nz2 = 1;
   const int mode = train_gemm_mode();
   if (mode != 0 && p.M >= 32 && p.N >= 32) {
-    dim3 grid((p.M + trn::TM - 1) / trn::TM, (p.N + trn::TN - 1) / trn::TN, nz);
-    if (mode == 3) trn::tgemm_kernel<3><<<grid, 256, 0, c.st>>>(p);
-    else trn::tgemm_kernel<1><<<grid, 256, 0, c.st>>>(p);
+    static bool configured = false;
+    if (!configured) {
+      MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<3, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(128)));
+      MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<1, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(128)));
+      MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<3, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(64)));
+      MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(64)));
+      configured = true;
+    }
+    // 64-row tiles only for short M: measured at cfg5's shape, trading 128-row tiles for twice the blocks on the
+    // ~128-block GEMMs is slower (28.9 against 28.2 ms per step: B fragments are re-read per flop twice as often)
+    const int tm = p.M <= 64 ? 64 : 128;
+    dim3 grid((p.M + tm - 1) / tm, (p.N + trn::TN - 1) / trn::TN, nz);
+    const int smem = trn::tgemm_smem_bytes(tm);
+    if (tm == 128) {
+      if (mode == 3) trn::tgemm_kernel<3, 128><<<grid, 256, smem, c.st>>>(p);
+      else trn::tgemm_kernel<1, 128><<<grid, 256, smem, c.st>>>(p);
+    } else {
+      if (mode == 3) trn::tgemm_kernel<3, 64><<<grid, 256, smem, c.st>>>(p);
+      else trn::tgemm_kernel<1, 64><<<grid, 256, smem, c.st>>>(p);
+    }
   } else {
     dim3 grid((p.M + trn::BM - 1) / trn::BM, (p.N + trn::BN - 1) / trn::BN, nz);
     trn::sgemm_kernel<<<grid, 256, 0, c.st>>>(p);

@@ -89,12 +89,19 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const Gemm p) {
 }
 
 // The same contract on the tensor cores: 128 x 128 x 16 tiles, 8 warps of 64 x 32, mma.sync.m16n8k8 TF32 with fp32
-// accumulation, register-staged double buffering (the next tile's global loads are in flight while this one is
-// multiplied; one __syncthreads per k step).  SPLIT = 3 is the error-compensated "3xTF32" product
+// accumulation, operands through a three-stage cp.async ring (one __syncthreads per k step).  SPLIT = 3 is the error-compensated "3xTF32" product
 //     a b ~= a_hi b_hi + a_lo b_hi + a_hi b_lo,   x_hi = tf32(x), x_lo = tf32(x - x_hi)
 // which keeps fp32-level accuracy (the dropped a_lo b_lo term is 2^-22 relative) at three MMAs per product - still far
 // above the FFMA rate; SPLIT = 1 is plain TF32 (10-bit mantissa operands).
-constexpr int TM = 128, TN = 128, TK = 16, TPAD = 8;
+constexpr int TN = 128, TK = 16, TPAD = 8, TSTAGES = 3;
+constexpr int tgemm_smem_bytes(int tm) { return TSTAGES * TK * (tm + TPAD + TN + TPAD) * 4; }
+
+// 4-byte asynchronous copy global -> shared (any element stride); `ok == false` writes a zero without reading
+__device__ __forceinline__ void cp_async4(float* dst, const float* src, bool ok) {
+  const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst));
+  const int n = ok ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
 
 __device__ __forceinline__ uint32_t to_tf32(float x) {
   uint32_t r;
@@ -107,17 +114,21 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], 
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
 }
 
-template <int SPLIT>
+// TM = 128 (warps of 64 x 32) or 64 (warps of 32 x 32, for M <= 64)
+template <int SPLIT, int TM>
 __global__ void __launch_bounds__(256) tgemm_kernel(const Gemm p) {
-  __shared__ float As[2][TK][TM + TPAD];
-  __shared__ float Bs[2][TK][TN + TPAD];
+  constexpr int MI = TM / 32;              // 16-row MMA tiles per warp
+  constexpr int RA = TM * TK / 256;        // A elements per thread per k tile
+  extern __shared__ float tg_smem[];
+  float (*As)[TK][TM + TPAD] = reinterpret_cast<float (*)[TK][TM + TPAD]>(tg_smem);
+  float (*Bs)[TK][TN + TPAD] = reinterpret_cast<float (*)[TK][TN + TPAD]>(tg_smem + TSTAGES * TK * (TM + TPAD));
   const int z1 = blockIdx.z / p.nz2, z2 = blockIdx.z % p.nz2;
   const float* __restrict__ A = p.A + z1 * p.bA1 + z2 * p.bA2;
   const float* __restrict__ B = p.B + z1 * p.bB1 + z2 * p.bB2;
   float* C = p.C + z1 * p.bC1 + z2 * p.bC2;
   const int m0 = blockIdx.x * TM, n0 = blockIdx.y * TN;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;
+  const int wm = (warp >> 2) * (TM / 2), wn = (warp & 3) * 32;
   const bool a_kfast = p.sAk == 1, b_kfast = p.sBk == 1;
   float acc[4][4][4];
 #pragma unroll
@@ -130,7 +141,6 @@ __global__ void __launch_bounds__(256) tgemm_kernel(const Gemm p) {
   // step, so one base pointer per operand, one 64-bit step and a pointer bump per k tile replace sixteen
   // multiply-add address computations per tile (measured: with them the kernel spent more time forming addresses than
   // in the MMAs, 21 TFLOP/s).
-  float ra[8], rb[8];
   int am, ak, a_dm, a_dk, bn, bk, b_dn, b_dk;
   if (a_kfast) { ak = threadIdx.x % TK; am = threadIdx.x / TK; a_dm = 256 / TK; a_dk = 0; }
   else { am = threadIdx.x % TM; ak = threadIdx.x / TM; a_dm = 0; a_dk = 256 / TM; }
@@ -141,29 +151,33 @@ __global__ void __launch_bounds__(256) tgemm_kernel(const Gemm p) {
   const long a_step = static_cast<long>(a_dm) * p.sAm + static_cast<long>(a_dk) * p.sAk;
   const long b_step = static_cast<long>(b_dn) * p.sBn + static_cast<long>(b_dk) * p.sBk;
   const long a_tile = static_cast<long>(TK) * p.sAk, b_tile = static_cast<long>(TK) * p.sBk;
-  auto gload = [&](int k0) {
+  // Tiles travel global -> shared with 4-byte cp.async (any stride, zero fill outside the matrix) through a ring of
+  // TSTAGES buffers: two tiles are in flight while one is multiplied.  With register staging and one tile of look-ahead
+  // every k step waited out a memory round trip (measured 3.2 us per k step against 1.2 us of MMA issue).
+  auto issue = [&](int k0, int buf) {
+    if (k0 < p.K) {
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      ra[r] = (m0 + am + r * a_dm < p.M && k0 + ak + r * a_dk < p.K) ? pa[r * a_step] : 0.f;
-      rb[r] = (n0 + bn + r * b_dn < p.N && k0 + bk + r * b_dk < p.K) ? pb[r * b_step] : 0.f;
-    }
-    pa += a_tile;
-    pb += b_tile;
-  };
-  auto sstore = [&](int buf) {
+      for (int r = 0; r < RA; ++r) {
+        const bool oka = m0 + am + r * a_dm < p.M && k0 + ak + r * a_dk < p.K;
+        cp_async4(&As[buf][ak + r * a_dk][am + r * a_dm], oka ? pa + r * a_step : A, oka);
+      }
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      As[buf][ak + r * a_dk][am + r * a_dm] = ra[r];
-      Bs[buf][bk + r * b_dk][bn + r * b_dn] = rb[r];
+      for (int r = 0; r < 8; ++r) {
+        const bool okb = n0 + bn + r * b_dn < p.N && k0 + bk + r * b_dk < p.K;
+        cp_async4(&Bs[buf][bk + r * b_dk][bn + r * b_dn], okb ? pb + r * b_step : B, okb);
+      }
+      pa += a_tile;
+      pb += b_tile;
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  gload(0);
-  sstore(0);
-  __syncthreads();
+#pragma unroll
+  for (int s = 0; s < TSTAGES - 1; ++s) issue(s * TK, s);
   int buf = 0;
   for (int k0 = 0; k0 < p.K; k0 += TK) {
-    const bool more = k0 + TK < p.K;
-    if (more) gload(k0 + TK);
+    asm volatile("cp.async.wait_group %0;" ::"n"(TSTAGES - 2) : "memory");
+    __syncthreads();      // this tile has landed for every thread; the buffer refilled next is no longer being read
+    issue(k0 + (TSTAGES - 1) * TK, (buf + TSTAGES - 1) % TSTAGES);
 #pragma unroll
     for (int ks = 0; ks < TK; ks += 8) {
       uint32_t bh[4][2], bl[4][2];
@@ -174,7 +188,7 @@ __global__ void __launch_bounds__(256) tgemm_kernel(const Gemm p) {
         if (SPLIT == 3) { bl[j][0] = to_tf32(b0 - __uint_as_float(bh[j][0])); bl[j][1] = to_tf32(b1 - __uint_as_float(bh[j][1])); }
       }
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
+      for (int i = 0; i < MI; ++i) {
         const float a[4] = {As[buf][ks + t][wm + i * 16 + g], As[buf][ks + t][wm + i * 16 + g + 8],
                             As[buf][ks + t + 4][wm + i * 16 + g], As[buf][ks + t + 4][wm + i * 16 + g + 8]};
         uint32_t ah[4], al[4];
@@ -193,15 +207,13 @@ __global__ void __launch_bounds__(256) tgemm_kernel(const Gemm p) {
         }
       }
     }
-    if (more) sstore(buf ^ 1);
-    __syncthreads();
-    buf ^= 1;
+    buf = (buf + 1) % TSTAGES;
   }
   // Epilogue.  `C += v` (conv taps after the first, residual gradients) is done 16 values at a time: all the old
   // values are requested first, then added and stored.  One read-modify-write at a time, each waiting out a full memory
   // round trip, was half of this kernel's run time (64 dependent round trips per thread).
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < MI; ++i) {
     float* cp[16];
     float old[16];
 #pragma unroll
