@@ -200,6 +200,8 @@ class Plan {
   DevBuf ws_est_[24];
   DevBuf ws_voc_[8];
   DevBuf ws_io_[8];
+  cudaStream_t copy_stream_ = nullptr;   // synthesise_host: mel read-back overlapping the vocoder
+  cudaEvent_t mel_ready_ = nullptr;
   std::map<std::tuple<int, int, int, int, long long>, std::unique_ptr<Program>> decode_cache_;   // (B,T,steps,spk,ptr-key)
   std::map<std::tuple<int, int>, std::unique_ptr<Program>> vocoder_cache_;
 

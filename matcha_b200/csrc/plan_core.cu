@@ -55,6 +55,8 @@ Plan::~Plan() {
   for (auto& b : ws_est_) if (b.p) cudaFree(b.p);
   for (auto& b : ws_voc_) if (b.p) cudaFree(b.p);
   for (auto& b : ws_io_) if (b.p) cudaFree(b.p);
+  if (mel_ready_) cudaEventDestroy(mel_ready_);
+  if (copy_stream_) cudaStreamDestroy(copy_stream_);
 }
 
 void* Plan::dalloc(size_t bytes) {

@@ -258,10 +258,26 @@ void Plan::synthesise_host(const float* mu, const float* mask, const float* z, c
   MB_CUDA(cudaMemcpyAsync(d_z, z, n_mel * 4, cudaMemcpyHostToDevice, st));
   MB_CUDA(cudaMemcpyAsync(d_mask, mask, n_mask * 4, cudaMemcpyHostToDevice, st));
   if (spks) MB_CUDA(cudaMemcpyAsync(d_spk, spks, n_spk * 4, cudaMemcpyHostToDevice, st));
-  synthesise(d_mu, d_mask, d_z, d_spk, B, T, n_steps, L, mel_mean, mel_std, nullptr, mel_out ? d_melo : nullptr, d_wav, st);
-  if (mel_out) MB_CUDA(cudaMemcpyAsync(mel_out, d_melo, n_out_mel * 4, cudaMemcpyDeviceToHost, st));
+  // The mel read-back (9 MB at cfg2) overlaps the vocoder: it is issued on a non-blocking copy stream as soon as the
+  // decode + crop have finished, while HiFi-GAN runs on the compute stream.
+  if (!copy_stream_) {
+    MB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+    MB_CUDA(cudaEventCreateWithFlags(&mel_ready_, cudaEventDisableTiming));
+  }
+  if (L < 1 || L > T) throw Error("vocoder length L must be in [1, T]");
+  float* dec = static_cast<float*>(ensure(ws_io_[1], n_mel * 4));
+  cfm_decode(d_mu, d_mask, d_z, d_spk, B, T, n_steps, dec, st);
+  if (mel_out) {
+    MB_CUDA(launch_affine_crop(dec, T, mel_std, mel_mean, d_melo, B, 80, L, st));
+    launches += 1;
+    MB_CUDA(cudaEventRecord(mel_ready_, st));
+    MB_CUDA(cudaStreamWaitEvent(copy_stream_, mel_ready_, 0));
+    MB_CUDA(cudaMemcpyAsync(mel_out, d_melo, n_out_mel * 4, cudaMemcpyDeviceToHost, copy_stream_));
+  }
+  hifigan_forward(dec, T, mel_std, mel_mean, B, L, d_wav, st);
   MB_CUDA(cudaMemcpyAsync(wav_out, d_wav, n_wav * 4, cudaMemcpyDeviceToHost, st));
   MB_CUDA(cudaStreamSynchronize(st));
+  if (mel_out) MB_CUDA(cudaStreamSynchronize(copy_stream_));
 }
 
 }  // namespace mb
