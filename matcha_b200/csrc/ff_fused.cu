@@ -256,10 +256,11 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (tid & 7) * 32));
       }
     }
-    auto ldp = [&](int col, float4 (&p)[6]) {   // bias, exp(alpha), 1/(exp(beta)+eps) of 8 hidden channels
-      p[0] = __ldg(reinterpret_cast<const float4*>(g.bias1 + col)); p[1] = __ldg(reinterpret_cast<const float4*>(g.bias1 + col) + 1);
-      p[2] = __ldg(reinterpret_cast<const float4*>(g.snake_a + col)); p[3] = __ldg(reinterpret_cast<const float4*>(g.snake_a + col) + 1);
-      p[4] = __ldg(reinterpret_cast<const float4*>(g.snake_invb + col)); p[5] = __ldg(reinterpret_cast<const float4*>(g.snake_invb + col) + 1);
+    float pc[6], pn[6];
+    auto ldpar = [&](int col, float (&pp)[6]) {   // lane l: channels col + l and col + 32 + l of the three arrays
+      pp[0] = __ldg(g.bias1 + col + lane); pp[1] = __ldg(g.bias1 + col + 32 + lane);
+      pp[2] = __ldg(g.snake_a + col + lane); pp[3] = __ldg(g.snake_a + col + 32 + lane);
+      pp[4] = __ldg(g.snake_invb + col + lane); pp[5] = __ldg(g.snake_invb + col + 32 + lane);
     };
     for (int n = 0; n < nt_cta; ++n) {
       const int tile = blockIdx.x + n * gridDim.x;
@@ -342,8 +343,13 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         const int jj = n * 8 + j, slot = jj & 1;
         uint8_t* mid_c = mid + slot * kFFMidBytes + half * 16384;
         const int nb = j * 128 + half * 64;                 // first hidden channel of this lane's 64 columns
-        float4 prm[2][6];
-        ldp(nb, prm[0]);                                    // in flight while the accumulator is waited for
+        // Per-channel parameters of this chunk (bias, exp(alpha), 1/(exp(beta)+eps) of 64 hidden channels): lane l holds
+        // channels l and 32 + l, fetched with six coalesced loads ONE CHUNK AHEAD, and every use is a warp shuffle.  As
+        // 48 broadcast LDG.128 per chunk issued one 8-channel group ahead, these loads were the kernel's dominant stall
+        // (long scoreboard: half of all warp-stall samples, profiles/r01_ncu_full_ff_fused.txt) - with ~226 KB of the SM
+        // carved out as shared memory the L1 does not hold even 13 KB of parameters.
+        if (j == 0 && n == 0) ldpar(nb, pc);
+        ldpar(((j + 1) & 7) * 128 + half * 64, pn);
         FW(mbar_wait(&t1_full[slot], (jj >> 1) & 1), ew[0]);
         tc_fence_after();
         float acc[2][32];
@@ -353,23 +359,24 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          if (q + 1 < 8) ldp(nb + 8 * (q + 1), prm[(q + 1) & 1]);
-          const float4* pq = prm[q & 1];
-          const float bv[8] = {pq[0].x, pq[0].y, pq[0].z, pq[0].w, pq[1].x, pq[1].y, pq[1].z, pq[1].w};
-          const float pa[8] = {pq[2].x, pq[2].y, pq[2].z, pq[2].w, pq[3].x, pq[3].y, pq[3].z, pq[3].w};
-          const float pb[8] = {pq[4].x, pq[4].y, pq[4].z, pq[4].w, pq[5].x, pq[5].y, pq[5].z, pq[5].w};
           float v[8];
           const float* a = acc[q >> 2] + 8 * (q & 3);
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) {
-            v[ch] = a[ch] + bv[ch];
-            const float sn = __sinf(v[ch] * pa[ch]);
-            v[ch] = fmaf(pb[ch] * sn, sn, v[ch]);
+            const int src = (8 * q + ch) & 31;
+            const float bv = __shfl_sync(0xffffffffu, pc[q >> 2], src);
+            const float pa = __shfl_sync(0xffffffffu, pc[2 + (q >> 2)], src);
+            const float pb = __shfl_sync(0xffffffffu, pc[4 + (q >> 2)], src);
+            v[ch] = a[ch] + bv;
+            const float sn = __sinf(v[ch] * pa);
+            v[ch] = fmaf(pb * sn, sn, v[ch]);
           }
           uint32_t off = static_cast<uint32_t>(r * 128 + q * 16);
           off ^= ((off >> 7) & 7u) << 4;
           *reinterpret_cast<uint4*>(mid_c + off) = pack8<T>(v);
         }
+#pragma unroll
+        for (int k = 0; k < 6; ++k) pc[k] = pn[k];
         tc_fence_before();
         fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async-proxy reads
         __syncwarp();
