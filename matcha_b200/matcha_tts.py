@@ -278,43 +278,46 @@ class MatchaTTS(nn.Module):
         if self.n_spks > 1:
             spks = self.spk_emb(spks)
         mu_x, logw, x_mask = self.encoder(x, x_lengths, spks)
-        y_max_length = y.shape[-1]
-        y_mask = sequence_mask(y_lengths, y_max_length).unsqueeze(1).to(x_mask)
-        attn_mask = x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)
+        y_mask = sequence_mask(y_lengths, y.shape[-1]).unsqueeze(1).to(x_mask)
         with torch.no_grad():
-            # log N(y_j; mu_x_i, I) for every (token, frame) pair, expanded into three terms as upstream
-            const = -0.5 * math.log(2 * math.pi) * self.n_feats
-            factor = -0.5 * torch.ones(mu_x.shape, dtype=mu_x.dtype, device=mu_x.device)
-            y_square = torch.matmul(factor.transpose(1, 2), y ** 2)
-            y_mu_double = torch.matmul(2.0 * (factor * mu_x).transpose(1, 2), y)
-            mu_square = torch.sum(factor * (mu_x ** 2), 1).unsqueeze(-1)
-            log_prior = y_square - y_mu_double + mu_square + const
-            attn = monotonic_align.maximum_path(log_prior, attn_mask.squeeze(1)).detach()
-        logw_ = torch.log(1e-8 + torch.sum(attn.unsqueeze(1), -1)) * x_mask
-        dur_loss = torch.sum((logw - logw_) ** 2) / torch.sum(x_lengths)        # utils/model.py:44-46
+            pair_mask = (x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)).squeeze(1)            # (B, Lx, T)
+            attn = monotonic_align.maximum_path(_log_prior(mu_x, y, self.n_feats), pair_mask).detach()
+        # duration head against the log of the aligned frame counts (utils/model.py:44-46)
+        frames_per_token = attn.sum(-1).unsqueeze(1)
+        dur_loss = torch.sum((logw - torch.log(1e-8 + frames_per_token) * x_mask) ** 2) / torch.sum(x_lengths)
         if out_size is not None:
-            # random segment of `out_size` frames per utterance (the Grad-TTS memory hack, matcha_tts.py:203-225)
-            max_offset = (y_lengths - out_size).clamp(0).tolist()
-            offsets = [random.choice(range(0, end)) if end > 0 else 0 for end in max_offset]
-            attn_cut = torch.zeros(attn.shape[0], attn.shape[1], out_size, dtype=attn.dtype, device=attn.device)
-            y_cut = torch.zeros(y.shape[0], self.n_feats, out_size, dtype=y.dtype, device=y.device)
-            cut_lengths = []
-            for i, off in enumerate(offsets):
-                n = out_size + min(int(y_lengths[i]) - out_size, 0)
-                cut_lengths.append(n)
-                y_cut[i, :, :n] = y[i, :, off:off + n]
-                attn_cut[i, :, :n] = attn[i, :, off:off + n]
-            y_cut_lengths = torch.tensor(cut_lengths, dtype=torch.long, device=y.device)
-            attn, y = attn_cut, y_cut
-            y_mask = sequence_mask(y_cut_lengths).unsqueeze(1).to(y_mask)
-        mu_y = torch.matmul(attn.squeeze(1).transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
+            attn, y, y_mask = _random_segments(attn, y, y_lengths, out_size, y_mask.dtype)
+        mu_y = torch.matmul(attn.transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
         diff_loss, _ = self.decoder.compute_loss(x1=y, mask=y_mask, mu=mu_y, spks=spks, cond=cond)
+        prior_loss = 0
         if self.prior_loss:
-            prior_loss = torch.sum(0.5 * ((y - mu_y) ** 2 + math.log(2 * math.pi)) * y_mask)
-            prior_loss = prior_loss / (torch.sum(y_mask) * self.n_feats)
-        else:
-            prior_loss = 0
+            nll = 0.5 * ((y - mu_y) ** 2 + math.log(2 * math.pi)) * y_mask
+            prior_loss = nll.sum() / (y_mask.sum() * self.n_feats)
         return dur_loss, prior_loss, diff_loss
+
+
+def _log_prior(mu_x, y, n_feats):
+    """log N(y_j; mu_i, I) for every (token i, frame j): (B, Lx, T).  The reference (matcha_tts.py:185-190) forms the
+    |y_j|^2 term with a (B, Lx, 80) x (B, 80, T) matmul against a constant; here it is a channel sum broadcast over tokens."""
+    y_sq = (y * y).sum(1, keepdim=True)                      # (B, 1, T)
+    mu_sq = (mu_x * mu_x).sum(1).unsqueeze(-1)               # (B, Lx, 1)
+    cross = torch.matmul(mu_x.transpose(1, 2), y)            # (B, Lx, T)
+    return -0.5 * (y_sq - 2.0 * cross + mu_sq) - 0.5 * math.log(2 * math.pi) * n_feats
+
+
+def _random_segments(attn, y, y_lengths, out_size, mask_dtype):
+    """One random window of `out_size` frames per utterance, zero-padded where the utterance is shorter (the Grad-TTS
+    memory hack the reference keeps, matcha_tts.py:203-225).  Returns the cut alignment, mel and frame mask."""
+    lengths = [int(v) for v in y_lengths.tolist()]
+    kept = [min(n, out_size) for n in lengths]
+    starts = [random.randrange(n - out_size) if n > out_size else 0 for n in lengths]
+    attn_seg = attn.new_zeros(attn.shape[0], attn.shape[1], out_size)
+    y_seg = y.new_zeros(y.shape[0], y.shape[1], out_size)
+    for i, (s0, n) in enumerate(zip(starts, kept)):
+        y_seg[i, :, :n] = y[i, :, s0:s0 + n]
+        attn_seg[i, :, :n] = attn[i, :, s0:s0 + n]
+    seg_mask = sequence_mask(torch.tensor(kept, device=y.device), out_size).unsqueeze(1).to(mask_dtype)
+    return attn_seg, y_seg, seg_mask
 
 
 def default_config(n_spks=1):

@@ -257,3 +257,28 @@ def test_training_forward_matches_reference_forward(name, monkeypatch):
     # autograd of the same encoder fed the CUDA-computed d(loss)/d(mu_y)): 3e-2.
     for k, rel in rels.items():
         assert rel <= (3e-2 if k == "encoder.prenet.proj.bias" else 2e-3), rels
+
+
+@pytest.mark.gpu
+def test_training_forward_segment_cut(monkeypatch):
+    """`out_size`: a window as long as the batch reproduces the uncut losses; a shorter one trains on zero-padded random
+    windows (finite losses, gradients reach encoder and decoder)."""
+    fx = _fx("fwd_lj_ragged")
+    model, _ = _training_model(fx)
+    model = model.cuda()
+    t, z = fx["t"].cuda(), fx["z"].cuda()
+    monkeypatch.setattr(torch, "rand", lambda *a, **k: t)
+    monkeypatch.setattr(torch, "randn_like", lambda *a, **k: z)
+    args = (fx["x"].cuda(), fx["x_lengths"].cuda(), fx["y"].cuda(), fx["y_lengths"].cuda())
+    full = model(*args, out_size=fx["y"].shape[-1])
+    for got, key in zip(full, ("dur_loss", "prior_loss", "diff_loss")):
+        assert abs(float(got) - float(fx[key])) <= 1e-3 * abs(float(fx[key])), key
+    monkeypatch.undo()
+    import random
+    random.seed(0)
+    dur, prior, diff = model(*args, out_size=16)
+    assert all(torch.isfinite(v) for v in (dur, prior, diff))
+    (dur + prior + diff).backward()
+    named = dict(model.named_parameters())
+    assert float(named["encoder.proj_m.weight"].grad.abs().sum()) > 0
+    assert float(named["decoder.estimator.final_proj.weight"].grad.abs().sum()) > 0
