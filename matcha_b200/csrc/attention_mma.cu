@@ -9,6 +9,16 @@
 namespace mb {
 
 namespace {
+constexpr float kLog2e = 1.4426950408889634f;
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+}  // namespace
+
+
+namespace {
 
 template <typename T> struct MmaT;
 template <> struct MmaT<__half> {
@@ -142,14 +152,17 @@ attention_mma_kernel(const T* __restrict__ qkv, const float* __restrict__ mask, 
     }
     mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    const float sc0 = __expf(m0 - mx0), sc1 = __expf(m1 - mx1);  // exp(-inf) = 0 on the first tile
+    // exp(s - m) as ex2(s log2e - m log2e): one FFMA + one MUFU per score (the checked __expf expansion is five
+    // instructions); m is finite from the first tile on (every tile 0 holds a valid key), -inf scores give ex2(-inf) = 0
+    const float nm0 = -mx0 * kLog2e, nm1 = -mx1 * kLog2e;
+    const float sc0 = ex2_ftz(fmaf(m0, kLog2e, nm0)), sc1 = ex2_ftz(fmaf(m1, kLog2e, nm1));  // 0 on the first tile (m = -inf)
     m0 = mx0; m1 = mx1;
     float ps0 = 0.f, ps1 = 0.f;
     uint32_t pa[4][4];  // P as A fragments for the 4 k-steps over keys
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float p0 = __expf(s[j][0] - m0), p1 = __expf(s[j][1] - m0);
-      const float p2 = __expf(s[j][2] - m1), p3 = __expf(s[j][3] - m1);
+      const float p0 = ex2_ftz(fmaf(s[j][0], kLog2e, nm0)), p1 = ex2_ftz(fmaf(s[j][1], kLog2e, nm0));
+      const float p2 = ex2_ftz(fmaf(s[j][2], kLog2e, nm1)), p3 = ex2_ftz(fmaf(s[j][3], kLog2e, nm1));
       ps0 += p0 + p1; ps1 += p2 + p3;
       pa[j >> 1][(j & 1) * 2] = MmaT<T>::pack(p0, p1);
       pa[j >> 1][(j & 1) * 2 + 1] = MmaT<T>::pack(p2, p3);
