@@ -202,6 +202,8 @@ class Plan {
   DevBuf ws_io_[8];
   cudaStream_t copy_stream_ = nullptr;   // synthesise_host: mel read-back overlapping the vocoder
   cudaEvent_t mel_ready_ = nullptr;
+  cudaEvent_t wav_ready_[4] = {nullptr, nullptr, nullptr, nullptr};
+  float* host_wav_dst_ = nullptr;        // set only while synthesise_host runs the vocoder
   std::map<std::tuple<int, int, int, int, long long>, std::unique_ptr<Program>> decode_cache_;   // (B,T,steps,spk,ptr-key)
   std::map<std::tuple<int, int>, std::unique_ptr<Program>> vocoder_cache_;
 

@@ -221,11 +221,27 @@ void Plan::hifigan_forward(const float* mel, int Tsrc, float scale, float shift,
     }
   }
   const long Lw = static_cast<long>(L) * 256;
-  const void* a = ws_voc_[V_A].p;
-  if (dtype == MB200_F32) MB_CUDA(launch_conv_post<float>((const float*)a, gen_.post_w, gen_.post_b, wav, B, Lw, st));
-  else if (dtype == MB200_BF16) MB_CUDA(launch_conv_post<__nv_bfloat16>((const __nv_bfloat16*)a, gen_.post_w, gen_.post_b, wav, B, Lw, st));
-  else MB_CUDA(launch_conv_post<__half>((const __half*)a, gen_.post_w, gen_.post_b, wav, B, Lw, st));
-  launches += 2;
+  const char* a = static_cast<const char*>(ws_voc_[V_A].p);
+  // conv_post + tanh.  On the host-buffer path (synthesise_host) it runs in four batch slices and each slice's waveform
+  // starts its device -> host copy on the copy stream while the next slice is computed: the read-back (29.5 MB at cfg2)
+  // is the longest single item outside the kernels.
+  const int parts = (host_wav_dst_ && B >= 4) ? 4 : 1;
+  for (int q = 0; q < parts; ++q) {
+    const int b0 = static_cast<int>(static_cast<long>(B) * q / parts), b1 = static_cast<int>(static_cast<long>(B) * (q + 1) / parts);
+    const char* aq = a + static_cast<size_t>(b0) * Lw * 32 * esize(dtype);
+    float* wq = wav + static_cast<long>(b0) * Lw;
+    if (dtype == MB200_F32) MB_CUDA(launch_conv_post<float>((const float*)aq, gen_.post_w, gen_.post_b, wq, b1 - b0, Lw, st));
+    else if (dtype == MB200_BF16) MB_CUDA(launch_conv_post<__nv_bfloat16>((const __nv_bfloat16*)aq, gen_.post_w, gen_.post_b, wq, b1 - b0, Lw, st));
+    else MB_CUDA(launch_conv_post<__half>((const __half*)aq, gen_.post_w, gen_.post_b, wq, b1 - b0, Lw, st));
+    launches += 1;
+    if (host_wav_dst_) {
+      MB_CUDA(cudaEventRecord(wav_ready_[q], st));
+      MB_CUDA(cudaStreamWaitEvent(copy_stream_, wav_ready_[q], 0));
+      MB_CUDA(cudaMemcpyAsync(host_wav_dst_ + static_cast<long>(b0) * Lw, wq, static_cast<size_t>(b1 - b0) * Lw * 4,
+                              cudaMemcpyDeviceToHost, copy_stream_));
+    }
+  }
+  launches += 1;
 }
 
 void Plan::synthesise(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
@@ -263,6 +279,7 @@ void Plan::synthesise_host(const float* mu, const float* mask, const float* z, c
   if (!copy_stream_) {
     MB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
     MB_CUDA(cudaEventCreateWithFlags(&mel_ready_, cudaEventDisableTiming));
+    for (auto& e : wav_ready_) MB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   if (L < 1 || L > T) throw Error("vocoder length L must be in [1, T]");
   float* dec = static_cast<float*>(ensure(ws_io_[1], n_mel * 4));
@@ -274,10 +291,16 @@ void Plan::synthesise_host(const float* mu, const float* mask, const float* z, c
     MB_CUDA(cudaStreamWaitEvent(copy_stream_, mel_ready_, 0));
     MB_CUDA(cudaMemcpyAsync(mel_out, d_melo, n_out_mel * 4, cudaMemcpyDeviceToHost, copy_stream_));
   }
-  hifigan_forward(dec, T, mel_std, mel_mean, B, L, d_wav, st);
-  MB_CUDA(cudaMemcpyAsync(wav_out, d_wav, n_wav * 4, cudaMemcpyDeviceToHost, st));
+  host_wav_dst_ = wav_out;                 // hifigan_forward slices conv_post and queues the waveform copies itself
+  try {
+    hifigan_forward(dec, T, mel_std, mel_mean, B, L, d_wav, st);
+  } catch (...) {
+    host_wav_dst_ = nullptr;
+    throw;
+  }
+  host_wav_dst_ = nullptr;
   MB_CUDA(cudaStreamSynchronize(st));
-  if (mel_out) MB_CUDA(cudaStreamSynchronize(copy_stream_));
+  MB_CUDA(cudaStreamSynchronize(copy_stream_));
 }
 
 }  // namespace mb

@@ -236,6 +236,31 @@ def test_hot_path_matches_oracle(prec, c_in):
     assert length == 60
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("b", [4, 7])
+def test_host_buffer_path_equals_device_path(b):
+    """`mb200_synthesise_host` with B >= 4 slices conv_post and overlaps the mel / waveform read-back with compute on a
+    copy stream: its results must equal the device-pointer entry point's (same kernels, same inputs), pinned or pageable."""
+    g = torch.Generator().manual_seed(17)
+    t_pad, n_steps, length = 24, 2, 23
+    lens = [24, 23, 9, 16, 24, 5, 20][:b]
+    mu = torch.randn(b, 80, t_pad, generator=g)
+    z = torch.randn(b, 80, t_pad, generator=g) * 0.667
+    mask = weights.prefix_mask(lens, t_pad)
+    plan = Plan("fp32", 160)
+    plan.load_estimator(weights.estimator_state_dict(160, seed=5))
+    plan.load_generator(weights.generator_state_dict(6))
+    dec, mel, wav = plan.synthesise(mu, mask, z, n_steps, length, -5.5, 2.1)
+    for pin in (False, True):
+        mel_out, wav_out = torch.empty(b, 80, length), torch.empty(b, 1, length * 256)
+        if pin:
+            mel_out, wav_out = mel_out.pin_memory(), wav_out.pin_memory()
+        for _ in range(2):     # twice: the second call reuses streams, events and staging buffers
+            mel_h, wav_h = plan.synthesise_host(mu, mask.contiguous(), z, n_steps, length, -5.5, 2.1, mel_out=mel_out, wav_out=wav_out)
+            assert float((wav_h.reshape(b, -1) - wav.cpu().reshape(b, -1)).abs().max()) <= 1e-5
+            assert float((mel_h - mel.cpu()).abs().max()) <= 1e-5
+
+
 def test_module_api_is_drop_in(golden_dir):
     """The nn.Module surface: CFM.forward / solve_euler / estimator / compute_loss and Generator.forward."""
     fx = _load(golden_dir, "est_lj_ragged")
