@@ -17,6 +17,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 #include "plan.h"
 
 namespace mb {
@@ -25,7 +27,7 @@ namespace {
 
 constexpr float kMasNeg = -1e9f;
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 mas_kernel(const float* __restrict__ value, const float* __restrict__ mask, int Tx, int Ty, int TC, float* __restrict__ path,
            uint32_t* __restrict__ dec) {
   extern __shared__ float sm[];
@@ -33,7 +35,7 @@ mas_kernel(const float* __restrict__ value, const float* __restrict__ mask, int 
   float* colB = colA + Tx;             // [Tx] current column
   float* tile = colB + Tx;             // [Tx][TC + 1] masked input values of TC frames
   __shared__ int s_cnt[2];
-  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, nt = blockDim.x;
   const long base = static_cast<long>(b) * Tx * Ty;
   const int W = (Tx + 31) >> 5;
 
@@ -41,13 +43,13 @@ mas_kernel(const float* __restrict__ value, const float* __restrict__ mask, int 
   if (tid < 2) s_cnt[tid] = 0;
   __syncthreads();
   int cx = 0, cy = 0;
-  for (int x = tid; x < Tx; x += 256) cx += mask[base + static_cast<long>(x) * Ty] != 0.f;
-  for (int y = tid; y < Ty; y += 256) cy += mask[base + y] != 0.f;
+  for (int x = tid; x < Tx; x += nt) cx += mask[base + static_cast<long>(x) * Ty] != 0.f;
+  for (int y = tid; y < Ty; y += nt) cy += mask[base + y] != 0.f;
   atomicAdd(&s_cnt[0], cx);
   atomicAdd(&s_cnt[1], cy);
   // path = 0 everywhere; the back-tracking thread sets the ones afterwards
-  for (long i = tid; i < static_cast<long>(Tx) * Ty; i += 256) path[base + i] = 0.f;
-  for (int x = tid; x < Tx; x += 256) colA[x] = 0.f;
+  for (long i = tid; i < static_cast<long>(Tx) * Ty; i += nt) path[base + i] = 0.f;
+  for (int x = tid; x < Tx; x += nt) colA[x] = 0.f;
   __syncthreads();
   const int t_x = s_cnt[0], t_y = s_cnt[1];
   if (t_x <= 0 || t_y <= 0) return;
@@ -56,7 +58,7 @@ mas_kernel(const float* __restrict__ value, const float* __restrict__ mask, int 
   float* cur = colB;
   const int x_round = ((t_x + 31) >> 5) << 5;
   for (int y0 = 0; y0 < t_y; y0 += TC) {
-    for (int idx = tid; idx < t_x * TC; idx += 256) {
+    for (int idx = tid; idx < t_x * TC; idx += nt) {
       const int x = idx / TC, c = idx - x * TC, y = y0 + c;
       float v = 0.f;
       if (y < t_y) v = value[base + static_cast<long>(x) * Ty + y] * mask[base + static_cast<long>(x) * Ty + y];
@@ -67,7 +69,7 @@ mas_kernel(const float* __restrict__ value, const float* __restrict__ mask, int 
     for (int c = 0; c < nc; ++c) {
       const int y = y0 + c;
       const int lo = max(0, t_x + y - t_y), hi = min(t_x, y + 1);
-      for (int x = tid; x < x_round; x += 256) {
+      for (int x = tid; x < x_round; x += nt) {
         bool step = false;
         if (x < t_x) {
           const float in = tile[x * (TC + 1) + c];
@@ -116,7 +118,12 @@ void maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, 
     MB_CUDA(cudaFuncSetAttribute(mas_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     configured = true;
   }
-  mas_kernel<<<B, 256, bytes(TC), st>>>(value, mask, Tx, Ty, TC, path, static_cast<uint32_t*>(workspace));
+  // 1024 threads: one CTA per utterance means few resident warps, and both the tile loads and the per-column pass are
+  // latency-bound (measured 256 / 512 / 1024 threads: 0.34 / 0.29 / 0.26 ms at 170 x 512, 5.2 / 3.4 / 2.4 ms at 667 x 2001)
+  int threads = 1024;
+  if (const char* e = std::getenv("MB200_MAS_THREADS")) threads = std::atoi(e);   // developer switch (256 / 512 / 1024)
+  if (threads != 256 && threads != 512 && threads != 1024) throw Error("MB200_MAS_THREADS must be 256, 512 or 1024");
+  mas_kernel<<<B, threads, bytes(TC), st>>>(value, mask, Tx, Ty, TC, path, static_cast<uint32_t*>(workspace));
   MB_CUDA(cudaGetLastError());
 }
 
