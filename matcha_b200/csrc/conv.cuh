@@ -143,7 +143,14 @@ struct EpiParams {
   const float* snake_invb;
   const float* mask;       // [B][T_o] float 0/1 or null; used by gn_raw and mask_out
   int mask_out;            // v *= mask
-  float* stats_out;        // GroupNorm partial sums [B][8][2] accumulated from v (32 channels per group)
+  // GroupNorm statistics of v, [B][8][2] = (sum, sum of squares) per 32-channel group over all T_out rows, in a FIXED
+  // summation order (no float atomics): every warp stores the partial sums of its 32 rows in slot t/32 of stats_part
+  // ([B][8][stats_slots] float2, stats_slots = ceil(T_out / 32)) and bumps stats_cnt[b][g]; the warp that arrives last
+  // adds the slots in index order into stats_out and re-arms the counter (gn_stats_commit below).
+  float* stats_out;
+  float2* stats_part;
+  int* stats_cnt;
+  int stats_slots;
   // Euler update fused into final_proj (flow_matching.py:79): x += dt * v ; second output = x * mask
   float* x_state;  int x_ld;  float dt;
   void* out0;  int out0_ld;  int out0_f32;  float out0_slope;   // main store; slope != 1 applies LeakyReLU
@@ -209,6 +216,26 @@ __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
+}
+
+// One lane of a warp hands in the warp's partial GroupNorm sums over rows [32 slot, 32 slot + 32) of (b, group).
+// Run-to-run deterministic: which warp arrives last changes, what it computes does not.
+__device__ __forceinline__ void gn_stats_commit(const EpiParams& e, int b, int group, int slot, float s, float ss) {
+  const int bg = b * 8 + group;
+  float2* part = e.stats_part + static_cast<size_t>(bg) * e.stats_slots;
+  __stcg(part + slot, make_float2(s, ss));
+  __threadfence();
+  if (atomicAdd(e.stats_cnt + bg, 1) == e.stats_slots - 1) {
+    __threadfence();
+    float a = 0.f, q = 0.f;
+    for (int i = 0; i < e.stats_slots; ++i) {
+      const float2 p = __ldcg(part + i);
+      a += p.x; q += p.y;
+    }
+    e.stats_out[bg * 2] = a;
+    e.stats_out[bg * 2 + 1] = q;
+    e.stats_cnt[bg] = 0;
+  }
 }
 
 // Fused epilogue for one thread's 32-channel slice [n0, n0+32) of output row (b, t, phase).
@@ -290,12 +317,9 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& e, int b, int t,
     }
     s = warp_sum(s);
     ss = warp_sum(ss);
-    // all rows of a warp belong to the same batch element b (tiles never straddle batch elements)
-    if ((threadIdx.x & 31) == 0 && do_store) {
-      float* st = e.stats_out + (static_cast<long>(b) * 8 + (n0 >> 5)) * 2;
-      atomicAdd(st, s);
-      atomicAdd(st + 1, ss);
-    }
+    // all rows of a warp belong to the same batch element b (tiles never straddle batch elements); lane 0 holds the
+    // warp's first row, a multiple of 32
+    if ((threadIdx.x & 31) == 0 && do_store && valid) gn_stats_commit(e, b, n0 >> 5, t >> 5, s, ss);
   }
   if (!valid) return;
   if (e.x_state) {

@@ -8,7 +8,7 @@ namespace mb {
 
 namespace {
 enum EstBuf { XIN, RAW, H1, RAW2, RES, LN, QKV, ATT, HID, FF, YA, YB, SKIP0, SKIP1, XSTATE, MU_NTC, MASK_T, MASK_H, SPK,
-              STATS, TVALS, TEMB0, TEMB1, TPROJ };
+              STATS, TVALS, TEMB0, TEMB1, TPROJ, STATS_PART, STATS_CNT };
 
 const HostTensor& need(const StateDict& sd, const std::string& k) {
   auto it = sd.find(k);
@@ -112,7 +112,11 @@ void Plan::estimator_buffers(int B, int T) {
   ensure(ws_est_[MASK_T], rows * 4);
   ensure(ws_est_[MASK_H], rows / 2 * 4);
   ensure(ws_est_[SPK], static_cast<size_t>(B) * 64 * 4);
+  // GroupNorm statistics of the 13 Block1D convs: final sums, per-32-row partial sums and arrival counters (conv.cuh,
+  // gn_stats_commit).  The counters start at zero (ensure() clears new allocations) and every launch re-arms them.
   ensure(ws_est_[STATS], static_cast<size_t>(13) * B * 16 * 4);
+  ensure(ws_est_[STATS_PART], static_cast<size_t>(13) * B * 8 * ((T + 31) / 32) * 8);
+  ensure(ws_est_[STATS_CNT], static_cast<size_t>(13) * B * 8 * 4);
 }
 
 // Appends one Decoder.forward to `prog`.  tproj: [.. ][6][256] time projections for this call (bstride 0 when t is a
@@ -127,19 +131,21 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   const float* maskT = static_cast<const float*>(buf(MASK_T));
   const float* maskH = static_cast<const float*>(buf(MASK_H));
   float* stats_base = static_cast<float*>(buf(STATS));
+  float2* part_base = static_cast<float2*>(buf(STATS_PART));
+  int* cnt_base = static_cast<int*>(buf(STATS_CNT));
   int stat_slot = 0;
   auto& ops = prog.ops;
   auto add = [&](Launch l) { ops.push_back(std::move(l)); prog.kernels++; };
-  auto next_stats = [&]() { return stats_base + static_cast<size_t>(stat_slot++) * B * 16; };
-
-  // stats of this call are zeroed in one memset
-  {
-    float* sb = stats_base;
-    const size_t bytes = static_cast<size_t>(13) * B * 16 * 4;
-    Launch ms([sb, bytes](cudaStream_t st) { return cudaMemsetAsync(sb, 0, bytes, st); });
-    ms.kind = 3;
-    ops.push_back(std::move(ms));
-  }
+  // statistics of the next Block1D conv over Tn rows: fills the epilogue's fields, returns the [B][8][2] sums the
+  // consumer reads.  Sums are written (not accumulated) in a fixed order, so nothing has to be cleared between calls.
+  auto next_stats = [&](EpiParams& e, int Tn) {
+    const int k = stat_slot++;
+    e.stats_out = stats_base + static_cast<size_t>(k) * B * 16;
+    e.stats_slots = (Tn + 31) / 32;
+    e.stats_part = part_base + static_cast<size_t>(k) * B * 8 * ((T + 31) / 32);
+    e.stats_cnt = cnt_base + static_cast<size_t>(k) * B * 8;
+    return e.stats_out;
+  };
 
   auto gn_mish = [&](const void* raw, const float* st, const float* g, const float* bta, const float* tadd, int tbs,
                      const float* mask, void* out, int Tn) {
@@ -172,14 +178,14 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   // ResnetBlock1D (decoder.py:46-61): in (1 or 2 sources, already masked) -> RES (unmasked), LN1(RES) -> LN
   auto resnet = [&](int r, Src s0, const Src* s1, int Tn, const float* mask, const TransformerW& X) {
     const ResnetW& R = est_.res[r];
-    float* st1 = next_stats();
-    float* st2 = next_stats();
     EpiParams e = epi();
-    e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32; e.stats_out = st1;
+    e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
+    const float* st1 = next_stats(e, Tn);
     add(conv_op(R.conv1, s0, s1, B, Tn, e));
     gn_mish(buf(RAW), st1, R.gn1_g, R.gn1_b, tproj + r * 256, tproj_bstride, mask, buf(H1), Tn);
     e = epi();
-    e.out0 = buf(RAW2); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32; e.stats_out = st2;
+    e.out0 = buf(RAW2); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
+    const float* st2 = next_stats(e, Tn);
     add(conv_op(R.conv2, Src{buf(H1), 256, 256, Tn}, nullptr, B, Tn, e));
     if (rq_supported()) {   // res_conv + GroupNorm/Mish + LayerNorm1 + QKV projection: one kernel (RES and QKV written)
       add(resqkv_op(R.res, X.qkv, s0, s1, buf(RAW2), st2, R.gn2_g, R.gn2_b, mask, buf(RES), X.ln1_g, X.ln1_b, buf(QKV), B, Tn));
@@ -263,9 +269,9 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   masked_conv(est_.up1, Src{buf(YA), 256, 256, T}, T, maskT, buf(YB));
   // final block + projection (decoder.py:440-443)
   {
-    float* stf = next_stats();
     EpiParams e = epi();
-    e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32; e.stats_out = stf;
+    e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
+    const float* stf = next_stats(e, T);
     add(conv_op(est_.final_conv, Src{buf(YB), 256, 256, T}, nullptr, B, T, e));
     gn_mish(buf(RAW), stf, est_.fgn_g, est_.fgn_b, nullptr, 0, maskT, buf(H1), T);
     e = epi();

@@ -197,7 +197,7 @@ class Plan {
   EstimatorW est_;
   GeneratorW gen_;
   // workspaces
-  DevBuf ws_est_[24];
+  DevBuf ws_est_[28];
   DevBuf ws_voc_[8];
   DevBuf ws_io_[8];
   cudaStream_t copy_stream_ = nullptr;   // synthesise_host: mel read-back overlapping the vocoder

@@ -71,9 +71,10 @@ class ChannelNorm(nn.Module):
         return F.layer_norm(x.transpose(1, 2), (x.shape[1],), self.gamma, self.beta, self.eps).transpose(1, 2)
 
 
-class _Prenet(nn.Module):  # text_encoder.py:36-67
-    def __init__(self, ch, k=5, n_layers=3):
+class _Prenet(nn.Module):  # text_encoder.py:36-67; ReLU -> Dropout(0.5) after every norm (:50, built at :356)
+    def __init__(self, ch, k=5, n_layers=3, p_dropout=0.5):
         super().__init__()
+        self.p_dropout = p_dropout
         self.conv_layers = nn.ModuleList(nn.Conv1d(ch, ch, k, padding=k // 2) for _ in range(n_layers))
         self.norm_layers = nn.ModuleList(ChannelNorm(ch) for _ in range(n_layers))
         self.proj = nn.Conv1d(ch, ch, 1)
@@ -83,13 +84,14 @@ class _Prenet(nn.Module):  # text_encoder.py:36-67
     def forward(self, x, x_mask):
         h = x
         for conv, norm in zip(self.conv_layers, self.norm_layers):
-            h = torch.relu(norm(conv(h * x_mask)))   # dropout is identity at inference
+            h = F.dropout(torch.relu(norm(conv(h * x_mask))), self.p_dropout, self.training)
         return (x + self.proj(h)) * x_mask
 
 
-class _DurationPredictor(nn.Module):  # text_encoder.py:70-93
-    def __init__(self, cin, filt, k):
+class _DurationPredictor(nn.Module):  # text_encoder.py:70-93; dropout after each norm (:77, :88, :92)
+    def __init__(self, cin, filt, k, p_dropout=0.0):
         super().__init__()
+        self.p_dropout = p_dropout
         self.conv_1 = nn.Conv1d(cin, filt, k, padding=k // 2)
         self.norm_1 = ChannelNorm(filt)
         self.conv_2 = nn.Conv1d(filt, filt, k, padding=k // 2)
@@ -97,8 +99,8 @@ class _DurationPredictor(nn.Module):  # text_encoder.py:70-93
         self.proj = nn.Conv1d(filt, 1, 1)
 
     def forward(self, x, x_mask):
-        x = self.norm_1(torch.relu(self.conv_1(x * x_mask)))
-        x = self.norm_2(torch.relu(self.conv_2(x * x_mask)))
+        x = F.dropout(self.norm_1(torch.relu(self.conv_1(x * x_mask))), self.p_dropout, self.training)
+        x = F.dropout(self.norm_2(torch.relu(self.conv_2(x * x_mask))), self.p_dropout, self.training)
         return self.proj(x * x_mask) * x_mask
 
 
@@ -116,9 +118,10 @@ def _rope(x, d, base=10000.0):
 
 
 class _SelfAttention(nn.Module):  # text_encoder.py:169-237 (no proximal bias in the shipped configs)
-    def __init__(self, ch, n_heads):
+    def __init__(self, ch, n_heads, p_dropout=0.0):
         super().__init__()
         assert ch % n_heads == 0
+        self.p_dropout = p_dropout     # on the attention probabilities (:207, :224)
         self.n_heads, self.k_channels = n_heads, ch // n_heads
         self.conv_q, self.conv_k, self.conv_v, self.conv_o = (nn.Conv1d(ch, ch, 1) for _ in range(4))
         for c in (self.conv_q, self.conv_k, self.conv_v):
@@ -132,34 +135,37 @@ class _SelfAttention(nn.Module):  # text_encoder.py:169-237 (no proximal bias in
         q, k = _rope(q, self.rope_dims), _rope(k, self.rope_dims)
         scores = torch.matmul(q, k.transpose(-2, -1)) / math.sqrt(self.k_channels)
         scores = scores.masked_fill(attn_mask == 0, -1e4)    # replaces, does not add (text_encoder.py:222)
-        o = torch.matmul(torch.softmax(scores, dim=-1), v)
+        o = torch.matmul(F.dropout(torch.softmax(scores, dim=-1), self.p_dropout, self.training), v)
         return self.conv_o(o.transpose(2, 3).reshape(b, c, t))
 
 
-class _FFN(nn.Module):  # text_encoder.py:240-257
-    def __init__(self, ch, filt, k):
+class _FFN(nn.Module):  # text_encoder.py:240-257; dropout after the ReLU (:243, :253)
+    def __init__(self, ch, filt, k, p_dropout=0.0):
         super().__init__()
+        self.p_dropout = p_dropout
         self.conv_1 = nn.Conv1d(ch, filt, k, padding=k // 2)
         self.conv_2 = nn.Conv1d(filt, ch, k, padding=k // 2)
 
     def forward(self, x, x_mask):
-        return self.conv_2(torch.relu(self.conv_1(x * x_mask)) * x_mask) * x_mask
+        h = F.dropout(torch.relu(self.conv_1(x * x_mask)), self.p_dropout, self.training)
+        return self.conv_2(h * x_mask) * x_mask
 
 
-class _Encoder(nn.Module):  # text_encoder.py:260-310
-    def __init__(self, ch, filt, n_heads, n_layers, k):
+class _Encoder(nn.Module):  # text_encoder.py:260-310; dropout on both sub-layer outputs (:266, :319-322)
+    def __init__(self, ch, filt, n_heads, n_layers, k, p_dropout=0.0):
         super().__init__()
-        self.attn_layers = nn.ModuleList(_SelfAttention(ch, n_heads) for _ in range(n_layers))
+        self.p_dropout = p_dropout
+        self.attn_layers = nn.ModuleList(_SelfAttention(ch, n_heads, p_dropout) for _ in range(n_layers))
         self.norm_layers_1 = nn.ModuleList(ChannelNorm(ch) for _ in range(n_layers))
-        self.ffn_layers = nn.ModuleList(_FFN(ch, filt, k) for _ in range(n_layers))
+        self.ffn_layers = nn.ModuleList(_FFN(ch, filt, k, p_dropout) for _ in range(n_layers))
         self.norm_layers_2 = nn.ModuleList(ChannelNorm(ch) for _ in range(n_layers))
 
     def forward(self, x, x_mask):
         attn_mask = x_mask.unsqueeze(2) * x_mask.unsqueeze(-1)
         for attn, n1, ffn, n2 in zip(self.attn_layers, self.norm_layers_1, self.ffn_layers, self.norm_layers_2):
             x = x * x_mask
-            x = n1(x + attn(x, attn_mask))
-            x = n2(x + ffn(x, x_mask))
+            x = n1(x + F.dropout(attn(x, attn_mask), self.p_dropout, self.training))
+            x = n2(x + F.dropout(ffn(x, x_mask), self.p_dropout, self.training))
         return x * x_mask
 
 
@@ -176,10 +182,11 @@ class TextEncoder(nn.Module):
         self.prenet = _Prenet(self.n_channels) if _get(p, "prenet", True) else None
         ch = self.n_channels + (spk_emb_dim if n_spks > 1 else 0)
         self.encoder = _Encoder(ch, _get(p, "filter_channels"), _get(p, "n_heads"), _get(p, "n_layers"),
-                                _get(p, "kernel_size"))
+                                _get(p, "kernel_size"), float(_get(p, "p_dropout", 0.0) or 0.0))
         self.proj_m = nn.Conv1d(ch, self.n_feats, 1)
         d = duration_predictor_params
-        self.proj_w = _DurationPredictor(ch, _get(d, "filter_channels_dp"), _get(d, "kernel_size"))
+        self.proj_w = _DurationPredictor(ch, _get(d, "filter_channels_dp"), _get(d, "kernel_size"),
+                                         float(_get(d, "p_dropout", 0.0) or 0.0))
 
     def forward(self, x, x_lengths, spks=None):
         h = self.emb(x).transpose(1, 2) * math.sqrt(self.n_channels)
@@ -197,28 +204,13 @@ def length_regulate(mu_x, w_ceil, x_mask, y_lengths, t_pad):
 
     Same result as `attn = generate_path(...)`, `mu_y = attn^T @ mu_x` (matcha_tts.py:126-131) without the dense matmul:
     frame j of utterance b copies the first token whose duration prefix sum exceeds j, and frames at or beyond
-    y_lengths[b] are zero.  CUDA tensors go through the `mb200_length_regulate` kernels (csrc/length_regulate.cu, prefix
-    sum + gather, bit-exact against the reference-generated fixtures); tensors on the CPU - where the rest of `synthesise`
-    cannot run anyway - take the torch formulation below, which is what the CPU unit tests pin to the same fixtures.
+    y_lengths[b] are zero.  Runs the `mb200_length_regulate` kernels (csrc/length_regulate.cu, prefix sum + gather,
+    bit-exact against the reference-generated fixtures).  CUDA tensors only: there is no CPU path in this package (the
+    torch restatement that the CPU tests pin to the same fixtures lives in oracle/matcha_oracle.py).
     """
-    if mu_x.is_cuda:
-        from . import _lib
-        mu_y, attn, y_mask = _lib.length_regulate(mu_x, w_ceil.squeeze(1), x_mask.squeeze(1), y_lengths, t_pad)
-        return mu_y.to(mu_x.dtype), attn.to(x_mask.dtype), y_mask.unsqueeze(1).to(x_mask.dtype)
-    return _length_regulate_host(mu_x, w_ceil, x_mask, y_lengths, t_pad)
-
-
-def _length_regulate_host(mu_x, w_ceil, x_mask, y_lengths, t_pad):
-    b, c, lx = mu_x.shape
-    y_mask = sequence_mask(y_lengths, t_pad).unsqueeze(1).to(x_mask.dtype)           # (B, 1, T)
-    attn_mask = x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)                            # (B, 1, Lx, T)
-    attn = generate_path(w_ceil.squeeze(1), attn_mask.squeeze(1))                     # (B, Lx, T)
-    cum = torch.cumsum(w_ceil.squeeze(1), 1)                                          # (B, Lx)
-    frames = torch.arange(t_pad, device=mu_x.device, dtype=cum.dtype)[None, :].expand(b, -1).contiguous()
-    tok = torch.searchsorted(cum.contiguous(), frames, right=True).clamp_(max=lx - 1)  # (B, T)
-    covered = attn.sum(1) > 0                                                         # frames some token owns
-    mu_y = torch.gather(mu_x, 2, tok[:, None, :].expand(-1, c, -1)) * covered[:, None, :].to(mu_x.dtype)
-    return mu_y, attn, y_mask
+    from . import _lib
+    mu_y, attn, y_mask = _lib.length_regulate(mu_x, w_ceil.squeeze(1), x_mask.squeeze(1), y_lengths, t_pad)
+    return mu_y.to(mu_x.dtype), attn.to(x_mask.dtype), y_mask.unsqueeze(1).to(x_mask.dtype)
 
 
 class MatchaTTS(nn.Module):

@@ -40,6 +40,16 @@ def _load(golden_dir, name):
     return torch.load(os.path.join(golden_dir, name + ".pt"), weights_only=False)
 
 
+def gate_or_known_miss(request, r, measured_bound, what):
+    """north_star's half-precision gate (rel-L2 <= 1e-2) with the cases that are KNOWN to miss it in bf16 recorded as
+    strict expected failures instead of a silently widened tolerance: r must stay under the measured bound, and when it
+    is over the gate the test is reported as xfailed with the value."""
+    assert r <= measured_bound, (what, r)
+    if r > HALF_REL_L2:
+        request.applymarker(pytest.mark.xfail(strict=True, reason=f"{what}: rel-L2 {r:.2e} misses the 1e-2 gate (bf16 operands)"))
+    assert r <= HALF_REL_L2, (what, r)
+
+
 def check(got, want, prec):
     got = got.cpu()
     assert torch.isfinite(got).all()
@@ -103,7 +113,7 @@ def test_attention_adds_the_float_mask(prec):
 # ------------------------------------------------------------------------------------------ golden vectors
 @pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
 @pytest.mark.parametrize("name", EST_CASES)
-def test_estimator_and_decode_match_reference_golden(golden_dir, name, prec):
+def test_estimator_and_decode_match_reference_golden(golden_dir, name, prec, request):
     fx = _load(golden_dir, name)
     plan = Plan(prec, fx["c_in"])
     plan.load_estimator(weights.estimator_state_dict(fx["c_in"], seed=fx["seed"]))
@@ -111,16 +121,20 @@ def test_estimator_and_decode_match_reference_golden(golden_dir, name, prec):
     vb = plan.estimator_forward(fx["z"], fx["mask"], fx["mu"], fx["t_batched"], fx["spks"])
     dec = plan.cfm_decode(fx["mu"], fx["mask"], fx["z"], fx["n_steps"], fx["spks"])
     replay = plan.cfm_decode(fx["mu"], fx["mask"], fx["z"], fx["n_steps"], fx["spks"])  # CUDA-graph replay
-    if prec == "bf16":  # a single velocity evaluation is the noisiest quantity in bf16 (precision)
-        assert rel_l2(v.cpu(), fx["v_scalar"]) < 2.5e-2 and rel_l2(vb.cpu(), fx["v_batched"]) < 2.5e-2
-    else:
-        check(v, fx["v_scalar"], prec)
-        check(vb, fx["v_batched"], prec)
     check(dec, fx["decoded"], prec)
     check(replay, fx["decoded"], prec)
+    assert torch.equal(dec, replay)                       # deterministic: eager pass == graph replay, bit for bit
     pad = fx["mask"].expand_as(fx["z"]) == 0
     assert (v.cpu()[pad] == 0).all()                      # velocity is masked (decoder.py:443)
     assert torch.equal(dec.cpu()[pad], fx["z"][pad])      # so padded frames keep their noise through the Euler loop
+    if prec == "bf16":  # a single velocity evaluation is the noisiest quantity in bf16 (precision):
+        # the gate is written for the decoded mel (checked above); the raw velocity is held to it as well, and recorded
+        # as a known miss where it is over (measured <= 2.5e-2)
+        gate_or_known_miss(request, max(rel_l2(v.cpu(), fx["v_scalar"]), rel_l2(vb.cpu(), fx["v_batched"])), 2.5e-2,
+                           "bf16 single velocity evaluation")
+    else:
+        check(v, fx["v_scalar"], prec)
+        check(vb, fx["v_batched"], prec)
 
 
 @pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
@@ -162,15 +176,14 @@ def test_fused_resblock_step_is_bit_identical_to_two_conv_launches(monkeypatch, 
 def test_fused_feed_forward_matches_two_conv_launches(monkeypatch, prec, b, t, lengths, var, mode, saved):
     """The transformer feed-forward (transformer.py:131-134, SnakeBeta :64-80) runs as one kernel that keeps the 1024-wide
     hidden activation in shared memory (ff_fused.cu): same MMA order, arithmetic and roundings as the ff1 / ff2 conv-GEMM
-    launches.  With one warp per GroupNorm group (T = 4) the estimator is deterministic and the outputs must be EQUAL.
-    At larger sizes the estimator's GroupNorm partial sums are accumulated with atomics, so two runs of the SAME path
-    already differ by half-precision ulps amplified through the network; there the fused path must be no further from the
-    two-launch path than that path is from itself, and as close to the fp32 path.  Sizes: a single partial tile, tiles
-    that straddle two utterances (the fused kernel tiles the flat B*L rows), several row tiles per CTA at cfg2's length.
-    mode 2 (the default) also runs the attention out-projection + residual + LayerNorm3 as the kernel's pre-stage: the
-    LayerNorm row sums are then added in another order, so that mode is held to the closeness bar at every size.
-    MB200_FUSE_RQ=1 (default) is the block's first half: res_conv + GroupNorm/Mish + LayerNorm1 + QKV projection as one
-    kernel (resqkv_fused.cu, both channel-concat sources, C_in padded to 192), same bar."""
+    launches.  GroupNorm statistics are summed in a fixed order (conv.cuh gn_stats_commit), so the estimator is
+    deterministic and the feed-forward-only fusion (mode 1) must be bit-EQUAL to the two-launch path at every size.
+    Sizes: a single partial tile, tiles that straddle two utterances (the fused kernel tiles the flat B*L rows), several
+    row tiles per CTA at cfg2's length.  mode 2 (the default) also runs the attention out-projection + residual +
+    LayerNorm3 as the kernel's pre-stage: the LayerNorm row sums are then added in another order, so that mode is held
+    to a closeness bar (no further from the fp32 path than the two-launch path is).  MB200_FUSE_RQ=1 (default) is the
+    block's first half: res_conv + GroupNorm/Mish + LayerNorm1 + QKV projection as one kernel (resqkv_fused.cu, both
+    channel-concat sources, C_in padded to 192), same bar."""
     sd = weights.estimator_state_dict(160, seed=5)
     g = torch.Generator().manual_seed(3)
     x, mu = torch.randn(b, 80, t, generator=g), torch.randn(b, 80, t, generator=g)
@@ -183,28 +196,23 @@ def test_fused_feed_forward_matches_two_conv_launches(monkeypatch, prec, b, t, l
         n0 = plan.launch_count()
         return plan.estimator_forward(x, mask, mu, torch.tensor(0.4)).cpu(), plan.launch_count() - n0
 
-    (fused, n_f), (plain, n_p), (plain2, _), (plain3, _) = run(prec, mode), run(prec, "0"), run(prec, "0"), run(prec, "0")
+    (fused, n_f), (plain, n_p), (plain2, _) = run(prec, mode), run(prec, "0"), run(prec, "0")
     assert n_p - n_f == saved      # six transformer blocks: two (three) launches became one
     assert torch.isfinite(fused).all()
-    if t == 4:
-        if (var, mode) == ("MB200_FUSE_FF", "1"):
-            assert torch.equal(fused, plain)
-        else:
-            assert rel_l2(fused, plain) <= (3e-3 if prec == "fp16" else 2e-2), rel_l2(fused, plain)
+    assert torch.equal(plain, plain2)          # run-to-run deterministic
+    if (var, mode) == ("MB200_FUSE_FF", "1"):
+        assert torch.equal(fused, plain)
         return
-    ref, _ = run("fp32", "0")
-    noise = max(rel_l2(plain2, plain), rel_l2(plain3, plain), rel_l2(plain3, plain2))
-    # the run-to-run noise is heavy-tailed in bf16 (1.5e-3 .. 1e-2 observed for the same binary): floor the bar at the
-    # half-precision gate's scale
-    assert rel_l2(fused, plain) <= max(3.0 * noise + 1e-3, 3e-3 if prec == "fp16" else 1.5e-2), (rel_l2(fused, plain), noise)
-    far = max(rel_l2(plain, ref), rel_l2(plain2, ref), rel_l2(plain3, ref))
-    assert rel_l2(fused, ref) <= 1.5 * far + 1e-4, (rel_l2(fused, ref), far)
+    assert rel_l2(fused, plain) <= (3e-3 if prec == "fp16" else 2e-2), rel_l2(fused, plain)
+    if t > 4:
+        ref, _ = run("fp32", "0")
+        assert rel_l2(fused, ref) <= 1.5 * rel_l2(plain, ref) + 1e-4, (rel_l2(fused, ref), rel_l2(plain, ref))
 
 
 # ------------------------------------------------------------------------------------------ oracle, seeded inputs
-@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
 @pytest.mark.parametrize("c_in", [160, 224])
-def test_hot_path_matches_oracle(prec, c_in):
+def test_hot_path_matches_oracle(prec, c_in, request):
     """decode (10 steps) -> crop -> denormalise -> vocoder against the CPU oracle, ragged batch, odd vocoder length."""
     g = torch.Generator().manual_seed(7)
     b, t_pad, lens, n_steps = 3, 60, [57, 60, 31], 10
@@ -226,14 +234,16 @@ def test_hot_path_matches_oracle(prec, c_in):
     check(dec, o_dec, prec)
     check(mel, o_mel, prec)
     assert wav.shape == o_wav.shape == (b, 1, 57 * 256)
-    if prec == "fp32":
-        check(wav, o_wav, prec)
-    else:
-        assert rel_l2(wav.cpu(), o_wav) <= HALF_REL_L2
     # host-buffer entry point gives the same answer
     mel_h, wav_h = plan.synthesise_host(mu, mask.contiguous(), z, n_steps, 57, mean, std, spks)
-    assert rel_l2(wav_h, o_wav) <= (1e-4 if prec == "fp32" else HALF_REL_L2)
+    assert torch.equal(wav_h.reshape(-1), wav.cpu().reshape(-1))
     assert length == 60
+    if prec == "fp32":
+        check(wav, o_wav, prec)
+    elif prec == "fp16":
+        assert rel_l2(wav.cpu(), o_wav) <= HALF_REL_L2
+    else:   # bf16 vocoder: operand rounding alone is ~1e-2 (tests/test_full_size_gpu.py docstring)
+        gate_or_known_miss(request, rel_l2(wav.cpu(), o_wav), 1.5e-2, "bf16 waveform")
 
 
 @pytest.mark.gpu
@@ -302,79 +312,3 @@ def test_module_api_is_drop_in(golden_dir):
     check(gen(gfx["mel"].cuda()), gfx["wav"], "fp32")
     gen.remove_weight_norm()   # cli.py:84-90 order: load with weight-norm keys, then remove
     check(gen(gfx["mel"].cuda()), gfx["wav"], "fp32")
-
-
-# ------------------------------------------------------------------------------------------ full size (BASELINE cfg2)
-def test_full_size_properties_cfg2():
-    """B=64, T=452, 10 Euler steps + vocoder: too large for the CPU oracle, so check size-independent properties:
-    the tensor-core path agrees with the independent FFMA fp32 path, padded frames keep their noise, masked velocity,
-    waveform bounded, batch-order equivariance."""
-    g = torch.Generator().manual_seed(1234)
-    b, t_pad, n_steps = 64, 452, 10
-    lens = [451] * 48 + [int(v) for v in torch.randint(60, 451, (16,), generator=g)]
-    est_sd, gen_sd = weights.estimator_state_dict(160, seed=1234), weights.generator_state_dict(1234)
-    mu = torch.randn(b, 80, t_pad, generator=g).cuda()
-    z = (torch.randn(b, 80, t_pad, generator=g) * 0.667).cuda()
-    mask = weights.prefix_mask(lens, t_pad).cuda()
-    mean, std = -5.536622, 2.116101
-    out = {}
-    for prec in ("fp16", "fp32"):
-        plan = Plan(prec, 160)
-        plan.load_estimator(est_sd)
-        plan.load_generator(gen_sd)
-        out[prec] = plan.synthesise(mu, mask, z, n_steps, 451, mean, std)
-        if prec == "fp16":
-            perm = torch.randperm(b, generator=g).cuda()
-            dec_p, _, wav_p = plan.synthesise(mu[perm], mask[perm], z[perm], n_steps, 451, mean, std)
-            assert rel_l2(dec_p.cpu(), out[prec][0][perm].cpu()) < 5e-3   # utterances are independent (atomics order only)
-            assert rel_l2(wav_p.cpu(), out[prec][2][perm].cpu()) < 5e-3
-        del plan
-        torch.cuda.empty_cache()
-    dec16, mel16, wav16 = out["fp16"]
-    dec32, mel32, wav32 = out["fp32"]
-    assert rel_l2(dec16.cpu(), dec32.cpu()) <= HALF_REL_L2
-    assert rel_l2(wav16.cpu(), wav32.cpu()) <= HALF_REL_L2
-    pad = (mask.expand_as(z) == 0)
-    assert torch.equal(dec16[pad], z[pad]) and torch.equal(dec32[pad], z[pad])
-    assert float(wav16.abs().max()) <= 1.0 and torch.isfinite(wav16).all()
-    assert wav16.shape == (b, 1, 451 * 256)
-
-
-@pytest.mark.parametrize("cfg", ["cfg3", "cfg4"])
-def test_full_size_properties_other_configs(cfg):
-    """BASELINE.json's other configurations as parity cases: cfg3 = VCTK (C_in 224, speaker vectors),
-    4 Euler steps, one GPU's share of the batch; cfg4 = long form, B=16, 3001 valid frames (T_pad 3004, vocoder length
-    not a multiple of 4), 10 steps.  Same size-independent properties as cfg2."""
-    g = torch.Generator().manual_seed(1234)
-    if cfg == "cfg3":
-        b, t_valid, n_steps, c_in = 64, 451, 4, 224
-        mean, std = -6.630575, 2.482914
-    else:
-        b, t_valid, n_steps, c_in = 16, 3001, 10, 160
-        mean, std = -5.536622, 2.116101
-    t_pad = (t_valid + 3) // 4 * 4
-    lens = [t_valid] * (b - 4) + [int(v) for v in torch.randint(t_valid // 8, t_valid, (4,), generator=g)]
-    est_sd, gen_sd = weights.estimator_state_dict(c_in, seed=1234), weights.generator_state_dict(1234)
-    mu = torch.randn(b, 80, t_pad, generator=g).cuda()
-    z = (torch.randn(b, 80, t_pad, generator=g) * 0.667).cuda()
-    spks = torch.randn(b, 64, generator=g).cuda() if c_in == 224 else None
-    mask = weights.prefix_mask(lens, t_pad).cuda()
-    out = {}
-    for prec in ("fp16", "fp32"):
-        plan = Plan(prec, c_in)
-        plan.load_estimator(est_sd)
-        plan.load_generator(gen_sd)
-        out[prec] = tuple(t.cpu() for t in plan.synthesise(mu, mask, z, n_steps, t_valid, mean, std, spks=spks))
-        if prec == "fp16":   # CUDA-graph replay gives the same result (atomics order only)
-            again = plan.synthesise(mu, mask, z, n_steps, t_valid, mean, std, spks=spks)
-            assert rel_l2(again[2].cpu(), out[prec][2]) < 5e-3
-        del plan
-        torch.cuda.empty_cache()
-    dec16, mel16, wav16 = out["fp16"]
-    dec32, mel32, wav32 = out["fp32"]
-    assert rel_l2(dec16, dec32) <= HALF_REL_L2
-    assert rel_l2(wav16, wav32) <= 2 * HALF_REL_L2   # long vocoder chains on random weights: still within 2 %
-    pad = (mask.expand_as(z) == 0).cpu()
-    assert torch.equal(dec16[pad], z.cpu()[pad]) and torch.equal(dec32[pad], z.cpu()[pad])
-    assert float(wav16.abs().max()) <= 1.0 and torch.isfinite(wav16).all()
-    assert wav16.shape == (b, 1, t_valid * 256)
