@@ -102,14 +102,7 @@ void Plan::test_attention(const float* qkv, const float* mask, int B, int T, flo
   MB_CUDA(cudaMemcpy(h.data(), qkv, n_in * 4, cudaMemcpyDeviceToHost));
   void* q = upload_operand(h);
   void* o = dalloc(n_out * esize(dtype));
-  if (dtype == MB200_F32) MB_CUDA(launch_attention_simt<float>((const float*)q, mask, (float*)o, B, T, st));
-  else if (dtype == MB200_BF16) {
-    if (tensor_core()) MB_CUDA(launch_attention_mma<__nv_bfloat16>((const __nv_bfloat16*)q, mask, (__nv_bfloat16*)o, B, T, st));
-    else MB_CUDA(launch_attention_simt<__nv_bfloat16>((const __nv_bfloat16*)q, mask, (__nv_bfloat16*)o, B, T, st));
-  } else {
-    if (tensor_core()) MB_CUDA(launch_attention_mma<__half>((const __half*)q, mask, (__half*)o, B, T, st));
-    else MB_CUDA(launch_attention_simt<__half>((const __half*)q, mask, (__half*)o, B, T, st));
-  }
+  MB_CUDA(attention_op(q, mask, o, B, T)(st));
   MB_CUDA(cudaStreamSynchronize(st));
   if (dtype == MB200_F32) {
     MB_CUDA(cudaMemcpy(out, o, n_out * 4, cudaMemcpyDeviceToDevice));

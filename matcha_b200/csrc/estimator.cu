@@ -162,18 +162,7 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
       return launch_layernorm<__half>((const __half*)in, g, bta, (__half*)out, rows, s);
     });
   };
-  auto attention = [&](const void* qkv, const float* mask, void* out, int L) {
-    Launch at([=](cudaStream_t s) -> cudaError_t {
-      if (dtype == MB200_F32) return launch_attention_simt<float>((const float*)qkv, mask, (float*)out, B, L, s);
-      if (dtype == MB200_BF16) return tc ? launch_attention_mma<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s)
-                                         : launch_attention_simt<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s);
-      return tc ? launch_attention_mma<__half>((const __half*)qkv, mask, (__half*)out, B, L, s)
-                : launch_attention_simt<__half>((const __half*)qkv, mask, (__half*)out, B, L, s);
-    });
-    at.kind = 1;
-    at.flops = 4.0 * B * 2 * static_cast<double>(L) * L * 64;   // QK^T + PV, dense over all L keys as the reference computes it
-    add(std::move(at));
-  };
+  auto attention = [&](const void* qkv, const float* mask, void* out, int L) { add(attention_op(qkv, mask, out, B, L)); };
 
   // ResnetBlock1D (decoder.py:46-61): in (1 or 2 sources, already masked) -> RES (unmasked), LN1(RES) -> LN
   auto resnet = [&](int r, Src s0, const Src* s1, int Tn, const float* mask, const TransformerW& X) {

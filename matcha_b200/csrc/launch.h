@@ -78,7 +78,16 @@ cudaError_t launch_conv_post(const T* in, const float* w /*[7][32]*/, float bias
 // ---- attention (attention.cu): qkv [B][L][384] (q | k | v, 2 heads x 64), additive key mask, out [B][L][128]
 template <typename T>
 cudaError_t launch_attention_simt(const T* qkv, const float* mask, T* out, int B, int L, cudaStream_t st);
-template <typename T>   // mma.sync tensor-core version (attention_mma.cu), half types only
+template <typename T>   // mma.sync tensor-core version (attention_mma.cu), half types only; kept as the A/B cross-check (MB200_ATTN=mma)
 cudaError_t launch_attention_mma(const T* qkv, const float* mask, T* out, int B, int L, cudaStream_t st);
+// tcgen05 / TMEM / TMA version (attention_umma.cu), half types only: the production kernel
+struct AttnLaunch {
+  CUtensorMap tmQKV;    // 3-D view (384 channels, L rows, B) of the qkv buffer, box 64 x 128 x 1, 128B swizzle
+  const float* mask;    // [B][L] float 0/1, added to the logits
+  void* out;            // [B][L][128] operand dtype
+  int B, L, grid;
+  long long* dbg;       // developer probe (MB200_ATTN_DBG): per-phase cycle counters of CTA 0, else null
+};
+template <typename T> cudaError_t launch_attention_umma(const AttnLaunch& A, cudaStream_t st);
 
 }  // namespace mb

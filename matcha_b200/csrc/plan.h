@@ -149,6 +149,7 @@ class Plan {
   int fuse_ff = 2;          // transformer feed-forward as one kernel, hidden activation kept on chip; 2 = also the attention
                             // out-projection + residual + LayerNorm as its pre-stage (MB200_FUSE_FF=1: FF only, 0: conv launches)
   int fuse_rq = 1;          // res_conv + GroupNorm/Mish + LayerNorm1 + QKV as one kernel (MB200_FUSE_RQ=0: two conv launches)
+  int attn_umma = 1;        // tcgen05 attention (attention_umma.cu); MB200_ATTN=mma selects the mma.sync kernel for A/B runs
   int fuse_pairs = 1;       // HiFi-GAN stages 3-4: one kernel per ResBlock step (MB200_FUSE_PAIRS=0: two conv launches)
   bool profiling = false;
   double prof[kProfRegions][kProfKinds][3] = {};   // [region][kind] = {launches, milliseconds, flops}
@@ -184,6 +185,8 @@ class Plan {
   Launch resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const Src* s1, const void* gn_raw, const float* gn_stats,
                    const float* gn_gamma, const float* gn_beta, const float* mask, void* res_out, const float* ln_g,
                    const float* ln_b, void* qkv_out, int B, int L);
+  // softmax(q k^T + mask) v on [B][L][384] qkv -> [B][L][128] (operand dtype; fp32 mode: SIMT kernel)
+  Launch attention_op(const void* qkv, const float* mask, void* out, int B, int L);
   bool rq_supported() const { return fuse_rq && tensor_core() && kernel_version >= 2; }
   bool ff_supported() const { return fuse_ff && tensor_core() && kernel_version >= 2; }
   bool pair_supported(int C) const { return fuse_pairs && tensor_core() && kernel_version >= 2 && (C == 64 || C == 32); }

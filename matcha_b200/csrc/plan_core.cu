@@ -43,6 +43,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_FUSE_PAIRS")) fuse_pairs = std::atoi(v);
   if (const char* v = std::getenv("MB200_FUSE_FF")) fuse_ff = std::atoi(v);
   if (const char* v = std::getenv("MB200_FUSE_RQ")) fuse_rq = std::atoi(v);
+  if (const char* v = std::getenv("MB200_ATTN")) attn_umma = std::strcmp(v, "mma") != 0;
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -547,6 +548,37 @@ Launch Plan::resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const S
   op.kind = 0;
   op.flops = 2.0 * static_cast<double>(g.rows) * (256.0 * Wres.k_real + 384.0 * 256.0);
   return op;
+}
+
+Launch Plan::attention_op(const void* qkv, const float* mask, void* out, int B, int L) {
+  const int dtype = cfg.dtype;
+  const bool tc = tensor_core();
+  Launch at;
+  if (tc && attn_umma) {
+    AttnLaunch A{};
+    A.tmQKV = tmap_act(qkv, 384, L, B, 64);
+    A.mask = mask; A.out = out; A.B = B; A.L = L;
+    A.grid = std::min(B * 2 * ((L + 255) / 256), num_sms);
+    A.dbg = nullptr;
+    if (std::getenv("MB200_ATTN_DBG")) {
+      A.dbg = static_cast<long long*>(dalloc(148 * 16 * sizeof(long long)));
+      probe_out = A.dbg;
+    }
+    at = Launch([A, dtype](cudaStream_t s) -> cudaError_t {
+      return dtype == MB200_BF16 ? launch_attention_umma<__nv_bfloat16>(A, s) : launch_attention_umma<__half>(A, s);
+    });
+  } else {
+    at = Launch([=](cudaStream_t s) -> cudaError_t {
+      if (dtype == MB200_F32) return launch_attention_simt<float>((const float*)qkv, mask, (float*)out, B, L, s);
+      if (dtype == MB200_BF16) return tc ? launch_attention_mma<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s)
+                                         : launch_attention_simt<__nv_bfloat16>((const __nv_bfloat16*)qkv, mask, (__nv_bfloat16*)out, B, L, s);
+      return tc ? launch_attention_mma<__half>((const __half*)qkv, mask, (__half*)out, B, L, s)
+                : launch_attention_simt<__half>((const __half*)qkv, mask, (__half*)out, B, L, s);
+    });
+  }
+  at.kind = 1;
+  at.flops = 4.0 * B * 2 * static_cast<double>(L) * L * 64;   // QK^T + PV, dense over all L keys as the reference computes it
+  return at;
 }
 
 void Plan::run(Program& prog, cudaStream_t st) {

@@ -97,9 +97,12 @@ def test_attention_adds_the_float_mask(prec):
     """softmax(q k^T + mask[key]) v over ALL padded keys, incl. L = 1 and ragged L."""
     plan = Plan(prec, 160, use_graph=False)
     g = torch.Generator().manual_seed(1)
-    for (b, t, lens) in [(2, 24, [24, 9]), (2, 140, [140, 77]), (1, 452, [400]), (1, 1, [1]), (2, 33, [33, 1])]:
+    for (b, t, lens) in [(2, 24, [24, 9]), (2, 140, [140, 77]), (1, 452, [400]), (1, 1, [1]), (2, 33, [33, 1]),
+                         (3, 256, [256, 129, 1]), (2, 700, [700, 300]), (1, 1502, [1400]), (75, 130, [130] * 75)]:
         qkv = torch.randn(b, t, 384, generator=g)
         qkv[:, :, :128] *= 0.3
+        if t == 700:   # logits that keep growing along the key axis: the running maximum of the online softmax must be
+            qkv[:, :, 128:256] *= torch.linspace(0.2, 4.0, t)[None, :, None]   # raised (and O rescaled) tile after tile
         mask = (torch.arange(t)[None] < torch.tensor(lens)[:, None]).float()
         x = _quant(qkv, prec).double()
         q, k, v = (x[:, :, i * 128:(i + 1) * 128].reshape(b, t, 2, 64).transpose(1, 2) for i in range(3))
@@ -107,7 +110,9 @@ def test_attention_adds_the_float_mask(prec):
         ref = ref.transpose(1, 2).reshape(b, t, 128)
         y = plan.test_attention(qkv, mask).cpu().double()
         tol = 2e-5 if prec == "fp32" else (2e-3 if prec == "fp16" else 1.6e-2)  # output rounding of the half types
-        assert float((y - ref).abs().max()) < tol, (prec, b, t)
+        # the bound is for outputs of unit scale; the peaky-softmax case (t == 700) produces outputs up to |4|, where one
+        # ulp of the half types is that much larger
+        assert float((y - ref).abs().max()) < tol * max(1.0, float(ref.abs().max()) / 2), (prec, b, t)
 
 
 # ------------------------------------------------------------------------------------------ golden vectors
