@@ -101,6 +101,18 @@ long long mb200_maximum_path_workspace_bytes(int B, int Tx, int Ty);
 int mb200_maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* workspace,
                        void* stream);
 
+/* Allocation-free variant of mb200_maximum_path.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernel, inputs, outputs and results; the scratch (B * Ty * ceil(Tx / 32) * 4 bytes of decision bits)
+ * lives in a file-scope __device__ array of MB200_MAS_STATIC_SCRATCH_BYTES inside the library, which every GPU that loads
+ * the library holds until the process exits.  Shapes that need more are rejected with an error (use mb200_maximum_path).
+ * The call performs no cudaMalloc / cudaFree and calls no allocating library routine.  The array is shared by all calls
+ * on a device and keeps the last call's contents (nothing needs clearing: every word read is written earlier in the same
+ * launch); calls that overlap on one GPU race on it - serialise them on one stream.  The first call on a device resolves
+ * the array's device address (cudaGetSymbolAddress) and configures the kernel: make it outside stream capture. */
+#define MB200_MAS_STATIC_SCRATCH_BYTES (4u * 1024u * 1024u)
+int mb200_maximum_path_static(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* stream);
+
 /* One estimator parameter for the training entry point: DEVICE fp32 tensors in the reference layout (SURVEY.md
  * Appendix A), `grad` may be NULL (that gradient is then not computed). */
 typedef struct {

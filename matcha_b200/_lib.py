@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_maximum_path", "mb200_maximum_path_workspace_bytes", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
+    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_maximum_path", "mb200_maximum_path_workspace_bytes", "mb200_maximum_path_static", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
 
 
@@ -71,6 +71,7 @@ def load():
         lib.mb200_denoise.argtypes = [vp, vp, i, i, vp, f, vp, vp]
         lib.mb200_length_regulate.argtypes = [vp, vp, vp, vp, i, i, i, i, vp, vp, vp, vp, vp]
         lib.mb200_maximum_path.argtypes = [vp, vp, i, i, i, vp, vp, vp]
+        lib.mb200_maximum_path_static.argtypes = [vp, vp, i, i, i, vp, vp]
         lib.mb200_maximum_path_workspace_bytes.argtypes = [i, i, i]
         lib.mb200_maximum_path_workspace_bytes.restype = ctypes.c_longlong
         lib.mb200_launch_count.argtypes = [vp]
@@ -155,6 +156,26 @@ def maximum_path(value, mask):
     with torch.cuda.device(dev):
         check(lib.mb200_maximum_path(_ptr(v), _ptr(m), b, tx, ty, _ptr(path), _ptr(ws), _stream()))
     return path.to(value.dtype)
+
+
+MAS_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024   # MB200_MAS_STATIC_SCRATCH_BYTES (include/matcha_b200.h)
+
+
+def maximum_path_static(value, mask, path):
+    """`mb200_maximum_path_static`: the same search with the kernel's scratch in a static device array inside the library.
+    Nothing is allocated here or below: value, mask (B, Tx, Ty) and the output `path` are the caller's contiguous fp32
+    CUDA tensors.  Raises when the shape needs more than MAS_STATIC_SCRATCH_BYTES of scratch.  Calls that overlap on one
+    GPU race on the shared array (no counterpart in the reference)."""
+    lib = load()
+    for t in (value, mask, path):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise ValueError("maximum_path_static takes contiguous fp32 CUDA tensors (it converts and allocates nothing)")
+    if value.dim() != 3 or tuple(mask.shape) != tuple(value.shape) or tuple(path.shape) != tuple(value.shape):
+        raise ValueError("value, mask and path must all be (B, Tx, Ty)")
+    b, tx, ty = value.shape
+    with torch.cuda.device(value.device):
+        check(lib.mb200_maximum_path_static(_ptr(value), _ptr(mask), b, tx, ty, _ptr(path), _stream()))
+    return path
 
 
 class Plan:

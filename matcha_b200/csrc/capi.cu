@@ -235,6 +235,12 @@ int mb200_maximum_path(const float* value, const float* mask, int B, int Tx, int
     mb::maximum_path(value, mask, B, Tx, Ty, path, workspace, static_cast<cudaStream_t>(stream));
   });
 }
+int mb200_maximum_path_static(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* stream) {
+  return guarded([&] {
+    if (!value || !mask || !path) throw mb::Error("null argument");
+    mb::maximum_path_static(value, mask, B, Tx, Ty, path, static_cast<cudaStream_t>(stream));
+  });
+}
 int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
                        const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
                        float sigma_min, int backward, float* loss, float* y, float* v, float* dmu, float* dspks,

@@ -127,4 +127,44 @@ void maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, 
   MB_CUDA(cudaGetLastError());
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (mb200_maximum_path_static).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it).  The kernel's decision-bit scratch lives in a file-scope __device__ array instead of a caller
+// allocation; every GPU that loads the library holds these bytes until the process exits.
+//
+// In host code the array's NAME is a host-side stand-in, not a device address: its device address is taken once per
+// device, with that device current, by cudaGetSymbolAddress below, and that pointer is what the kernel receives.
+// The array is shared by every call on a device and keeps the last call's contents.  Nothing has to be cleared: each
+// decision word the back-tracking walk reads (frame y, token word index >> 5, index < t_x) is written earlier in the
+// same launch by the forward pass.  Calls that overlap on one GPU (different streams, or threads) race on it.
+constexpr size_t kMasStaticBytes = MB200_MAS_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_mas_scratch[kMasStaticBytes];
+
+void maximum_path_static(const float* value, const float* mask, int B, int Tx, int Ty, float* path, cudaStream_t st) {
+  if (B <= 0 || Tx <= 0 || Ty <= 0) throw Error("maximum_path_static: empty shape");
+  const size_t need = maximum_path_workspace_bytes(B, Tx, Ty);
+  if (need > kMasStaticBytes)
+    throw Error("maximum_path_static: B * Ty * ceil(Tx / 32) * 4 = " + std::to_string(need) + " bytes of scratch exceed the static limit of " +
+                std::to_string(kMasStaticBytes) + " bytes (MB200_MAS_STATIC_SCRATCH_BYTES); use mb200_maximum_path with a caller workspace");
+  constexpr int kMaxDev = 64;
+  static void* scratch_addr[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = 0;
+  MB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) throw Error("maximum_path_static: device ordinal out of range");
+  void* ptr = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!scratch_addr[dev]) {   // set-up, once per device, with that device current
+      void* p = nullptr;
+      MB_CUDA(cudaGetSymbolAddress(&p, g_mas_scratch));
+      if (!p) throw Error("maximum_path_static: cudaGetSymbolAddress returned a null address");
+      scratch_addr[dev] = p;
+    }
+    ptr = scratch_addr[dev];
+  }
+  maximum_path(value, mask, B, Tx, Ty, path, ptr, st);   // same kernel, same launch; no cudaMalloc / cudaFree anywhere
+}
+
 }  // namespace mb

@@ -226,5 +226,7 @@ void length_regulate(const float* mu_x, const float* w, const float* x_mask, con
 // Monotonic alignment search (monotonic_align/core.pyx:11-47), mas.cu.  Plan-independent.
 size_t maximum_path_workspace_bytes(int B, int Tx, int Ty);
 void maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* workspace, cudaStream_t st);
+// Same, scratch in a file-scope __device__ array of MB200_MAS_STATIC_SCRATCH_BYTES (mas.cu): allocates nothing.
+void maximum_path_static(const float* value, const float* mask, int B, int Tx, int Ty, float* path, cudaStream_t st);
 
 }  // namespace mb
