@@ -164,7 +164,10 @@ def workload(cfg_name, rank, world):
         # so which GPU runs a batch does not change its result
         mine = mdist.partition([int(x / 1e9) for x in cost], world)[rank]
         batches = [make_batch(c["c_in"], groups[i], t_pads[i], 1234 + i) for i in sorted(mine)]
-        return batches, sum(lens), dict(n_batches=len(groups), t_pads=sorted(set(t_pads)), pad_waste=1.0 - sum(lens) / sum(len(g) * tp for g, tp in zip(groups, t_pads)))
+        # the final gather's buffer shape is the same on every rank and known from the global partition: no size exchange
+        b_max = max(sum(len(groups[i]) for i in part) for part in mdist.partition([int(x / 1e9) for x in cost], world))
+        return batches, sum(lens), dict(n_batches=len(groups), t_pads=sorted(set(t_pads)), gather_rows=b_max, gather_len=lens[0],
+                                        pad_waste=1.0 - sum(lens) / sum(len(g) * tp for g, tp in zip(groups, t_pads)))
     t_valid = c["t_valid"]
     t_pad = ceil_to(t_valid, 4)
     if c["scaling"] == "strong":      # cfg3: the 256 utterances are dealt to the ranks
@@ -252,7 +255,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL logs to stdout by default; stdout carries the JSON line
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120))
     dev = torch.device("cuda", local)
     c = CONFIGS[args.config]
     mean, std = c["stats"]
@@ -275,21 +279,17 @@ def run_ours(args):
     # The path's only exchange: the final gather of mels / waveforms to rank 0 over NVLink.  It is issued asynchronously
     # (NCCL's own stream) and overlaps the NEXT step's decode; every rank's contribution has the same shape per batch
     # slot in cfg2 / cfg3 / cfg4, and cfg2b gathers its (ragged) batches one gather_padded per step.
-    l_max = max((bt["length"] for bt in batches), default=1)
-    b_loc = sum(len(bt["lens"]) for bt in batches)
     pending = []
 
     def gather_async(mels, wavs):
         if world == 1:
             return
-        if args.config == "cfg2b":   # ragged shards: padded gather (host-side sizes exchange), on the compute stream
-            wav = torch.cat([torch.nn.functional.pad(w, (0, 256 * l_max - w.shape[-1])) for w in wavs]) if wavs else torch.zeros(0, 1, 256 * l_max, device=dev)
-            sizes = torch.tensor([wav.shape[0]], device=dev)
-            all_sizes = [torch.empty_like(sizes) for _ in range(world)]
-            dist.all_gather(all_sizes, sizes)
-            b_max = max(int(s) for s in all_sizes)
-            buf = wav.new_zeros(b_max, 1, wav.shape[-1])
-            buf[:wav.shape[0]] = wav
+        if args.config == "cfg2b":   # ragged shards: one padded buffer per rank, (rows, length) fixed by the global partition
+            buf = torch.zeros(shape_info["gather_rows"], 1, 256 * shape_info["gather_len"], device=dev)
+            row = 0
+            for w in wavs:
+                buf[row:row + w.shape[0], :, :w.shape[-1]] = w
+                row += w.shape[0]
             out = [torch.empty_like(buf) for _ in range(world)] if rank == 0 else None
             pending.append(dist.gather(buf, out, dst=0, async_op=True))
             return
@@ -494,7 +494,8 @@ def run_train(args):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120))
     dev = torch.device("cuda", local)
     c = CONFIGS["cfg5"]
     b, t_pad = c["batch"], c["t_pad"]

@@ -146,11 +146,11 @@ def allreduce_gradients(params, bucket_bytes: int = 32 << 20, group: Optional[di
         return
     world = dist.get_world_size(group)
     weight = None
-    if valid_frames is not None:
+    if valid_frames is not None:   # stays on the device: no host synchronisation between the backward and the exchange
         total = valid_frames.detach().clone().to(params[0].grad.device, torch.float32).reshape(1)
         mine = total.clone()
         dist.all_reduce(total, group=group)
-        weight = (mine / total).item()
+        weight = mine / total
     buckets, cur, size = [], [], 0
     for p in params:
         n = p.grad.numel() * p.grad.element_size()
@@ -171,8 +171,6 @@ def allreduce_gradients(params, bucket_bytes: int = 32 << 20, group: Optional[di
         work.wait()
         if weight is None:
             flat.div_(world)
-        off = 0
-        for p in bucket:
-            n = p.grad.numel()
-            p.grad.copy_(flat[off:off + n].view_as(p.grad))
-            off += n
+        # one batched copy back into the 180 gradient tensors instead of one small kernel each
+        views = [v.view_as(p.grad) for v, p in zip(flat.split([p.grad.numel() for p in bucket]), bucket)]
+        torch._foreach_copy_([p.grad for p in bucket], views)
