@@ -127,7 +127,7 @@ typedef struct {
  * loss = sum((v-u)^2) / (sum(mask) * 80).  With backward != 0 the whole estimator backward pass runs as well:
  * d loss / d parameter is ACCUMULATED (+=) into every non-NULL `grad` (zero-fill them for plain gradients),
  * d loss / d mu -> dmu (B,80,T) and d loss / d spks -> dspks (B, c_in-160), both optional (NULL = skip).
- * Parameters are read in place (no repacking between optimiser steps).  fp32 FFMA kernels in every plan dtype.
+ * Parameters are read in place (no repacking between optimiser steps).  fp32 data in every plan dtype; the GEMMs are error-compensated 3xTF32 tensor-core kernels (mma.sync, fp32-level accuracy; csrc/train_kernels.cuh), the element-wise kernels fp32.
  * loss: device scalar; y, v: optional (B,80,T) outputs.  `prefix` is stripped from parameter names. */
 int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
                        const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,

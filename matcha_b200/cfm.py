@@ -190,15 +190,25 @@ class BASECFM(nn.Module):
     @torch.inference_mode()
     def forward(self, mu, mask, n_timesteps, temperature=1.0, spks=None, cond=None):
         z = torch.randn_like(mu) * temperature
-        t_span = torch.linspace(0, 1, n_timesteps + 1, device=mu.device)
-        return self.solve_euler(z, t_span=t_span, mu=mu, mask=mask, spks=spks, cond=cond)
+        # the reference builds t_span = linspace(0, 1, n + 1) here (flow_matching.py:52); the CUDA path evaluates exactly
+        # that grid inside its graph, so no tensor is built, moved or compared (no device -> host sync on this call)
+        return self.estimator.plan().cfm_decode(mu, mask, z, int(n_timesteps), spks)
 
     def solve_euler(self, x, t_span, mu, mask, spks, cond):
         n = len(t_span) - 1
-        uniform = torch.equal(t_span.detach().float().cpu(), torch.linspace(0, 1, n + 1))
-        if uniform:  # the grid every caller uses (flow_matching.py:52): whole loop in one CUDA graph
+        # Is this the uniform grid every caller of the reference uses?  Decided on the host, with a tolerance (CUDA and
+        # CPU linspace may differ by an ulp), against the schedule the kernels use.  A t_span that lives on the device costs
+        # one small read-back here; BASECFM.forward never comes this way.
+        span = t_span.detach().to("cpu", torch.float32)
+        uniform = n >= 1 and bool(torch.allclose(span, torch.linspace(0, 1, n + 1), rtol=0.0, atol=2e-7))
+        if uniform:  # whole loop in one CUDA graph
             return self.estimator.plan().cfm_decode(mu, mask, x, n, spks)
-        # arbitrary grid: same recurrence, one estimator launch program per step
+        # arbitrary grid: same recurrence, one estimator launch program per step (slow path, said once)
+        if not getattr(self, "_warned_slow_grid", False):
+            import warnings
+            warnings.warn("matcha_b200: solve_euler got a non-uniform t_span; running one estimator call per step instead of "
+                          "the captured Euler graph", stacklevel=2)
+            self._warned_slow_grid = True
         t, dt = t_span[0], t_span[1] - t_span[0]
         for step in range(1, len(t_span)):
             x = x + dt * self.estimator(x, mask, mu, t, spks, cond)

@@ -424,11 +424,11 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
 template <typename T>
 cudaError_t launch_attention_umma(const AttnLaunch& A, cudaStream_t st) {
   auto kern = attention_umma_kernel<T>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem);
     if (err != cudaSuccess) return err;
-    configured = true;
+    configured.mark();
   }
   kern<<<A.grid, kAttnThreads, kAttnSmem, st>>>(A.tmQKV, A.mask, static_cast<T*>(A.out), A.B, A.L, A.dbg);
   return cudaGetLastError();

@@ -149,11 +149,11 @@ template <int NTILE, int KC, int STAGES, typename T>
 static cudaError_t launch_umma_inst(const ConvLaunch& L, cudaStream_t st) {
   using S = UmmaSmem<NTILE, KC, STAGES>;
   auto kern = conv_gemm_umma_kernel<NTILE, KC, STAGES, T>;
-  static bool configured = false;  // per instantiation; one device per process
-  if (!configured) {
+  static PerDeviceOnce configured;
+  if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
     if (err != cudaSuccess) return err;
-    configured = true;
+    configured.mark();
   }
   dim3 grid((L.g.T_out + 127) / 128, (L.g.N / NTILE) * L.g.n_phases, L.g.B);
   kern<<<grid, 192, S::TOTAL, st>>>(L.tmA[0], L.tmA[L.g.n_src > 1 ? 1 : 0], L.tmW, L.g, L.e);

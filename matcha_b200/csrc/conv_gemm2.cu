@@ -279,11 +279,11 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
 template <int NTILE, int KC, int MB, int EG, typename T, uint32_t F>
 static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
   auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, EG, T, F>;
-  static int configured = 0;
-  if (configured < L.smem_bytes) {
+  static PerDeviceOnce configured;
+  if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (err != cudaSuccess) return err;
-    configured = 227 * 1024;
+    configured.mark();
   }
   const bool two = L.g.n_src > 1;
   cudaLaunchConfig_t cfg{};

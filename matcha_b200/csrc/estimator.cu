@@ -357,6 +357,7 @@ void Plan::estimator_forward(const float* x, const float* mask, const float* mu,
   add([=](cudaStream_t s) { return launch_btc_to_bct(v, out, B, 80, T, s); });
   for (auto& op : prog.ops) MB_CUDA(op(st));
   launches += prog.kernels;
+  mark_busy(st);
 }
 
 void Plan::cfm_decode(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
@@ -406,12 +407,14 @@ void Plan::cfm_decode(const float* mu, const float* mask, const float* z, const 
     build_time_embed(*prog, tv, n_steps);
     const float* tproj = static_cast<const float*>(ws_est_[TPROJ].p);
     for (int s = 0; s < n_steps; ++s) build_estimator_step(*prog, B, T, tproj + static_cast<size_t>(s) * 6 * 256, 0, true, dts[s], nullptr);
+    make_room(decode_cache_);
     it = decode_cache_.emplace(key, std::move(prog)).first;
   }
   // the schedule buffer is shared with other shapes / estimator_forward: refresh it (n_steps floats) every call
   MB_CUDA(cudaMemcpyAsync(tv, it->second->host_f32.data(), n_steps * 4, cudaMemcpyHostToDevice, st));
   run(*it->second, st);
   if (out) { MB_CUDA(launch_btc_to_bct(xs, out, B, 80, T, st)); launches += 1; }
+  mark_busy(st);
 }
 
 }  // namespace mb

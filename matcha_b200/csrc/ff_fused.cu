@@ -473,11 +473,11 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 template <typename T>
 cudaError_t launch_ff_fused(const FFLaunch& L, cudaStream_t st) {
   auto kern = ff_fused_kernel<T>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (err != cudaSuccess) return err;
-    configured = true;
+    configured.mark();
   }
   kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmX, L.tmW1, L.tmW2, L.tmWo, L.g);
   return cudaGetLastError();

@@ -3,9 +3,24 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 #include "conv.cuh"
 
 namespace mb {
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-DEVICE setting: every kernel instantiation remembers the
+// devices it has been configured on (a plan may live on any GPU of the process).  Setting it twice is harmless, so two
+// threads racing through the first launch on a device need no lock.
+struct PerDeviceOnce {
+  std::atomic<unsigned long long> done{0};
+  int dev = 0;
+  bool needed() {
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+    return !((done.load(std::memory_order_acquire) >> (dev & 63)) & 1ull);
+  }
+  void mark() { done.fetch_or(1ull << (dev & 63), std::memory_order_release); }
+};
 
 struct ConvLaunch {
   ConvGeom g;

@@ -113,10 +113,10 @@ void maximum_path(const float* value, const float* mask, int B, int Tx, int Ty, 
   auto bytes = [&](int tc) { return (2 * static_cast<size_t>(Tx) + static_cast<size_t>(Tx) * (tc + 1)) * sizeof(float); };
   while (TC > 1 && bytes(TC) > 200 * 1024) TC >>= 1;
   if (bytes(TC) > 200 * 1024) throw Error("maximum_path: too many tokens for one CTA's shared memory");
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  if (configured.needed()) {
     MB_CUDA(cudaFuncSetAttribute(mas_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    configured = true;
+    configured.mark();
   }
   // 1024 threads: one CTA per utterance means few resident warps, and both the tile loads and the per-column pass are
   // latency-bound (measured 256 / 512 / 1024 threads: 0.34 / 0.29 / 0.26 ms at 170 x 512, 5.2 / 3.4 / 2.4 ms at 667 x 2001)

@@ -78,10 +78,14 @@ struct Launch {
   cudaError_t operator()(cudaStream_t s) const { return fn(s); }
 };
 constexpr int kProfRegions = 6, kProfKinds = 4;
+// Cached launch programs (one CUDA graph per shape) a plan keeps per cache: serving sees a bounded set of T_pad buckets,
+// and an unbounded map of instantiated graphs is a slow leak when it does not.
+constexpr size_t kMaxCachedPrograms = 32;
 struct Program {
   std::vector<Launch> ops;
   cudaGraphExec_t graph = nullptr;
   long long kernels = 0;  // kernel launches per run (memsets not counted)
+  unsigned long long last_use = 0;   // plan-wide use counter at the last run: the program caches are bounded LRUs
   std::vector<float> host_f32;  // small per-program host constants (Euler t schedule)
 };
 
@@ -191,6 +195,18 @@ class Plan {
   bool ff_supported() const { return fuse_ff && tensor_core() && kernel_version >= 2; }
   bool pair_supported(int C) const { return fuse_pairs && tensor_core() && kernel_version >= 2 && (C == 64 || C == 32); }
   void run(Program& prog, cudaStream_t st);
+  // makes room for one more entry: evicts the least recently used program (its graph is freed once it has drained)
+  template <class Map>
+  void make_room(Map& cache) {
+    while (cache.size() >= kMaxCachedPrograms) {
+      auto victim = cache.begin();
+      for (auto it = cache.begin(); it != cache.end(); ++it)
+        if (it->second->last_use < victim->second->last_use) victim = it;
+      if (victim->second->graph) cudaGraphExecDestroy(victim->second->graph);
+      cache.erase(victim);
+    }
+  }
+  size_t cached_programs() const { return decode_cache_.size() + vocoder_cache_.size(); }
 
  private:
   std::vector<void*> owned_;
@@ -203,6 +219,11 @@ class Plan {
   DevBuf ws_est_[28];
   DevBuf ws_voc_[8];
   DevBuf ws_io_[8];
+  unsigned long long use_clock_ = 0;
+  cudaStream_t host_stream_ = nullptr;   // synthesise_host: private non-blocking compute stream (never the legacy default stream)
+  cudaEvent_t busy_ = nullptr;           // recorded after every asynchronous call on the caller's stream: the workspaces'
+                                         // last user, which the private stream waits for
+  void mark_busy(cudaStream_t st);
   cudaStream_t copy_stream_ = nullptr;   // synthesise_host: mel read-back overlapping the vocoder
   cudaEvent_t mel_ready_ = nullptr;
   cudaEvent_t wav_ready_[4] = {nullptr, nullptr, nullptr, nullptr};

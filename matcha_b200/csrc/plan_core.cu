@@ -59,6 +59,13 @@ Plan::~Plan() {
   if (mel_ready_) cudaEventDestroy(mel_ready_);
   for (auto e : wav_ready_) if (e) cudaEventDestroy(e);
   if (copy_stream_) cudaStreamDestroy(copy_stream_);
+  if (host_stream_) cudaStreamDestroy(host_stream_);
+  if (busy_) cudaEventDestroy(busy_);
+}
+
+void Plan::mark_busy(cudaStream_t st) {
+  if (!busy_) MB_CUDA(cudaEventCreateWithFlags(&busy_, cudaEventDisableTiming));
+  MB_CUDA(cudaEventRecord(busy_, st));
 }
 
 void* Plan::dalloc(size_t bytes) {
@@ -66,6 +73,7 @@ void* Plan::dalloc(size_t bytes) {
   bytes = (bytes + 255) & ~size_t(255);
   MB_CUDA(cudaMalloc(&p, bytes));
   MB_CUDA(cudaMemset(p, 0, bytes));
+  MB_CUDA(cudaDeviceSynchronize());   // the memset runs on the legacy default stream, which non-blocking streams do not wait for
   owned_.push_back(p);
   bytes_allocated += static_cast<long long>(bytes);
   return p;
@@ -88,6 +96,8 @@ void* Plan::ensure(DevBuf& b, size_t bytes) {
   bytes = (bytes + 1023) & ~size_t(1023);
   MB_CUDA(cudaMalloc(&b.p, bytes));
   MB_CUDA(cudaMemset(b.p, 0, bytes));
+  MB_CUDA(cudaDeviceSynchronize());   // as in dalloc: callers' streams (torch side streams, synthesise_host's private stream)
+                                      // are not ordered against the legacy stream's memset; growth is rare
   b.bytes = bytes;
   bytes_allocated += static_cast<long long>(bytes);
   return b.p;
@@ -582,6 +592,7 @@ Launch Plan::attention_op(const void* qkv, const float* mask, void* out, int B, 
 }
 
 void Plan::run(Program& prog, cudaStream_t st) {
+  prog.last_use = ++use_clock_;
   if (profiling) {
     std::vector<cudaEvent_t> ev(prog.ops.size() + 1);
     for (auto& e : ev) MB_CUDA(cudaEventCreate(&e));

@@ -322,11 +322,11 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 template <int C, int MB, typename T>
 static cudaError_t launch_pair_inst(const PairLaunch& L, cudaStream_t st) {
   auto kern = resblock_pair_kernel<C, MB, T>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (err != cudaSuccess) return err;
-    configured = true;
+    configured.mark();
   }
   kern<<<L.grid, 448, L.smem_bytes, st>>>(L.tmA, L.tmA8, L.tmW1, L.tmW2, L.g, L.e);
   return cudaGetLastError();

@@ -177,11 +177,11 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
 template <typename T>
 cudaError_t launch_resqkv_fused(const RQLaunch& L, cudaStream_t st) {
   auto kern = resqkv_fused_kernel<T>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (err != cudaSuccess) return err;
-    configured = true;
+    configured.mark();
   }
   kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmA0, L.tmA1, L.tmWres, L.tmWqkv, L.g);
   return cudaGetLastError();

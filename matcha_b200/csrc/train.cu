@@ -39,13 +39,13 @@ void gemm(Ctx& c, Gemm p, int nz) {
   if (p.nz2 <= 0) p.nz2 = 1;
   const int mode = train_gemm_mode();
   if (mode != 0 && p.M >= 32 && p.N >= 32) {
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    if (configured.needed()) {
       MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<3, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(128)));
       MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<1, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(128)));
       MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<3, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(64)));
       MB_CUDA(cudaFuncSetAttribute(trn::tgemm_kernel<1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, trn::tgemm_smem_bytes(64)));
-      configured = true;
+      configured.mark();
     }
     // 64-row tiles only for short M: measured at cfg5's shape, trading 128-row tiles for twice the blocks on the
     // ~128-block GEMMs is slower (28.9 against 28.2 ms per step: B fragments are re-read per flop twice as often)

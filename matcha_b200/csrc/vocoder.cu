@@ -205,6 +205,7 @@ void Plan::hifigan_forward(const float* mel, int Tsrc, float scale, float shift,
   if (it == vocoder_cache_.end()) {
     auto prog = std::make_unique<Program>();
     build_vocoder(*prog, B, L, nullptr);
+    make_room(vocoder_cache_);
     it = vocoder_cache_.emplace(key, std::move(prog)).first;
   }
   run(*it->second, st);
@@ -242,6 +243,7 @@ void Plan::hifigan_forward(const float* mel, int Tsrc, float scale, float shift,
     }
   }
   launches += 1;
+  mark_busy(st);
 }
 
 void Plan::synthesise(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
@@ -269,7 +271,12 @@ void Plan::synthesise_host(const float* mu, const float* mask, const float* z, c
   float* d_spk = spks ? static_cast<float*>(ensure(ws_io_[5], n_spk * 4)) : nullptr;
   float* d_melo = static_cast<float*>(ensure(ws_io_[6], n_out_mel * 4));
   float* d_wav = static_cast<float*>(ensure(ws_io_[7], n_wav * 4));
-  cudaStream_t st = nullptr;  // legacy default stream: ordered against everything else in the process
+  // A private NON-BLOCKING stream: the call neither serialises against the legacy default stream's implicit barriers nor
+  // stalls other streams of the process.  It is ordered after the plan's last asynchronous call (the workspaces' last user)
+  // and ends synchronous, so later calls on any stream are ordered after it by the host.
+  if (!host_stream_) MB_CUDA(cudaStreamCreateWithFlags(&host_stream_, cudaStreamNonBlocking));
+  cudaStream_t st = host_stream_;
+  if (busy_) MB_CUDA(cudaStreamWaitEvent(st, busy_, 0));
   MB_CUDA(cudaMemcpyAsync(d_mu, mu, n_mel * 4, cudaMemcpyHostToDevice, st));
   MB_CUDA(cudaMemcpyAsync(d_z, z, n_mel * 4, cudaMemcpyHostToDevice, st));
   MB_CUDA(cudaMemcpyAsync(d_mask, mask, n_mask * 4, cudaMemcpyHostToDevice, st));

@@ -317,3 +317,38 @@ def test_module_api_is_drop_in(golden_dir):
     check(gen(gfx["mel"].cuda()), gfx["wav"], "fp32")
     gen.remove_weight_norm()   # cli.py:84-90 order: load with weight-norm keys, then remove
     check(gen(gfx["mel"].cuda()), gfx["wav"], "fp32")
+
+
+# ------------------------------------------------------------------------------------------ operand range
+@pytest.mark.parametrize("scale,fp16_overflows", [(1e3, False), (3e4, True)])
+def test_large_pre_groupnorm_activations_and_the_half_modes(scale, fp16_overflows):
+    """What the 16-bit modes do when a checkpoint's raw conv outputs are large.  Every Block1D conv (decoder.py:36) is
+    scaled by `scale`: GroupNorm right after it is scale-invariant, so the reference's velocity barely changes, but the
+    conv output that the CUDA path stores in the operand dtype reaches ~4e3 (scale 1e3) and ~1e5 (scale 3e4).
+      * fp32 and bf16 (8 exponent bits) are unaffected at both scales;
+      * fp16 is fine while the raw values stay below 65504 and OVERFLOWS beyond: the output is then non-finite - loudly
+        wrong, never silently so.  That is the failure mode to know about before choosing fp16 (the benchmark dtype, picked
+        for its 3 extra mantissa bits) for a trained checkpoint: use precision="bf16" when pre-norm activations can
+        exceed ~6e4 (precision modes)."""
+    sd = weights.estimator_state_dict(160, seed=21)
+    for k in list(sd):
+        if k.endswith("block.0.weight") or k.endswith("block.0.bias"):
+            sd[k] = sd[k] * scale
+    g = torch.Generator().manual_seed(9)
+    b, t = 2, 24
+    x, mu = torch.randn(b, 80, t, generator=g), torch.randn(b, 80, t, generator=g)
+    mask = weights.prefix_mask([24, 17], t)
+    tt = torch.tensor(0.3)
+    with torch.inference_mode():
+        want = mo.estimator_forward(sd, x, mask, mu, tt)
+    out = {}
+    for prec in ("fp32", "bf16", "fp16"):
+        plan = Plan(prec, 160, use_graph=False)
+        plan.load_estimator(sd)
+        out[prec] = plan.estimator_forward(x, mask, mu, tt).cpu()
+    assert maxabs(out["fp32"], want) <= 5 * FP32_MAXABS        # raw values of 1e5 carry 1e-2 of absolute fp32 rounding into GroupNorm
+    assert torch.isfinite(out["bf16"]).all() and rel_l2(out["bf16"], want) <= 2.5e-2
+    if fp16_overflows:
+        assert not torch.isfinite(out["fp16"]).all()
+    else:
+        assert torch.isfinite(out["fp16"]).all() and rel_l2(out["fp16"], want) <= HALF_REL_L2

@@ -35,5 +35,5 @@ valid = sum(lengths)
 flop_fwd = B * T * (10_985_472 + 1536 * T)
 res["frames_per_s_fwd_bwd"] = valid / (res["fwd+bwd"]["ms"] * 1e-3)
 res["tflops_fwd_bwd"] = 3 * flop_fwd / (res["fwd+bwd"]["ms"] * 1e-3) / 1e12
-res["config"] = {"B": B, "T": T, "valid_frames": valid, "dtype": "f32", "gemm": os.environ.get("MB200_TRAIN_GEMM", "tf32x3"), "workspace_gb": plan.workspace_bytes() / 1e9}
+res["config"] = {"B": B, "T": T, "valid_frames": valid, "dtype": "f32 data, GEMMs " + {"tf32x3": "3xTF32 tensor-core (fp32-accurate)", "tf32": "plain TF32 tensor-core", "ffma": "FFMA"}.get(os.environ.get("MB200_TRAIN_GEMM", "tf32x3"), "?"), "gemm": os.environ.get("MB200_TRAIN_GEMM", "tf32x3"), "workspace_gb": plan.workspace_bytes() / 1e9}
 print(json.dumps(res))
