@@ -47,6 +47,17 @@ int mb200_load_estimator(mb200_plan* plan, const mb200_tensor* tensors, int n, c
  * matcha/cli.py:87) or plain weight (after remove_weight_norm, models.py:199-206). */
 int mb200_load_generator(mb200_plan* plan, const mb200_tensor* tensors, int n);
 
+/* TextEncoder parameters (matcha/models/components/text_encoder.py:328-376: emb, prenet.*, encoder.*, proj_m, proj_w.*);
+ * `prefix` ("encoder." in a MatchaTTS state_dict) is stripped.  n_heads = encoder_params.n_heads (2 in the shipped
+ * configs; head dims 96 = LJSpeech and 128 = VCTK have kernels).  fp32 plans only: see mb200_text_encoder_forward. */
+int mb200_load_text_encoder(mb200_plan* plan, const mb200_tensor* tensors, int n, const char* prefix, int n_heads);
+/* TextEncoder.forward(x, x_lengths, spks) (text_encoder.py:378-410) including the DurationPredictor (:70-94).  DEVICE
+ * pointers: ids (B, Lx) int64 phoneme ids, lengths (B,) int64, spks (B, spk_emb_dim) fp32 speaker vectors or NULL for a
+ * single-speaker model; outputs mu_x (B, 80, Lx), logw (B, 1, Lx), x_mask (B, 1, Lx), fp32.  Runs in fp32 whatever the
+ * decoder's mode: the durations go through ceil(exp(logw)) (matcha_tts.py:118-119).  Inference only (no dropout). */
+int mb200_text_encoder_forward(mb200_plan* plan, const long long* ids, const long long* lengths, const float* spks, int B, int Lx,
+                               float* mu_x, float* logw, float* x_mask, void* stream);
+
 /* The (t, dt) pairs BASECFM.solve_euler uses (matcha/models/components/flow_matching.py:52,70-83), fp32. Host only. */
 int mb200_euler_schedule(int n_steps, float* t_out, float* dt_out);
 

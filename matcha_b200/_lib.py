@@ -16,7 +16,7 @@ DTYPES = {"fp32": F32, "float32": F32, "bf16": BF16, "bfloat16": BF16, "fp16": F
 
 EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
-    "mb200_load_generator", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
+    "mb200_load_generator", "mb200_load_text_encoder", "mb200_text_encoder_forward", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
     "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_maximum_path", "mb200_maximum_path_workspace_bytes", "mb200_maximum_path_static", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
@@ -59,6 +59,8 @@ def load():
         lib.mb200_plan_destroy.restype = None
         lib.mb200_load_estimator.argtypes = [vp, ctypes.POINTER(Tensor), i, ctypes.c_char_p]
         lib.mb200_load_generator.argtypes = [vp, ctypes.POINTER(Tensor), i]
+        lib.mb200_load_text_encoder.argtypes = [vp, ctypes.POINTER(Tensor), i, ctypes.c_char_p, i]
+        lib.mb200_text_encoder_forward.argtypes = [vp, vp, vp, vp, i, i, vp, vp, vp, vp]
         lib.mb200_euler_schedule.argtypes = [i, ctypes.POINTER(f), ctypes.POINTER(f)]
         lib.mb200_estimator_forward.argtypes = [vp, vp, vp, vp, vp, i, vp, i, i, vp, vp]
         lib.mb200_cfm_decode.argtypes = [vp, vp, vp, vp, vp, i, i, i, vp, vp]
@@ -231,7 +233,27 @@ class Plan:
             check(self.lib.mb200_load_generator(self.handle, arr, n))
         del keep
 
+    def load_text_encoder(self, state_dict, n_heads=2, prefix=""):
+        arr, n, keep = self._tensor_array(state_dict)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_load_text_encoder(self.handle, arr, n, prefix.encode(), int(n_heads)))
+        del keep
+
     # ---- compute
+    def text_encoder_forward(self, x, x_lengths, spks=None):
+        """TextEncoder.forward on the CUDA kernels: ids (B, Lx), lengths (B,) -> mu_x (B,80,Lx), logw (B,1,Lx), x_mask (B,1,Lx)."""
+        b, lx = x.shape
+        ids = x.detach().to(device=self.device, dtype=torch.int64).contiguous()
+        lens = x_lengths.detach().to(device=self.device, dtype=torch.int64).contiguous()
+        spks = _dev_f32(spks, self.device)
+        mu_x = torch.empty(b, 80, lx, device=self.device, dtype=torch.float32)
+        logw = torch.empty(b, 1, lx, device=self.device, dtype=torch.float32)
+        x_mask = torch.empty(b, 1, lx, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_text_encoder_forward(self.handle, _ptr(ids), _ptr(lens), _ptr(spks), b, lx, _ptr(mu_x),
+                                                      _ptr(logw), _ptr(x_mask), _stream()))
+        return mu_x, logw, x_mask
+
     def estimator_forward(self, x, mask, mu, t, spks=None):
         b, c, tt = x.shape
         x, mask, mu, spks = (_dev_f32(v, self.device) for v in (x, mask, mu, spks))

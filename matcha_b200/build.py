@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmatcha_b200.so")
-SOURCES = ["conv_gemm.cu", "conv_gemm2.cu", "resblock_pair.cu", "ff_fused.cu", "resqkv_fused.cu", "elementwise.cu", "attention.cu", "attention_mma.cu", "attention_umma.cu", "plan_core.cu", "estimator.cu", "vocoder.cu", "train.cu", "denoiser.cu", "length_regulate.cu", "mas.cu", "capi.cu"]
+SOURCES = ["conv_gemm.cu", "conv_gemm2.cu", "resblock_pair.cu", "ff_fused.cu", "resqkv_fused.cu", "elementwise.cu", "attention.cu", "attention_mma.cu", "attention_umma.cu", "plan_core.cu", "estimator.cu", "vocoder.cu", "train.cu", "denoiser.cu", "length_regulate.cu", "text_encoder.cu", "mas.cu", "capi.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
               "-Xcompiler", "-fPIC"]
 if os.environ.get("MB200_PROBE_BUILD"):   # developer builds: pipeline-stage knockout switches in the persistent kernel

@@ -235,6 +235,16 @@ int mb200_maximum_path(const float* value, const float* mask, int B, int Tx, int
     mb::maximum_path(value, mask, B, Tx, Ty, path, workspace, static_cast<cudaStream_t>(stream));
   });
 }
+int mb200_load_text_encoder(mb200_plan* plan, const mb200_tensor* tensors, int n, const char* prefix, int n_heads) {
+  return guarded([&] { P(plan)->load_text_encoder(to_state_dict(tensors, n, prefix ? prefix : ""), n_heads); });
+}
+int mb200_text_encoder_forward(mb200_plan* plan, const long long* ids, const long long* lengths, const float* spks, int B, int Lx,
+                               float* mu_x, float* logw, float* x_mask, void* stream) {
+  return guarded([&] {
+    if (!ids || !lengths || !mu_x || !logw || !x_mask) throw mb::Error("null argument");
+    P(plan)->text_encoder_forward(ids, lengths, spks, B, Lx, mu_x, logw, x_mask, static_cast<cudaStream_t>(stream));
+  });
+}
 int mb200_maximum_path_static(const float* value, const float* mask, int B, int Tx, int Ty, float* path, void* stream) {
   return guarded([&] {
     if (!value || !mask || !path) throw mb::Error("null argument");

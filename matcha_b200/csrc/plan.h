@@ -113,6 +113,22 @@ struct GeneratorW {
   float post_b = 0.f;
 };
 
+// Text encoder + duration predictor (text_encoder.cu); fp32 plans only.
+struct TextEncW {
+  bool loaded = false;
+  int n_vocab = 0, C0 = 0, C = 0, H = 0, Dh = 0, n_layers = 0, filt = 0, filt_dp = 0, spk_dim = 0, n_feats = 80;
+  float* emb = nullptr;
+  PackedW pre_conv[3], pre_proj;
+  float *pre_g[3], *pre_b[3];
+  struct Layer {
+    PackedW qkv, o, ffn1, ffn2;
+    float *n1_g, *n1_b, *n2_g, *n2_b;
+  } layer[8];
+  PackedW proj_m, dp_conv1, dp_conv2, dp_proj;
+  float *dp_g1, *dp_b1, *dp_g2, *dp_b2;
+  float* theta = nullptr;   // [Dh / 4] rotary frequencies
+};
+
 class Plan {
  public:
   explicit Plan(const mb200_cfg& cfg);
@@ -135,6 +151,11 @@ class Plan {
                          const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
                          float sigma_min, float* loss_out, float* y_out, float* v_out, float* dmu, float* dspks, bool backward,
                          cudaStream_t st);
+  // TextEncoder.forward (text_encoder.py:378-410): ids (B, Lx) int64, lengths (B,) int64, spks (B, spk_dim) or null ->
+  // mu_x (B, 80, Lx), logw (B, 1, Lx), x_mask (B, 1, Lx); all device pointers.  fp32 plans only.
+  void load_text_encoder(const StateDict& sd, int n_heads);
+  void text_encoder_forward(const long long* ids, const long long* lengths, const float* spks, int B, int Lx, float* mu_x,
+                            float* logw, float* x_mask, cudaStream_t st);
   // HiFi-GAN bias denoiser (hifigan/denoiser.py:53-64): bias = |STFT(audio)|[:, 0] (513 bins); out (B, 256*(L/256))
   void denoiser_bias(const float* audio, int L, float* bias, cudaStream_t st);
   void denoise(const float* audio, int B, int L, const float* bias, float strength, float* out, cudaStream_t st);
@@ -215,6 +236,8 @@ class Plan {
   std::recursive_mutex mu_;
   EstimatorW est_;
   GeneratorW gen_;
+  TextEncW enc_;
+  DevBuf ws_enc_[10];
   // workspaces
   DevBuf ws_est_[28];
   DevBuf ws_voc_[8];

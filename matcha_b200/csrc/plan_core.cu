@@ -56,6 +56,7 @@ Plan::~Plan() {
   for (auto& b : ws_est_) if (b.p) cudaFree(b.p);
   for (auto& b : ws_voc_) if (b.p) cudaFree(b.p);
   for (auto& b : ws_io_) if (b.p) cudaFree(b.p);
+  for (auto& b : ws_enc_) if (b.p) cudaFree(b.p);
   if (mel_ready_) cudaEventDestroy(mel_ready_);
   for (auto e : wav_ready_) if (e) cudaEventDestroy(e);
   if (copy_stream_) cudaStreamDestroy(copy_stream_);

@@ -188,7 +188,24 @@ class TextEncoder(nn.Module):
         self.proj_w = _DurationPredictor(ch, _get(d, "filter_channels_dp"), _get(d, "kernel_size"),
                                          float(_get(d, "p_dropout", 0.0) or 0.0))
 
+    def _cuda_plan(self):
+        """The fp32 plan holding this module's packed weights for the CUDA kernels (csrc/text_encoder.cu); re-packed when
+        a parameter changed."""
+        from . import _lib
+        version = tuple(p._version for p in self.parameters())
+        if getattr(self, "_plan_version", None) != version or getattr(self, "_plan", None) is None:
+            dev = next(self.parameters()).device
+            plan = _lib.Plan("fp32", 160, device=dev)
+            plan.load_text_encoder(self.state_dict(), n_heads=self.encoder.attn_layers[0].n_heads)
+            self._plan, self._plan_version = plan, version
+        return self._plan
+
     def forward(self, x, x_lengths, spks=None):
+        """Inference on a GPU (no gradients wanted, module in eval mode) runs the hand-written kernels (SURVEY.md section 8(f)
+        row 3).  Training keeps the torch formulation below: it needs autograd and dropout, and north_star leaves the
+        encoder's training to PyTorch."""
+        if x.is_cuda and not self.training and not torch.is_grad_enabled() and self.prenet is not None:
+            return self._cuda_plan().text_encoder_forward(x, x_lengths, spks)
         h = self.emb(x).transpose(1, 2) * math.sqrt(self.n_channels)
         x_mask = sequence_mask(x_lengths, h.shape[2]).unsqueeze(1).to(h.dtype)
         if self.prenet is not None:
