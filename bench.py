@@ -273,8 +273,9 @@ def run_ours(args):
                 bt[k] = bt[k + "_h"].to(dev)
             else:
                 bt[k + "_h"] = None
-        bt["mel_h"] = torch.empty(len(bt["lens"]), 80, bt["length"]).pin_memory()
-        bt["wav_h"] = torch.empty(len(bt["lens"]), 1, 256 * bt["length"]).pin_memory()
+        # two sets of pinned output buffers: the end-to-end loop keeps two batches in flight
+        bt["mel_h"] = [torch.empty(len(bt["lens"]), 80, bt["length"]).pin_memory() for _ in range(2)]
+        bt["wav_h"] = [torch.empty(len(bt["lens"]), 1, 256 * bt["length"]).pin_memory() for _ in range(2)]
 
     # The path's only exchange: the final gather of mels / waveforms to rank 0 over NVLink.  It is issued asynchronously
     # (NCCL's own stream) and overlaps the NEXT step's decode; every rank's contribution has the same shape per batch
@@ -341,26 +342,32 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t)
 
-    # ---- end to end through the host-buffer C-ABI call (pinned inputs H2D + mel/wav D2H inside the timed region)
-    def step_host():
-        for bt in batches:
-            plan.synthesise_host(bt["mu_h"], bt["mask_h"], bt["z_h"], n_steps, bt["length"], mean, std, spks=bt["spks_h"],
-                                 mel_out=bt["mel_h"], wav_out=bt["wav_h"])
+    # ---- end to end through the host-buffer C-ABI calls (pinned inputs H2D + mel/wav D2H of EVERY step inside the timed
+    # region).  A serving loop double-buffers: batch i+1 is submitted before batch i is waited for, so its upload and batch
+    # i's read-back overlap the other's compute (mb200_synthesise_host_submit / _wait, two slots).
+    jobs = [bt for _ in range(args.steps) for bt in batches]
 
-    for _ in range(2):
-        step_host()
+    def run_host(job_list):
+        for i, bt in enumerate(job_list):
+            if i >= 2:
+                plan.synthesise_host_wait(i % 2)
+            plan.synthesise_host_submit(bt["mu_h"], bt["mask_h"], bt["z_h"], n_steps, bt["length"], mean, std,
+                                        bt["mel_h"][i % 2], bt["wav_h"][i % 2], spks=bt["spks_h"], slot=i % 2)
+        for i in range(max(0, len(job_list) - 2), len(job_list)):
+            plan.synthesise_host_wait(i % 2)
+
+    run_host(batches * 2)
     sync_all()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_host()
-    ms_e2e = (time.perf_counter() - t0) * 1e3 / args.steps   # the call synchronises before returning
+    run_host(jobs)
+    ms_e2e = (time.perf_counter() - t0) * 1e3 / args.steps   # every output is in host memory when run_host returns
     clocks = sampler.stop() if rank == 0 else None
     if world > 1:
         t = torch.tensor([ms_e2e], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_e2e = float(t)
     h2d = sum(bt[k].numel() * 4 for bt in batches for k in ("mu_h", "z_h", "mask_h", "spks_h") if bt[k] is not None)
-    d2h = sum((bt["mel_h"].numel() + bt["wav_h"].numel()) * 4 for bt in batches)
+    d2h = sum((bt["mel_h"][0].numel() + bt["wav_h"][0].numel()) * 4 for bt in batches)
 
     # ---- per-kernel-family timing (CUDA events around every launch, on the launching stream), rank 0
     roofline, breakdown = None, None

@@ -86,6 +86,17 @@ int mb200_synthesise(mb200_plan* plan, const float* mu, const float* mask, const
 int mb200_synthesise_host(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
                           int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out);
 
+/* mb200_synthesise_host split in two, for double buffering by a serving loop (no counterpart in the reference, whose
+ * synthesise is one synchronous call): submit queues the upload, the hot path and the read-backs of one batch on the
+ * plan's private streams and returns at once; wait blocks until that batch's mel_out / wav_out are complete in host
+ * memory.  slot is 0 or 1: with two batches in flight the upload of batch i+1 and the read-back of batch i overlap the
+ * other's compute.  Host buffers must stay valid (and untouched) until wait, and must be pinned for the copies to overlap.
+ * A slot must be waited for before it is submitted again.  mb200_synthesise_host = submit(slot 0) + wait(0). */
+int mb200_synthesise_host_submit(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B,
+                                 int T, int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out,
+                                 int slot);
+int mb200_synthesise_host_wait(mb200_plan* plan, int slot);
+
 /* Denoiser.__init__ (matcha/hifigan/denoiser.py:53-57): bias (513,) = |STFT(bias_audio (L,))|[:, frame 0] with
  * n_fft = win = 1024, hop 256, periodic Hann, center / reflect padding (denoiser.py:26-44).  L > 512. */
 int mb200_denoiser_bias(mb200_plan* plan, const float* bias_audio, int L, float* bias, void* stream);

@@ -17,7 +17,7 @@ DTYPES = {"fp32": F32, "float32": F32, "bf16": BF16, "bfloat16": BF16, "fp16": F
 EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_load_text_encoder", "mb200_text_encoder_forward", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
-    "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_launch_count",
+    "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_synthesise_host_submit", "mb200_synthesise_host_wait", "mb200_launch_count",
     "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_maximum_path", "mb200_maximum_path_workspace_bytes", "mb200_maximum_path_static", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
 
@@ -67,6 +67,8 @@ def load():
         lib.mb200_hifigan_forward.argtypes = [vp, vp, i, i, vp, vp]
         lib.mb200_synthesise.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp, vp, vp]
         lib.mb200_synthesise_host.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp]
+        lib.mb200_synthesise_host_submit.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, f, f, vp, vp, i]
+        lib.mb200_synthesise_host_wait.argtypes = [vp, i]
         lib.mb200_compute_loss.argtypes = [vp, ctypes.POINTER(Param), i, ctypes.c_char_p, vp, vp, vp, vp, vp, vp, i, i, f, i,
                                            vp, vp, vp, vp, vp, vp]
         lib.mb200_denoiser_bias.argtypes = [vp, vp, i, vp, vp]
@@ -314,6 +316,22 @@ class Plan:
                                                  int(n_steps), int(length), float(mel_mean), float(mel_std),
                                                  _ptr(mel_out), _ptr(wav_out)))
         return mel_out, wav_out
+
+    def synthesise_host_submit(self, mu, mask, z, n_steps, length, mel_mean, mel_std, mel_out, wav_out, spks=None, slot=0):
+        """First half of synthesise_host: queue one batch (pinned fp32 CPU tensors in, pinned outputs) and return.  Pair
+        with synthesise_host_wait(slot); two slots allow the copies of one batch to overlap the compute of the other."""
+        b, c, tt = mu.shape
+        for v in (mu, mask, z, spks, mel_out, wav_out):
+            if v is not None and (v.is_cuda or v.dtype != torch.float32 or not v.is_contiguous()):
+                raise ValueError("synthesise_host_submit takes contiguous fp32 CPU tensors")
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_synthesise_host_submit(self.handle, _ptr(mu), _ptr(mask), _ptr(z), _ptr(spks), b, tt,
+                                                        int(n_steps), int(length), float(mel_mean), float(mel_std),
+                                                        _ptr(mel_out), _ptr(wav_out), int(slot)))
+
+    def synthesise_host_wait(self, slot=0):
+        with torch.cuda.device(self.device):
+            check(self.lib.mb200_synthesise_host_wait(self.handle, int(slot)))
 
     def compute_loss(self, named_params, x1, mask, mu, z, t, spks=None, sigma_min=1e-4, backward=True, want_dmu=False,
                      want_dspks=False):

@@ -235,6 +235,16 @@ int mb200_maximum_path(const float* value, const float* mask, int B, int Tx, int
     mb::maximum_path(value, mask, B, Tx, Ty, path, workspace, static_cast<cudaStream_t>(stream));
   });
 }
+int mb200_synthesise_host_submit(mb200_plan* plan, const float* mu, const float* mask, const float* z, const float* spks, int B, int T,
+                                 int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out, int slot) {
+  return guarded([&] {
+    if (!mu || !mask || !z || !wav_out) throw mb::Error("null argument");
+    P(plan)->synthesise_host_submit(mu, mask, z, spks, B, T, n_steps, L, mel_mean, mel_std, mel_out, wav_out, slot);
+  });
+}
+int mb200_synthesise_host_wait(mb200_plan* plan, int slot) {
+  return guarded([&] { P(plan)->synthesise_host_wait(slot); });
+}
 int mb200_load_text_encoder(mb200_plan* plan, const mb200_tensor* tensors, int n, const char* prefix, int n_heads) {
   return guarded([&] { P(plan)->load_text_encoder(to_state_dict(tensors, n, prefix ? prefix : ""), n_heads); });
 }

@@ -368,7 +368,6 @@ void Plan::cfm_decode(const float* mu, const float* mask, const float* z, const 
   if (n_steps < 1 || n_steps > 1024) throw Error("n_steps out of range");
   if ((cfg.c_in > 160) != (spks != nullptr)) throw Error("spks must be given exactly when c_in > 160");
   estimator_buffers(B, T);
-  ensure(ws_est_[TVALS], n_steps * 4);
   ensure(ws_est_[TEMB0], static_cast<size_t>(n_steps) * 1024 * 4);
   ensure(ws_est_[TEMB1], static_cast<size_t>(n_steps) * 1024 * 4);
   ensure(ws_est_[TPROJ], static_cast<size_t>(n_steps) * 6 * 256 * 4);
@@ -377,7 +376,6 @@ void Plan::cfm_decode(const float* mu, const float* mask, const float* z, const 
   float* mT = static_cast<float*>(ws_est_[MASK_T].p);
   float* mH = static_cast<float*>(ws_est_[MASK_H].p);
   float* spk = static_cast<float*>(ws_est_[SPK].p);
-  float* tv = static_cast<float*>(ws_est_[TVALS].p);
   const int spk_dim = cfg.c_in - 160;
   const int cpad = (cfg.c_in + 63) / 64 * 64;
 
@@ -394,7 +392,10 @@ void Plan::cfm_decode(const float* mu, const float* mask, const float* z, const 
     auto prog = std::make_unique<Program>();
     std::vector<float> ts(n_steps), dts(n_steps);
     euler_schedule_host(n_steps, ts.data(), dts.data());
-    prog->host_f32 = ts;
+    // The schedule is a constant of the program: its own device copy, uploaded once here.  (It used to be refreshed every
+    // call from pageable host memory; the runtime drains the stream before such a copy, which serialised back-to-back
+    // host-buffer calls against each other.)
+    float* tv = upload_f32(ts.data(), ts.size());
     auto add = [&](Launch l) { prog->ops.push_back(std::move(l)); prog->kernels++; };
     add([=](cudaStream_t s) { return launch_mask_half(mT, mH, B, T, s); });
     const int dtype = cfg.dtype;
@@ -410,8 +411,6 @@ void Plan::cfm_decode(const float* mu, const float* mask, const float* z, const 
     make_room(decode_cache_);
     it = decode_cache_.emplace(key, std::move(prog)).first;
   }
-  // the schedule buffer is shared with other shapes / estimator_forward: refresh it (n_steps floats) every call
-  MB_CUDA(cudaMemcpyAsync(tv, it->second->host_f32.data(), n_steps * 4, cudaMemcpyHostToDevice, st));
   run(*it->second, st);
   if (out) { MB_CUDA(launch_btc_to_bct(xs, out, B, 80, T, st)); launches += 1; }
   mark_busy(st);

@@ -145,6 +145,12 @@ class Plan {
                   float mel_mean, float mel_std, float* dec_out, float* mel_out, float* wav_out, cudaStream_t st);
   void synthesise_host(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
                        int L, float mel_mean, float mel_std, float* mel_out, float* wav_out);
+  // The same call split in two for double buffering: submit() queues upload, hot path and read-backs of one batch on the
+  // plan's private streams and returns; wait() blocks until that batch's outputs are in host memory.  Two slots: the upload
+  // of batch i+1 and the read-back of batch i overlap the compute of the other.  Host buffers must stay valid until wait().
+  void synthesise_host_submit(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
+                              int L, float mel_mean, float mel_std, float* mel_out, float* wav_out, int slot);
+  void synthesise_host_wait(int slot);
   // BASECFM.compute_loss forward (+ backward) on the fp32 training kernels (train.cu).  params: name -> (parameter, gradient)
   // device pointers in the reference layout; gradients are ACCUMULATED (+=) into non-null gradient pointers.
   void compute_loss_grad(const std::map<std::string, std::pair<const float*, float*>>& params, const float* x1,
@@ -247,6 +253,12 @@ class Plan {
   cudaEvent_t busy_ = nullptr;           // recorded after every asynchronous call on the caller's stream: the workspaces'
                                          // last user, which the private stream waits for
   void mark_busy(cudaStream_t st);
+  struct HostSlot {                      // staging of one in-flight synthesise_host_submit
+    DevBuf mu, z, mask, spk, mel, wav;
+    cudaEvent_t uploaded = nullptr, computed = nullptr, copied = nullptr;
+    bool busy = false;
+  } slots_[2];
+  cudaStream_t upload_stream_ = nullptr; // host -> device copies of the next batch, overlapping the current batch's compute
   cudaStream_t copy_stream_ = nullptr;   // synthesise_host: mel read-back overlapping the vocoder
   cudaEvent_t mel_ready_ = nullptr;
   cudaEvent_t wav_ready_[4] = {nullptr, nullptr, nullptr, nullptr};

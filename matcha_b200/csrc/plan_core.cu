@@ -61,6 +61,11 @@ Plan::~Plan() {
   for (auto e : wav_ready_) if (e) cudaEventDestroy(e);
   if (copy_stream_) cudaStreamDestroy(copy_stream_);
   if (host_stream_) cudaStreamDestroy(host_stream_);
+  if (upload_stream_) cudaStreamDestroy(upload_stream_);
+  for (auto& sl : slots_) {
+    for (DevBuf* b : {&sl.mu, &sl.z, &sl.mask, &sl.spk, &sl.mel, &sl.wav}) if (b->p) cudaFree(b->p);
+    for (cudaEvent_t e : {sl.uploaded, sl.computed, sl.copied}) if (e) cudaEventDestroy(e);
+  }
   if (busy_) cudaEventDestroy(busy_);
 }
 

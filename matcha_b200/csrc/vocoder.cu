@@ -261,36 +261,59 @@ void Plan::synthesise(const float* mu, const float* mask, const float* z, const 
 
 void Plan::synthesise_host(const float* mu, const float* mask, const float* z, const float* spks, int B, int T, int n_steps,
                            int L, float mel_mean, float mel_std, float* mel_out, float* wav_out) {
+  synthesise_host_submit(mu, mask, z, spks, B, T, n_steps, L, mel_mean, mel_std, mel_out, wav_out, 0);
+  synthesise_host_wait(0);
+}
+
+void Plan::synthesise_host_submit(const float* mu, const float* mask, const float* z, const float* spks, int B, int T,
+                                  int n_steps, int L, float mel_mean, float mel_std, float* mel_out, float* wav_out, int slot) {
   std::lock_guard<std::recursive_mutex> lk(mu_);
+  if (slot < 0 || slot > 1) throw Error("synthesise_host_submit: slot must be 0 or 1");
+  HostSlot& S = slots_[slot];
+  if (S.busy) throw Error("synthesise_host_submit: this slot still holds a batch; call mb200_synthesise_host_wait first");
+  if (L < 1 || L > T) throw Error("vocoder length L must be in [1, T]");
   const size_t n_mel = static_cast<size_t>(B) * 80 * T, n_mask = static_cast<size_t>(B) * T;
   const size_t n_spk = spks ? static_cast<size_t>(B) * (cfg.c_in - 160) : 0;
   const size_t n_out_mel = static_cast<size_t>(B) * 80 * L, n_wav = static_cast<size_t>(B) * 256 * L;
-  float* d_mu = static_cast<float*>(ensure(ws_io_[2], n_mel * 4));
-  float* d_z = static_cast<float*>(ensure(ws_io_[3], n_mel * 4));
-  float* d_mask = static_cast<float*>(ensure(ws_io_[4], n_mask * 4));
-  float* d_spk = spks ? static_cast<float*>(ensure(ws_io_[5], n_spk * 4)) : nullptr;
-  float* d_melo = static_cast<float*>(ensure(ws_io_[6], n_out_mel * 4));
-  float* d_wav = static_cast<float*>(ensure(ws_io_[7], n_wav * 4));
-  // A private NON-BLOCKING stream: the call neither serialises against the legacy default stream's implicit barriers nor
-  // stalls other streams of the process.  It is ordered after the plan's last asynchronous call (the workspaces' last user)
-  // and ends synchronous, so later calls on any stream are ordered after it by the host.
-  if (!host_stream_) MB_CUDA(cudaStreamCreateWithFlags(&host_stream_, cudaStreamNonBlocking));
-  cudaStream_t st = host_stream_;
-  if (busy_) MB_CUDA(cudaStreamWaitEvent(st, busy_, 0));
-  MB_CUDA(cudaMemcpyAsync(d_mu, mu, n_mel * 4, cudaMemcpyHostToDevice, st));
-  MB_CUDA(cudaMemcpyAsync(d_z, z, n_mel * 4, cudaMemcpyHostToDevice, st));
-  MB_CUDA(cudaMemcpyAsync(d_mask, mask, n_mask * 4, cudaMemcpyHostToDevice, st));
-  if (spks) MB_CUDA(cudaMemcpyAsync(d_spk, spks, n_spk * 4, cudaMemcpyHostToDevice, st));
-  // The mel read-back (9 MB at cfg2) overlaps the vocoder: it is issued on a non-blocking copy stream as soon as the
-  // decode + crop have finished, while HiFi-GAN runs on the compute stream.
-  if (!copy_stream_) {
+  // Private NON-BLOCKING streams: the call neither serialises against the legacy default stream's implicit barriers nor
+  // stalls other streams of the process.  upload -> compute -> copy, chained by events; the compute stream is also ordered
+  // after the plan's last asynchronous call on a caller's stream (the shared workspaces' last user).
+  if (!host_stream_) {
+    MB_CUDA(cudaStreamCreateWithFlags(&host_stream_, cudaStreamNonBlocking));
+    MB_CUDA(cudaStreamCreateWithFlags(&upload_stream_, cudaStreamNonBlocking));
     MB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
     MB_CUDA(cudaEventCreateWithFlags(&mel_ready_, cudaEventDisableTiming));
     for (auto& e : wav_ready_) MB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& sl : slots_)
+      for (cudaEvent_t* e : {&sl.uploaded, &sl.computed, &sl.copied}) MB_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   }
-  if (L < 1 || L > T) throw Error("vocoder length L must be in [1, T]");
+  // slot staging is private to the slot (not part of any cached program): plain grow-only device buffers
+  auto grow = [&](DevBuf& b, size_t bytes) -> float* {
+    if (b.bytes < bytes) {
+      if (b.p) { MB_CUDA(cudaDeviceSynchronize()); cudaFree(b.p); bytes_allocated -= static_cast<long long>(b.bytes); }
+      MB_CUDA(cudaMalloc(&b.p, bytes));
+      b.bytes = bytes;
+      bytes_allocated += static_cast<long long>(bytes);
+    }
+    return static_cast<float*>(b.p);
+  };
+  float* d_mu = grow(S.mu, n_mel * 4);
+  float* d_z = grow(S.z, n_mel * 4);
+  float* d_mask = grow(S.mask, n_mask * 4);
+  float* d_spk = spks ? grow(S.spk, n_spk * 4) : nullptr;
+  float* d_melo = grow(S.mel, n_out_mel * 4);
+  float* d_wav = grow(S.wav, n_wav * 4);
   float* dec = static_cast<float*>(ensure(ws_io_[1], n_mel * 4));
+  MB_CUDA(cudaMemcpyAsync(d_mu, mu, n_mel * 4, cudaMemcpyHostToDevice, upload_stream_));
+  MB_CUDA(cudaMemcpyAsync(d_z, z, n_mel * 4, cudaMemcpyHostToDevice, upload_stream_));
+  MB_CUDA(cudaMemcpyAsync(d_mask, mask, n_mask * 4, cudaMemcpyHostToDevice, upload_stream_));
+  if (spks) MB_CUDA(cudaMemcpyAsync(d_spk, spks, n_spk * 4, cudaMemcpyHostToDevice, upload_stream_));
+  MB_CUDA(cudaEventRecord(S.uploaded, upload_stream_));
+  cudaStream_t st = host_stream_;
+  MB_CUDA(cudaStreamWaitEvent(st, S.uploaded, 0));
+  if (busy_) MB_CUDA(cudaStreamWaitEvent(st, busy_, 0));
   cfm_decode(d_mu, d_mask, d_z, d_spk, B, T, n_steps, dec, st);
+  // The mel read-back (9 MB at cfg2) overlaps the vocoder: it is issued on the copy stream as soon as decode + crop are done.
   if (mel_out) {
     MB_CUDA(launch_affine_crop(dec, T, mel_std, mel_mean, d_melo, B, 80, L, st));
     launches += 1;
@@ -306,8 +329,18 @@ void Plan::synthesise_host(const float* mu, const float* mask, const float* z, c
     throw;
   }
   host_wav_dst_ = nullptr;
-  MB_CUDA(cudaStreamSynchronize(st));
-  MB_CUDA(cudaStreamSynchronize(copy_stream_));
+  MB_CUDA(cudaEventRecord(S.computed, st));
+  MB_CUDA(cudaEventRecord(S.copied, copy_stream_));
+  S.busy = true;
+}
+
+void Plan::synthesise_host_wait(int slot) {
+  if (slot < 0 || slot > 1) throw Error("synthesise_host_wait: slot must be 0 or 1");
+  HostSlot& S = slots_[slot];
+  if (!S.busy) throw Error("synthesise_host_wait: nothing was submitted in this slot");
+  MB_CUDA(cudaEventSynchronize(S.computed));
+  MB_CUDA(cudaEventSynchronize(S.copied));
+  S.busy = false;
 }
 
 }  // namespace mb

@@ -247,6 +247,11 @@ class MatchaTTS(nn.Module):
         self.decoder = CFM(in_channels=2 * nf, out_channel=nf, cfm_params=cfm, decoder_params=decoder, n_spks=n_spks,
                            spk_emb_dim=spk_emb_dim)
         self.update_data_statistics(data_statistics)
+        # Padded mel length = y_max rounded up to a multiple of this.  4 is the reference's (utils/model.py:14-20) and the
+        # default: padded frames are attended to and enter the GroupNorm statistics, so the padded
+        # length is part of the result.  A serving caller may set 32 or 64 to bound the number of distinct shapes (one
+        # CUDA graph each, at most kMaxCachedPrograms kept): results then equal the reference's run with that padding.
+        self.t_pad_multiple = 4
 
     def update_data_statistics(self, data_statistics):   # baselightningmodule.py:20-28
         if data_statistics is None:
@@ -263,7 +268,10 @@ class MatchaTTS(nn.Module):
         w_ceil = torch.ceil(torch.exp(logw) * x_mask) * length_scale
         y_lengths = torch.clamp_min(torch.sum(w_ceil, [1, 2]), 1).long()
         y_max_length = int(y_lengths.max())
-        mu_y, attn, y_mask = length_regulate(mu_x, w_ceil, x_mask, y_lengths, fix_len_compatibility(y_max_length))
+        t_pad = fix_len_compatibility(y_max_length)
+        if self.t_pad_multiple > 4:
+            t_pad = -(-t_pad // self.t_pad_multiple) * self.t_pad_multiple
+        mu_y, attn, y_mask = length_regulate(mu_x, w_ceil, x_mask, y_lengths, t_pad)
         encoder_outputs = mu_y[:, :, :y_max_length]
         decoder_outputs = self.decoder(mu_y, y_mask, n_timesteps, temperature, spks)[:, :, :y_max_length]
         seconds = (dt.datetime.now() - t0).total_seconds()

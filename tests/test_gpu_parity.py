@@ -352,3 +352,37 @@ def test_large_pre_groupnorm_activations_and_the_half_modes(scale, fp16_overflow
         assert not torch.isfinite(out["fp16"]).all()
     else:
         assert torch.isfinite(out["fp16"]).all() and rel_l2(out["fp16"], want) <= HALF_REL_L2
+
+
+def test_double_buffered_host_calls_equal_the_synchronous_call():
+    """mb200_synthesise_host_submit / _wait with two batches of DIFFERENT shapes in flight (uploads and read-backs of one
+    overlapping the compute of the other, several rounds so every slot is reused): same outputs as the synchronous call."""
+    g = torch.Generator().manual_seed(23)
+    plan = Plan("fp16", 160)
+    plan.load_estimator(weights.estimator_state_dict(160, seed=5))
+    plan.load_generator(weights.generator_state_dict(6))
+    cases = []
+    for (b, t_pad, lens) in [(5, 24, [24, 23, 9, 16, 24]), (2, 40, [40, 31]), (4, 24, [5, 24, 20, 11])]:
+        mu = torch.randn(b, 80, t_pad, generator=g).pin_memory()
+        z = (torch.randn(b, 80, t_pad, generator=g) * 0.667).pin_memory()
+        mask = weights.prefix_mask(lens, t_pad).contiguous().pin_memory()
+        length = max(lens) - 1
+        mel, wav = plan.synthesise_host(mu, mask, z, 2, length, -5.5, 2.1)
+        cases.append((mu, mask, z, length, mel.clone(), wav.clone()))
+    outs = []
+    for i in range(7):
+        mu, mask, z, length, _, _ = cases[i % 3]
+        if i >= 2:
+            plan.synthesise_host_wait(i % 2)
+        mel_o = torch.empty(mu.shape[0], 80, length).pin_memory()
+        wav_o = torch.empty(mu.shape[0], 1, 256 * length).pin_memory()
+        outs.append((mel_o, wav_o))
+        plan.synthesise_host_submit(mu, mask, z, 2, length, -5.5, 2.1, mel_o, wav_o, slot=i % 2)
+    with pytest.raises(RuntimeError, match="still holds a batch"):
+        plan.synthesise_host_submit(*cases[0][:3], 2, cases[0][3], -5.5, 2.1, outs[0][0], outs[0][1], slot=0)
+    plan.synthesise_host_wait(1)
+    plan.synthesise_host_wait(0)
+    for i, (mel_o, wav_o) in enumerate(outs):
+        assert torch.equal(mel_o, cases[i % 3][4]) and torch.equal(wav_o, cases[i % 3][5]), i
+    with pytest.raises(RuntimeError, match="nothing was submitted"):
+        plan.synthesise_host_wait(0)
