@@ -510,7 +510,7 @@ def run_train(args):
                act_fn="snakebeta")
     cfm = mb.CFM(160, 80, types.SimpleNamespace(solver="euler", sigma_min=1e-4), dec, precision="fp32")
     cfm.load_state_dict(weights.estimator_state_dict(160, seed=1234), strict=True)
-    cfm = cfm.to(dev).train()
+    cfm = cfm.to(dev).train()      # training mode: the transformer blocks' Dropout(0.05) is inside the timed step
     params = list(cfm.estimator.parameters())
     g = torch.Generator().manual_seed(1234 + rank)
     lengths = [int(v) for v in (torch.randint(64, 129, (b,), generator=g) * 4)]

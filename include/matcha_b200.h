@@ -143,6 +143,15 @@ typedef struct {
   float* grad;
 } mb200_param;
 
+/* Dropout of the estimator's transformer blocks for the mb200_compute_loss calls that follow (decoder.py:206 ->
+ * transformer.py:124 after the feed-forward activation, :200 -> Attention.to_out[1] after the attention out-projection;
+ * rate 0.05 in configs/model/decoder/default.yaml:2).  p = 0 (the default) is eval mode.  The keep mask of element i at site
+ * s = 2 * block + {0 attention, 1 feed-forward} (blocks in the order down 0, down 1, mid 0, mid 1, up 0, up 1; i indexes
+ * the (B, L, C) activation) is splitmix64(seed + 0x632BE59BD9B4E019 (s + 1) + i) >> 32 >= p * 2^32: reproducible from
+ * the seed, regenerated in the backward pass, and injectable into a reference run (tests/test_train_gpu.py).  It is not
+ * torch's Philox stream: draws differ from the reference's, their distribution does not. */
+int mb200_set_train_dropout(mb200_plan* plan, float p, unsigned long long seed);
+
 /* BASECFM.compute_loss(x1, mask, mu, spks) (matcha/models/components/flow_matching.py:87-118) with the random draws
  * injected: t (B,) ~ U(0,1) and z (B,80,T) ~ N(0,1) are device inputs.  Computes y = (1-(1-sigma_min) t) z + t x1,
  * u = x1 - (1-sigma_min) z, v = Decoder.forward(y, mask, mu, t, spks) (decoder.py:363-443, per-sample t) and

@@ -18,7 +18,7 @@ EXPORTS = [
     "mb200_last_error", "mb200_version", "mb200_plan_create", "mb200_plan_destroy", "mb200_load_estimator",
     "mb200_load_generator", "mb200_load_text_encoder", "mb200_text_encoder_forward", "mb200_euler_schedule", "mb200_estimator_forward", "mb200_cfm_decode",
     "mb200_hifigan_forward", "mb200_synthesise", "mb200_synthesise_host", "mb200_synthesise_host_submit", "mb200_synthesise_host_wait", "mb200_launch_count",
-    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_maximum_path", "mb200_maximum_path_workspace_bytes", "mb200_maximum_path_static", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
+    "mb200_workspace_bytes", "mb200_compute_loss", "mb200_set_train_dropout", "mb200_denoiser_bias", "mb200_denoise", "mb200_length_regulate", "mb200_maximum_path", "mb200_maximum_path_workspace_bytes", "mb200_maximum_path_static", "mb200_set_profiling", "mb200_get_profile", "mb200_test_conv1d", "mb200_test_attention", "mb200_debug_probe",
 ]
 
 
@@ -71,6 +71,7 @@ def load():
         lib.mb200_synthesise_host_wait.argtypes = [vp, i]
         lib.mb200_compute_loss.argtypes = [vp, ctypes.POINTER(Param), i, ctypes.c_char_p, vp, vp, vp, vp, vp, vp, i, i, f, i,
                                            vp, vp, vp, vp, vp, vp]
+        lib.mb200_set_train_dropout.argtypes = [vp, f, ctypes.c_ulonglong]
         lib.mb200_denoiser_bias.argtypes = [vp, vp, i, vp, vp]
         lib.mb200_denoise.argtypes = [vp, vp, i, i, vp, f, vp, vp]
         lib.mb200_length_regulate.argtypes = [vp, vp, vp, vp, i, i, i, i, vp, vp, vp, vp, vp]
@@ -332,6 +333,10 @@ class Plan:
     def synthesise_host_wait(self, slot=0):
         with torch.cuda.device(self.device):
             check(self.lib.mb200_synthesise_host_wait(self.handle, int(slot)))
+
+    def set_train_dropout(self, p, seed=0):
+        """Transformer-block dropout for the following compute_loss calls (0 = eval mode)."""
+        check(self.lib.mb200_set_train_dropout(self.handle, float(p), int(seed) & 0xFFFFFFFFFFFFFFFF))
 
     def compute_loss(self, named_params, x1, mask, mu, z, t, spks=None, sigma_min=1e-4, backward=True, want_dmu=False,
                      want_dspks=False):

@@ -99,6 +99,7 @@ class Decoder(nn.Module):
             raise NotImplementedError("matcha_b200 has kernels for the shipped decoder configuration only "
                                       "(configs/model/decoder/default.yaml); unsupported: " + ", ".join(unsupported))
         self.in_channels, self.out_channels, self.precision = in_channels, out_channels, precision
+        self.dropout = float(dropout)     # transformer-block dropout, active in .train() on the CUDA training path
         temb = channels[0] * 4
         tm = _Params()
         tm.linear_1 = nn.Linear(in_channels, temb)
@@ -242,6 +243,15 @@ class _ComputeLoss(torch.autograd.Function):
         nig = ctx.needs_input_grad          # (estimator, names, sigma_min, x1, mask, mu, spks, t, z, *params)
         need = bool(nig[5] or nig[6] or any(nig[9:]))
         plan = estimator.train_plan()
+        # decoder.py:206: the transformer blocks' dropout is active in training mode.  The seed comes from torch's generator,
+        # so torch.manual_seed makes a training run reproducible; `estimator.dropout_seed` (tests) overrides it.
+        if estimator.training and estimator.dropout > 0:
+            seed = getattr(estimator, "dropout_seed", None)
+            if seed is None:
+                seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            plan.set_train_dropout(estimator.dropout, seed)
+        else:
+            plan.set_train_dropout(0.0, 0)
         out = plan.compute_loss(zip(names, (p.detach() for p in params)), x1.detach(), mask, mu.detach(), z, t,
                                 None if spks is None else spks.detach(), sigma_min, backward=need,
                                 want_dmu=bool(nig[5]), want_dspks=bool(nig[6]))

@@ -261,6 +261,9 @@ int mb200_maximum_path_static(const float* value, const float* mask, int B, int 
     mb::maximum_path_static(value, mask, B, Tx, Ty, path, static_cast<cudaStream_t>(stream));
   });
 }
+int mb200_set_train_dropout(mb200_plan* plan, float p, unsigned long long seed) {
+  return guarded([&] { P(plan)->set_train_dropout(p, seed); });
+}
 int mb200_compute_loss(mb200_plan* plan, const mb200_param* params, int n, const char* prefix, const float* x1,
                        const float* mask, const float* mu, const float* z, const float* t, const float* spks, int B, int T,
                        float sigma_min, int backward, float* loss, float* y, float* v, float* dmu, float* dspks,

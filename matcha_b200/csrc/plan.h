@@ -162,6 +162,11 @@ class Plan {
   void load_text_encoder(const StateDict& sd, int n_heads);
   void text_encoder_forward(const long long* ids, const long long* lengths, const float* spks, int B, int Lx, float* mu_x,
                             float* logw, float* x_mask, cudaStream_t st);
+  // Dropout of the transformer blocks for the following compute_loss_grad calls (0 = eval mode, the default)
+  void set_train_dropout(float p, unsigned long long seed) {
+    if (!(p >= 0.f && p < 1.f)) throw Error("dropout rate must be in [0, 1)");
+    train_dropout_p_ = p; train_dropout_seed_ = seed;
+  }
   // HiFi-GAN bias denoiser (hifigan/denoiser.py:53-64): bias = |STFT(audio)|[:, 0] (513 bins); out (B, 256*(L/256))
   void denoiser_bias(const float* audio, int L, float* bias, cudaStream_t st);
   void denoise(const float* audio, int B, int L, const float* bias, float strength, float* out, cudaStream_t st);
@@ -249,6 +254,8 @@ class Plan {
   DevBuf ws_voc_[8];
   DevBuf ws_io_[8];
   unsigned long long use_clock_ = 0;
+  float train_dropout_p_ = 0.f;
+  unsigned long long train_dropout_seed_ = 0;
   cudaStream_t host_stream_ = nullptr;   // synthesise_host: private non-blocking compute stream (never the legacy default stream)
   cudaEvent_t busy_ = nullptr;           // recorded after every asynchronous call on the caller's stream: the workspaces'
                                          // last user, which the private stream waits for

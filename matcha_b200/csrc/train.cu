@@ -240,12 +240,21 @@ struct Engine {
   WS& w;
   int B, T, cin;
   const float* maskT;
+  float drop_p = 0.f;                   // transformer-block dropout (0 = eval): Plan::set_train_dropout
+  unsigned long long drop_seed = 0;
   const char* rn[6] = {"down_blocks.0.0", "down_blocks.1.0", "mid_blocks.0.0", "mid_blocks.1.0", "up_blocks.0.0", "up_blocks.1.0"};
   const char* tn[6] = {"down_blocks.0.1.0", "down_blocks.1.1.0", "mid_blocks.0.1.0", "mid_blocks.1.1.0", "up_blocks.0.1.0", "up_blocks.1.1.0"};
 
   void zero(float* p, size_t n) { if (cudaMemsetAsync(p, 0, n * 4, c.st) != cudaSuccess) throw Error("cudaMemsetAsync failed"); }
   void mul_mask(float* x, const float* mask, long rows, int N) {
     trn::mul_mask_kernel<<<blocks256(rows * N), 256, 0, c.st>>>(x, mask, rows, N); c.check(); c.launches++;
+  }
+  // site = 2 * transformer block + {0: after attn1.to_out (transformer.py:200 -> to_out.1), 1: after the FF activation (:124)}
+  void dropout(const float* in, float* out, long n, int site) {
+    if (drop_p <= 0.f) { if (in != out) MB_CUDA(cudaMemcpyAsync(out, in, n * 4, cudaMemcpyDeviceToDevice, c.st)); return; }
+    const unsigned int thresh = static_cast<unsigned int>(static_cast<double>(drop_p) * 4294967296.0);
+    trn::dropout_kernel<<<blocks256(n), 256, 0, c.st>>>(in, out, n, drop_seed, static_cast<unsigned int>(site), thresh, 1.f / (1.f - drop_p));
+    c.check(); c.launches++;
   }
   ConvSpec linear(const std::string& name, int in, int out, bool bias = true) {
     ConvSpec s = conv1d_spec(in, out, 1);
@@ -391,6 +400,7 @@ struct Engine {
     Part att{View{X.att, 128, L}, 0, 128};
     ConvSpec so = linear(p + "attn1.to_out.0", 128, 256);
     conv_forward(c, so, &att, 1, View{X.hid, 256, L}, B, L);
+    if (drop_p > 0.f) dropout(X.hid, X.hid, rows * 256, 2 * x);
     axpy_launch(X.hid, res, rows * 256);
     ln_fwd(X.hid, p + "norm3", X.ln3, rows);
     Part ln3{View{X.ln3, 256, L}, 0, 256};
@@ -398,6 +408,7 @@ struct Engine {
     conv_forward(c, f1, &ln3, 1, View{X.pre, 1024, L}, B, L);
     trn::snake_fwd_kernel<<<blocks256(rows * 1024), 256, 0, c.st>>>(X.pre, P.p(p + "ff.net.0.alpha"), P.p(p + "ff.net.0.beta"), X.ff, rows * 1024);
     c.check(); c.launches++;
+    if (drop_p > 0.f) dropout(X.ff, X.ff, rows * 1024, 2 * x + 1);   // X.ff = what ff.net.2 multiplies (and its wgrad reads)
     Part ff{View{X.ff, 1024, L}, 0, 1024};
     ConvSpec f2 = linear(p + "ff.net.2", 1024, 256);
     conv_forward(c, f2, &ff, 1, View{X.out, 256, L}, B, L);
@@ -417,6 +428,7 @@ struct Engine {
     zero(w.GFF, rows * 1024);
     Part dff{View{w.GFF, 1024, L}, 0, 1024};
     conv_dgrad(c, f2, &dff, 1, g, B, L);
+    if (drop_p > 0.f) dropout(w.GFF, w.GFF, rows * 1024, 2 * x + 1);
     trn::snake_bwd_kernel<<<static_cast<unsigned>((rows + 63) / 64), 256, 0, c.st>>>(w.GFF, X.pre, P.p(p + "ff.net.0.alpha"), P.p(p + "ff.net.0.beta"),
                                                                                   P.g(p + "ff.net.0.alpha"), P.g(p + "ff.net.0.beta"), rows);
     c.check(); c.launches++;
@@ -429,10 +441,12 @@ struct Engine {
     ln_bwd(w.TA, X.hid, p + "norm3", w.G, rows);                  // G = d hid (residual + LN path)
     Part att{View{X.att, 128, L}, 0, 128};
     ConvSpec so = linear(p + "attn1.to_out.0", 128, 256);
-    conv_wgrad(c, so, &att, 1, g, B, L);
+    View go = g;                                 // gradient at the out-projection's output: d hid through the dropout
+    if (drop_p > 0.f) { dropout(w.G, w.TA, rows * 256, 2 * x); go = View{w.TA, 256, L}; }   // TA is free here (consumed by ln_bwd above)
+    conv_wgrad(c, so, &att, 1, go, B, L);
     zero(w.GATT, rows * 128);
     Part datt{View{w.GATT, 128, L}, 0, 128};
-    conv_dgrad(c, so, &datt, 1, g, B, L);
+    conv_dgrad(c, so, &datt, 1, go, B, L);
     attention_bwd(X, L);
     Part ln1{View{X.ln1, 256, L}, 0, 256};
     zero(w.TA, rows * 256);
@@ -507,6 +521,8 @@ void Plan::compute_loss_grad(const std::map<std::string, std::pair<const float*,
   Params P;
   P.m = params;
   Engine e{Ctx{st}, P, w, B, T, cin, mask};
+  e.drop_p = train_dropout_p_;
+  e.drop_seed = train_dropout_seed_;
   Ctx& c = e.c;
   const int Th = T / 2;
   const long rT = static_cast<long>(B) * T, rH = rT / 2;

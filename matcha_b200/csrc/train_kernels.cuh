@@ -288,6 +288,23 @@ __global__ void fill_rows_kernel(float* __restrict__ Y, const float* __restrict_
   const int n = static_cast<int>(i % N);
   Y[r * ld + n] = bias ? bias[n] : 0.f;
 }
+// Dropout (decoder.py:206 -> transformer.py:124, :200; rate configs/model/decoder/default.yaml:2).  The keep decision of
+// element i at site s is a pure function of (seed, s, i): splitmix64(seed + K (s + 1) + i) >> 32 >= rate * 2^32, so the
+// backward pass regenerates the mask instead of storing it and a test can inject the same masks into the oracle.
+__host__ __device__ inline unsigned int dropout_bits(unsigned long long seed, unsigned int site, unsigned long long i) {
+  unsigned long long z = seed + 0x632BE59BD9B4E019ull * (site + 1ull) + i + 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return static_cast<unsigned int>(z >> 32);
+}
+// out[i] = in[i] * keep(i) / (1 - rate)   (in == out allowed)
+__global__ void dropout_kernel(const float* __restrict__ in, float* __restrict__ out, long n, unsigned long long seed,
+                               unsigned int site, unsigned int thresh, float inv_keep) {
+  const long i = blockIdx.x * 256L + threadIdx.x;
+  if (i >= n) return;
+  out[i] = dropout_bits(seed, site, static_cast<unsigned long long>(i)) >= thresh ? in[i] * inv_keep : 0.f;
+}
 // X[r][:] *= mask[r]
 __global__ void mul_mask_kernel(float* __restrict__ X, const float* __restrict__ mask, long rows, int N) {
   const long i = blockIdx.x * 256L + threadIdx.x;

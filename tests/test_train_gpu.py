@@ -80,6 +80,7 @@ def test_compute_loss_module_is_an_autograd_node():
     sd = weights.estimator_state_dict(160, seed=3)
     cfm = mb.CFM(160, 80, CFM_PARAMS, DEC, n_spks=1, spk_emb_dim=64).to(dev)
     cfm.load_state_dict(sd, strict=True)
+    cfm.eval()      # no dropout: the oracle below runs without it (training-mode dropout is pinned further down)
     x1, mask, mu, z, tt, _ = _case(2, 40, [40, 29], 160, 5)
     x1, mask, z, tt = x1.to(dev), mask.to(dev), z.to(dev), tt.to(dev)
     mu = mu.to(dev).requires_grad_(True)
@@ -146,3 +147,60 @@ def test_compute_loss_gradients_match_reference_golden(golden_dir, name):
     assert rel_l2(out["dmu"].cpu(), fx["dmu"]) <= GRAD_REL_L2
     if fx["spks"] is not None:
         assert rel_l2(out["dspks"].cpu(), fx["dspks"]) <= GRAD_REL_L2
+
+
+@pytest.mark.parametrize("b,t,lengths,c_in,p", [(2, 24, [24, 13], 160, 0.05), (3, 52, [52, 40, 7], 224, 0.3)])
+def test_training_dropout_matches_autograd_oracle_with_the_same_masks(b, t, lengths, c_in, p):
+    """Dropout of the transformer blocks in training mode (decoder.py:206 -> transformer.py:124, :200; rate 0.05 shipped).
+    The CUDA path draws its keep masks from a counter-based hash of (seed, site, element); the oracle applies the SAME masks
+    at the reference's two positions per block and differentiates with torch autograd: loss, velocity and every gradient
+    must agree at the fp32 bar.  (Which elements are dropped is this package's stream, not torch's Philox - as with any two
+    seeds of the reference; where, how often and how the survivors are scaled is the reference's.)"""
+    sd = weights.estimator_state_dict(c_in, seed=7)
+    x1, mask, mu, z, tt, spks = _case(b, t, lengths, c_in, 11)
+    seed = 987654321
+    sdo = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    mu_o = mu.clone().requires_grad_(True)
+    loss_o, _ = mo.compute_loss(sdo, x1, mask, mu_o, tt, z, spks, drop=(p, seed))
+    loss_o.backward()
+    loss_eval, _ = mo.compute_loss(sd, x1, mask, mu, tt, z, spks)
+
+    dev = torch.device("cuda")
+    plan = Plan("fp32", c_in, use_graph=False)
+    named = [(k[len("estimator."):], v.to(dev).contiguous()) for k, v in sd.items()]
+    plan.set_train_dropout(p, seed)
+    out = plan.compute_loss(named, x1, mask, mu, z, tt, spks, 1e-4, backward=True, want_dmu=True)
+    again = plan.compute_loss(named, x1, mask, mu, z, tt, spks, 1e-4, backward=True, want_dmu=True)
+    plan.set_train_dropout(0.0, 0)
+    ev = plan.compute_loss(named, x1, mask, mu, z, tt, spks, 1e-4, backward=False)
+    torch.cuda.synchronize()
+    assert abs(float(out["loss"]) - float(loss_o)) <= 1e-3 * max(1.0, abs(float(loss_o)))
+    assert abs(float(loss_o) - float(loss_eval)) > 1e-4                        # the masks did something
+    assert abs(float(ev["loss"]) - float(loss_eval)) <= 1e-3 * max(1.0, abs(float(loss_eval)))   # p = 0 is eval mode again
+    # same seed, same masks (the training kernels reduce with atomics, so two runs agree to rounding, not bit for bit)
+    assert abs(float(out["loss"]) - float(again["loss"])) <= 1e-6 * abs(float(out["loss"]))
+    worst = max(rel_l2(out["grads"][k[len("estimator."):]].cpu(), v.grad) for k, v in sdo.items())
+    assert worst <= GRAD_REL_L2, worst
+    assert rel_l2(out["dmu"].cpu(), mu_o.grad) <= GRAD_REL_L2
+
+
+def test_module_training_mode_applies_dropout_and_eval_does_not():
+    cfm = mb.CFM(160, 80, CFM_PARAMS, DEC, precision="fp32")
+    cfm.load_state_dict(weights.estimator_state_dict(160, seed=7), strict=True)
+    cfm = cfm.cuda()
+    x1, mask, mu, z, tt, _ = (None if v is None else v.cuda() for v in _case(2, 24, [24, 13], 160, 11))
+    assert cfm.estimator.dropout == 0.05
+    losses = {}
+    for mode in ("eval", "train_a", "train_a2", "train_b"):
+        cfm.train(mode != "eval")
+        cfm.estimator.dropout_seed = {"train_a": 1, "train_a2": 1, "train_b": 2}.get(mode)
+        loss, _ = cfm.compute_loss(x1, mask, mu, t=tt, z=z)
+        losses[mode] = float(loss)
+    close = lambda a, b: abs(a - b) <= 1e-6 * abs(a)      # noqa: E731  (atomics: equal to rounding)
+    assert close(losses["train_a"], losses["train_a2"])
+    assert not close(losses["train_a"], losses["train_b"]) and not close(losses["train_b"], losses["eval"])
+    cfm.estimator.dropout_seed = None        # seeds now come from torch's generator
+    cfm.train()
+    torch.manual_seed(5); l1 = float(cfm.compute_loss(x1, mask, mu, t=tt, z=z)[0])
+    torch.manual_seed(5); l2 = float(cfm.compute_loss(x1, mask, mu, t=tt, z=z)[0])
+    assert close(l1, l2)
