@@ -145,8 +145,8 @@ struct EpiParams {
   int mask_out;            // v *= mask
   // GroupNorm statistics of v, [B][8][2] = (sum, sum of squares) per 32-channel group over all T_out rows, in a FIXED
   // summation order (no float atomics): every warp stores the partial sums of its 32 rows in slot t/32 of stats_part
-  // ([B][8][stats_slots] float2, stats_slots = ceil(T_out / 32)) and bumps stats_cnt[b][g]; the warp that arrives last
-  // adds the slots in index order into stats_out and re-arms the counter (gn_stats_commit below).
+  // ([B][8][stats_slots] float2, stats_slots = ceil(T_out / 32)); the last CTA of the launch to finish (stats_cnt, ONE
+  // counter per launch) adds the slots in index order into stats_out (gn_stats_store / gn_stats_finish below).
   float* stats_out;
   float2* stats_part;
   int* stats_cnt;
@@ -218,15 +218,32 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-// One lane of a warp hands in the warp's partial GroupNorm sums over rows [32 slot, 32 slot + 32) of (b, group).
-// Run-to-run deterministic: which warp arrives last changes, what it computes does not.
-__device__ __forceinline__ void gn_stats_commit(const EpiParams& e, int b, int group, int slot, float s, float ss) {
-  const int bg = b * 8 + group;
-  float2* part = e.stats_part + static_cast<size_t>(bg) * e.stats_slots;
-  __stcg(part + slot, make_float2(s, ss));
+// GroupNorm statistics in a FIXED summation order, without float atomics (run-to-run deterministic):
+//  * gn_stats_store: one lane of a warp stores the warp's partial sums over rows [32 slot, 32 slot + 32) of (b, group) into
+//    its own slot - a plain store, nothing waits for it;
+//  * gn_stats_finish: at the end of the kernel every CTA bumps ONE per-launch counter; the CTA that arrives last adds the
+//    slots of every (b, group) in index order into stats_out and re-arms the counter.  Which CTA is last changes from run
+//    to run, what it computes does not.  (A first version committed per item with fence + atomic-with-return; the fence
+//    waited for the thread's output-tile stores each time: +8 us on a 20 us launch, profiles/r02_launch_list_summary.txt.)
+__device__ __forceinline__ void gn_stats_store(const EpiParams& e, int b, int group, int slot, float s, float ss) {
+  __stcg(e.stats_part + static_cast<size_t>(b * 8 + group) * e.stats_slots + slot, make_float2(s, ss));
+}
+// Called by ALL threads of the CTA (contains __syncthreads), after its last gn_stats_store.  s_last_p: one int of shared
+// memory the caller owns (the persistent kernel has no static shared memory to spare beside its 227 KB).
+// Measured per launch of the Block1D conv (ncu launch lists, cfg2): round 1's float atomics 19.7 us; fence + atomic per
+// item 28.2; this form 25.4; fencing right after a warp's last tile, or summing with 16-lane teams and a shuffle tree,
+// 29-30 (slower: kept simple).  Bit-identical runs cost about 0.7 ms of a 31.7 ms cfg2 step.
+__device__ __forceinline__ void gn_stats_publish() {}
+__device__ __forceinline__ void gn_stats_finish(const EpiParams& e, int B, unsigned n_ctas, int* s_last_p) {
+  volatile int& s_last = *s_last_p;
+  __threadfence();                    // every thread publishes its own stores (partial sums among them) device-wide ...
+  __syncthreads();                    // ... before the CTA checks in
+  if (threadIdx.x == 0) s_last = atomicAdd(e.stats_cnt, 1) == static_cast<int>(n_ctas) - 1;
+  __syncthreads();
+  if (!s_last) return;
   __threadfence();
-  if (atomicAdd(e.stats_cnt + bg, 1) == e.stats_slots - 1) {
-    __threadfence();
+  for (int bg = threadIdx.x; bg < B * 8; bg += blockDim.x) {
+    const float2* part = e.stats_part + static_cast<size_t>(bg) * e.stats_slots;
     float a = 0.f, q = 0.f;
     for (int i = 0; i < e.stats_slots; ++i) {
       const float2 p = __ldcg(part + i);
@@ -234,8 +251,8 @@ __device__ __forceinline__ void gn_stats_commit(const EpiParams& e, int b, int g
     }
     e.stats_out[bg * 2] = a;
     e.stats_out[bg * 2 + 1] = q;
-    e.stats_cnt[bg] = 0;
   }
+  if (threadIdx.x == 0) *e.stats_cnt = 0;
 }
 
 // Fused epilogue for one thread's 32-channel slice [n0, n0+32) of output row (b, t, phase).
@@ -319,7 +336,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& e, int b, int t,
     ss = warp_sum(ss);
     // all rows of a warp belong to the same batch element b (tiles never straddle batch elements); lane 0 holds the
     // warp's first row, a multiple of 32
-    if ((threadIdx.x & 31) == 0 && do_store && valid) gn_stats_commit(e, b, n0 >> 5, t >> 5, s, ss);
+    if ((threadIdx.x & 31) == 0 && do_store && valid) gn_stats_store(e, b, n0 >> 5, t >> 5, s, ss);
   }
   if (!valid) return;
   if (e.x_state) {

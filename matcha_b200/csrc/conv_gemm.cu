@@ -142,6 +142,9 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_con
   }
   tc_fence_before();
   __syncthreads();
+  __shared__ int stats_last;
+  if (e.stats_out && (threadIdx.x & 31) == 0) gn_stats_publish();
+  if (e.stats_out) gn_stats_finish(e, g.B, gridDim.x * gridDim.y * gridDim.z, &stats_last);   // ordered GroupNorm sums by the last CTA
   if (warp == 1) tmem_dealloc<(NTILE < 32 ? 32 : NTILE)>(tmem_base);
 }
 
@@ -241,6 +244,9 @@ conv_gemm_simt_kernel(const T* __restrict__ a0, const T* __restrict__ a1, const 
   const int t = t0 + row;
   const int n0 = n_tile * 64 + half * 32;
   if (n0 < g.N) epilogue_chunk<T>(e, b, t, phase, n0, t < g.T_out, true, acc);  // n0 is warp-uniform
+  __shared__ int stats_last;
+  if (e.stats_out && (threadIdx.x & 31) == 0) gn_stats_publish();
+  if (e.stats_out) gn_stats_finish(e, g.B, gridDim.x * gridDim.y * gridDim.z, &stats_last);   // ordered GroupNorm sums by the last CTA
 }
 
 template <typename T>

@@ -265,11 +265,17 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       if (lane == 0) mbar_arrive(&t_empty[slot]);
       if (++slot == NACC) { slot = 0; tph ^= 1; }
     }
+    if constexpr ((F & kF_STATS) != 0) {
+      if (e.stats_out && lane == 0) gn_stats_publish();   // this lane stored the warp's partial GroupNorm sums
+    }
     if (warp == 2) { MB_TEND(2); }
     if (warp == 6) { MB_TEND(3); }
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr ((F & kF_STATS) != 0) {
+    if (e.stats_out) gn_stats_finish(e, g.B, gridDim.x, reinterpret_cast<int*>(tmem_slot + 1));   // ordered GroupNorm sums by the last CTA to get here
+  }
 #ifdef MB200_PROBE
   if (threadIdx.x == 0 && g.dbg_out) { g.dbg_out[blockIdx.x * 16 + 8] = clock64() - probe_k0; g.dbg_out[blockIdx.x * 16 + 9] = probe_k1 - probe_k0; }
 #endif

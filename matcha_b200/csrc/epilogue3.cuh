@@ -413,7 +413,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
       }
       sm = warp_sum(sm);
       ss = warp_sum(ss);
-      if (lane == 0) gn_stats_commit(e, b, (nbase + c * 32) >> 5, (t0 + 128 * i + lane_grp * 32) >> 5, sm, ss);
+      if (lane == 0) gn_stats_store(e, b, (nbase + c * 32) >> 5, (t0 + 128 * i + lane_grp * 32) >> 5, sm, ss);
     }
     if (e.x_state) {     // Euler update of the fp32 state; the stored copy below is x * mask
       const int ld = e.x_ld;

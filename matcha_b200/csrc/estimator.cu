@@ -112,8 +112,9 @@ void Plan::estimator_buffers(int B, int T) {
   ensure(ws_est_[MASK_T], rows * 4);
   ensure(ws_est_[MASK_H], rows / 2 * 4);
   ensure(ws_est_[SPK], static_cast<size_t>(B) * 64 * 4);
-  // GroupNorm statistics of the 13 Block1D convs: final sums, per-32-row partial sums and arrival counters (conv.cuh,
-  // gn_stats_commit).  The counters start at zero (ensure() clears new allocations) and every launch re-arms them.
+  // GroupNorm statistics of the 13 Block1D convs: final sums, per-32-row partial sums and one arrival counter per conv
+  // (conv.cuh, gn_stats_store / gn_stats_finish).  The counters start at zero (ensure() clears new allocations) and every
+  // launch re-arms its own.
   ensure(ws_est_[STATS], static_cast<size_t>(13) * B * 16 * 4);
   ensure(ws_est_[STATS_PART], static_cast<size_t>(13) * B * 8 * ((T + 31) / 32) * 8);
   ensure(ws_est_[STATS_CNT], static_cast<size_t>(13) * B * 8 * 4);

@@ -13,7 +13,7 @@ import re
 import sys
 
 TENSOR = "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"
-GEMM_FAMILY = ("conv_gemm_umma2_kernel", "resblock_pair_kernel", "ff_fused_kernel", "resqkv_fused_kernel")
+GEMM_FAMILY = ("conv_gemm_umma2_kernel", "resblock_pair_kernel", "ff_fused_kernel", "resqkv_fused_kernel")   # attention_umma_kernel is reported on its own line
 
 
 def short(name):

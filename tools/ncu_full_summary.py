@@ -34,7 +34,7 @@ stalls = [c for c in src[h] if c.startswith("stall_") and "Not Issued" not in c]
 tot = collections.Counter()
 lines = []
 for r in src[h + 1:]:
-    if len(r) < len(cols):
+    if len(r) < len(cols) or not r[cols["# Samples"]].isdigit():   # a report with several launches repeats the header row
         continue
     n = int(r[cols["# Samples"]])
     lines.append((n, r[cols["Source"]].strip()))
