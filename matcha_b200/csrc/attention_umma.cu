@@ -31,6 +31,7 @@ namespace mb {
 
 namespace {
 constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
 constexpr int kKvStages = 3;
 constexpr float kRaise = 12.f;   // the running maximum is raised only when a tile exceeds it by more than this (log2 units)
 constexpr int kTile = 16384;                            // 128 rows x 128 bytes
@@ -85,8 +86,13 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __restrict__ mask, T* __restrict__ out,
                       const int B, const int L, long long* __restrict__ dbg) {
   // developer probe (MB200_ATTN_DBG): cumulative clock64 cycles per phase of softmax warp 2 and of the issuer, CTA 0
+#ifdef MB200_PROBE   // MB200_PROBE_BUILD=1 builds only: the counters cost 22 registers and the hot loop has none to spare
 #define AT_T0() long long at_last = clock64(), at_acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}
 #define AT_MARK(k) do { if (dbg) { const long long at_now = clock64(); at_acc[k] += at_now - at_last; at_last = at_now; } } while (0)
+#else
+#define AT_T0() do {} while (0)
+#define AT_MARK(k) do {} while (0)
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
@@ -228,7 +234,9 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
       if (nw == 2) base[1] += nkt;
       kc += nkt;
     }
+#ifdef MB200_PROBE
     if (dbg && blockIdx.x == 0 && lane == 0) { for (int k = 0; k < 10; ++k) dbg[16 + k] = at_acc[k]; }
+#endif
   } else {
     // ================================================================= softmax warpgroups (one query row per thread)
     const int w = (warp - 2) >> 2;
@@ -258,7 +266,8 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
       for (int j = 0; j < nkt; ++j, ++nt) {
         AT_MARK(9);
         // uniform = every key of the tile exists and carries the same bias (always, except at most two tiles of a
-        // prefix-masked utterance): the bias then folds into the exponent's additive constant
+        // prefix-masked utterance): the bias then folds into the exponent's additive constant.  Any other tile is MADE
+        // uniform first: its scores are rewritten in TMEM with each key's bias difference folded in (see below).
         float bcur[4] = {mkb[0] * kLog2e, mkb[1] * kLog2e, mkb[2] * kLog2e, mkb[3] * kLog2e};
         const float bias_u = __shfl_sync(0xffffffffu, bcur[0], 0);
         const bool uni = __all_sync(0xffffffffu, bcur[0] == bias_u && bcur[1] == bias_u && bcur[2] == bias_u && bcur[3] == bias_u);
@@ -269,14 +278,30 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
         tc_fence_after();
         uint32_t pk[64];
         float part[2] = {0.f, 0.f};                   // this tile's contribution to the row sum
-        bool redo = !uni;
+        if (!uni) {
+          // Irregular tile (a mask edge, or the keys run out): S[k] += (bias[k] - bias[key 0]) in place, -inf for a key that
+          // does not exist, 32-key chunk by chunk and only where a chunk needs it.  One tcgen05.ld / st round trip per
+          // chunk (~150 cycles) instead of a separate slow path through the whole tile.
+          float sv[32];
+          for (int ch = 0; ch < 4; ++ch) {
+            const float mine = ch == 0 ? bcur[0] : ch == 1 ? bcur[1] : ch == 2 ? bcur[2] : bcur[3];   // log2 domain
+            if (__all_sync(0xffffffffu, mine == bias_u)) continue;
+            tmem_ld_32x32(t_s + 32 * ch, sv);
+            tmem_ld_wait_on(sv);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) sv[i] = fmaf(__shfl_sync(0xffffffffu, mine, i) - bias_u, kLn2, sv[i]);
+            tmem_st_32x32(t_s + 32 * ch, sv);
+          }
+          tmem_st_wait();
+        }
+        bool redo = false;
         bool waited = j == 0;                         // nothing of this item is in flight on P_w / O_w at its first tile
         auto signal_s_read = [&]() {                  // S_w is out of TMEM: the issuer may overwrite it with the next tile's
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&s_read[w]);
         };
-        if (uni) {
+        {
           // ---- ONE streaming pass with the running maximum of the previous tiles (first tile: of its first 32 keys)
           float m0 = -INFINITY, m1 = -INFINITY;
           float sa[32], sb[32];
@@ -318,9 +343,8 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
         }
         AT_MARK(2);
         if (redo) {
-          // ---- two passes over S (it stays in TMEM): non-uniform mask over the key tile, or a raised maximum
-          auto two_pass = [&](auto uni_tag) {
-            constexpr bool kUni = decltype(uni_tag)::value;
+          // ---- two passes over S (it stays in TMEM): the running maximum has to be raised before this tile's exponentials
+          {
             float sv[32];
             float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
@@ -329,9 +353,7 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
               tmem_ld_wait_on(sv);
 #pragma unroll
               for (int i = 0; i < 32; ++i) {
-                float bk = bias_u;
-                if constexpr (!kUni) bk = __shfl_sync(0xffffffffu, bcur[ch], i);
-                const float x = fmaf(sv[i], kLog2e, bk);
+                const float x = fmaf(sv[i], kLog2e, bias_u);
                 if (i & 1) m1 = fmaxf(m1, x); else m0 = fmaxf(m0, x);
               }
             }
@@ -366,15 +388,13 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
               if (ch == 3) signal_s_read();
 #pragma unroll
               for (int i = 0; i < 16; ++i) {
-                float b0 = bias_u, b1 = bias_u;
-                if constexpr (!kUni) { b0 = __shfl_sync(0xffffffffu, bcur[ch], 2 * i); b1 = __shfl_sync(0xffffffffu, bcur[ch], 2 * i + 1); }
-                const float p0 = ex2_ftz(fmaf(sv[2 * i], kLog2e, b0 - m_used)), p1 = ex2_ftz(fmaf(sv[2 * i + 1], kLog2e, b1 - m_used));
+                const float cr = bias_u - m_used;
+                const float p0 = ex2_ftz(fmaf(sv[2 * i], kLog2e, cr)), p1 = ex2_ftz(fmaf(sv[2 * i + 1], kLog2e, cr));
                 part[i & 1] += p0 + p1;
                 pk[ch * 16 + i] = pack2<T>(p0, p1);
               }
             }
-          };
-          if (uni) two_pass(std::true_type{}); else two_pass(std::false_type{});
+          }
         }
         AT_MARK(3);
         l2[0] += part[0]; l2[1] += part[1];
@@ -412,7 +432,9 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const float* __
       tc_fence_before();
     }
     AT_MARK(9);
+#ifdef MB200_PROBE
     if (dbg && blockIdx.x == 0 && warp == 2 && lane == 0) { for (int k = 0; k < 10; ++k) dbg[k] = at_acc[k]; }
+#endif
   }
 #undef AT_T0
 #undef AT_MARK

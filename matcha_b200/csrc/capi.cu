@@ -102,8 +102,23 @@ void Plan::test_attention(const float* qkv, const float* mask, int B, int T, flo
   MB_CUDA(cudaMemcpy(h.data(), qkv, n_in * 4, cudaMemcpyDeviceToHost));
   void* q = upload_operand(h);
   void* o = dalloc(n_out * esize(dtype));
-  MB_CUDA(attention_op(q, mask, o, B, T)(st));
+  Launch aop = attention_op(q, mask, o, B, T);
+  MB_CUDA(aop(st));
   MB_CUDA(cudaStreamSynchronize(st));
+  if (const char* v = std::getenv("MB200_PROBE")) {       // developer probe: time repeated launches of this op
+    const int reps = std::max(1, std::atoi(v));
+    cudaEvent_t e0, e1;
+    MB_CUDA(cudaEventCreate(&e0)); MB_CUDA(cudaEventCreate(&e1));
+    MB_CUDA(cudaEventRecord(e0, st));
+    for (int r = 0; r < reps; ++r) MB_CUDA(aop(st));
+    MB_CUDA(cudaEventRecord(e1, st));
+    MB_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    MB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    std::fprintf(stderr, "[probe] attention B=%d L=%d: %.1f us/launch, %.1f TFLOP/s\n", B, T, 1e3 * ms / reps,
+                 aop.flops * reps / (ms * 1e9));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+  }
   if (dtype == MB200_F32) {
     MB_CUDA(cudaMemcpy(out, o, n_out * 4, cudaMemcpyDeviceToDevice));
   } else {

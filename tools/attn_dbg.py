@@ -1,4 +1,4 @@
-"""Per-phase cycle counters of the tcgen05 attention kernel (MB200_ATTN_DBG=1), CTA 0, one launch at B=16, L given.
+"""Per-phase cycle counters of the tcgen05 attention kernel (MB200_ATTN_DBG=1), CTA 0, one launch at B=16, L given.  Needs a MB200_PROBE_BUILD=1 build of the library.
 softmax warp 2 (query tile 0): [mask vote, wait S, streaming pass, two-pass redo, wait PV, store+arrive, -, -, -, item epilogue]
 issuer: [item set-up, polling loop]"""
 import os
