@@ -57,6 +57,7 @@ void Plan::test_conv1d(const float* x, const float* w, const float* bias, int B,
       if (std::atoi(v) > 1) { e.out0 = dalloc(static_cast<size_t>(B) * T_o * W.N * es); e.out0_f32 = 0; }
     }
   }
+  reserve_split(static_cast<size_t>(B) * T * cpad);
   Launch op = conv_op(W, Src{xa, view_ld, transposed || stride == 1 ? cpad : Cin, view_rows}, nullptr, B, T_out, e);
   MB_CUDA(op(st));
   if (const char* v = std::getenv("MB200_PROBE")) {       // developer probe: time repeated launches of this op
@@ -79,7 +80,8 @@ void Plan::test_conv1d(const float* x, const float* w, const float* bias, int B,
       for (int cta : {0, 147}) {
         std::fprintf(stderr, "  [cta %3d]", cta);
         for (int r = 0; r < 5; ++r) std::fprintf(stderr, " %s %lld/%lld", names[r], h[cta * 16 + 2 * r], h[cta * 16 + 2 * r + 1]);
-        std::fprintf(stderr, "  (role: cycles total/in waits; kernel: total/setup)\n");
+        std::fprintf(stderr, "  (role: cycles total/in waits; kernel: total/setup)\n      epilogue w2 phases: header %lld, tmem %lld, staging %lld, arithmetic %lld, stores %lld\n", h[cta * 16 + 10],
+                     h[cta * 16 + 11], h[cta * 16 + 12], h[cta * 16 + 13], h[cta * 16 + 14]);
       }
     }
   }

@@ -33,8 +33,8 @@ struct ConvGeom {
 // Geometry of the persistent kernel (conv_gemm2.cu).  The K loop is organised in A-load GROUPS: one group = one source
 // view and channel base; for each K chunk of a group the A tile is loaded ONCE with a halo (128 + 8*extra rows) and
 // every tap of the group reuses it through a row-shifted shared-memory descriptor.
-constexpr int kMaxGroups = 4;
-constexpr int kMaxSched = 192;
+constexpr int kMaxGroups = 6;   // 2 sources x 2 channel bases, or 3 split-precision products x 2 bases
+constexpr int kMaxSched = 512;
 constexpr uint32_t kSchedNull = 1u << 27;    // padding entry: the issuer handles two entries per iteration
 constexpr uint32_t kSchedWFirst = 1u << 28;  // first tap of a streamed weight stage: wait for it
 constexpr uint32_t kSchedWLast = 1u << 29;   // last tap of a streamed weight stage: release it
@@ -157,6 +157,9 @@ struct EpiParams {
   void* out1;  int out1_ld;  float out1_slope;                  // second store (operand dtype), LeakyReLU(slope)
   // LayerNorm of the finished row (needs the whole row in one tile: N == 256) -> ln_out (operand dtype)
   void* ln_out;  int ln_ld;  const float* ln_g;  const float* ln_b;
+  // Split-precision fp32 mode (bf16 hi/lo operands, fp32 everything else): EVERY activation stream of the epilogue
+  // (gn_raw, resid, resid2, out0, out1, ln_out) is fp32, whatever the kernel's operand type T is.
+  int all_f32;
 };
 
 template <typename T> struct Elem;

@@ -20,11 +20,13 @@ namespace mb {
 #define MB_DBG(bit) (g.dbg & (bit))
 // cycle accounting of one role: total loop time and time spent inside barrier waits
 #define MB_T0() const long long probe_t0 = clock64(); long long probe_w = 0
+#define MB_T0E() const long long probe_t0 = clock64(); long long probe_e[6] = {0, 0, 0, 0, 0, 0}; long long& probe_w = probe_e[0]
 #define MB_WAIT(stmt) do { const long long probe_a = clock64(); stmt; probe_w += clock64() - probe_a; } while (0)
 #define MB_TEND(slot) do { if (lane == 0 && g.dbg_out) { g.dbg_out[blockIdx.x * 16 + 2 * (slot)] = clock64() - probe_t0; g.dbg_out[blockIdx.x * 16 + 2 * (slot) + 1] = probe_w; } } while (0)
 #else
 #define MB_DBG(bit) false
 #define MB_T0()
+#define MB_T0E()
 #define MB_WAIT(stmt) stmt
 #define MB_TEND(slot)
 #endif
@@ -243,7 +245,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     griddep_wait();
     int slot = 0, it = 0;
     uint32_t tph = 0;
-    MB_T0();
+    MB_T0E();
     for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++it) {
       const int nn = tile % np, mm = tile / np;
       const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
@@ -254,7 +256,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
         MB_WAIT(mbar_wait(&t_full[slot], tph));
       } else {
         epilogue_tile3<NTILE, MB, EG, T, F>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
-                                 lane_grp, grp, &t_full[slot], tph, &probe_w);
+                                 lane_grp, grp, &t_full[slot], tph, probe_e);
       }
 #else
       epilogue_tile3<NTILE, MB, EG, T, F>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
@@ -269,6 +271,9 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       if (e.stats_out && lane == 0) gn_stats_publish();   // this lane stored the warp's partial GroupNorm sums
     }
     if (warp == 2) { MB_TEND(2); }
+#ifdef MB200_PROBE
+    if (warp == 2 && lane == 0 && g.dbg_out) { for (int k = 1; k < 6; ++k) g.dbg_out[blockIdx.x * 16 + 9 + k] = probe_e[k]; }
+#endif
     if (warp == 6) { MB_TEND(3); }
   }
   tc_fence_before();

@@ -2,6 +2,7 @@
 // boundary layout changes (B,C,T) <-> [B][T][C], estimator input packing, timestep embedding, vocoder head.
 // All are one pass, 16-byte vector accesses along the contiguous channel axis.
 #include <math.h>
+#include <algorithm>
 
 #include "conv.cuh"
 #include "launch.h"
@@ -333,5 +334,43 @@ template cudaError_t launch_conv_post<float>(const float*, const float*, float, 
 template cudaError_t launch_conv_post<__nv_bfloat16>(const __nv_bfloat16*, const float*, float, float*, int, long,
                                                      cudaStream_t);
 template cudaError_t launch_conv_post<__half>(const __half*, const float*, float, float*, int, long, cudaStream_t);
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Split-precision fp32 mode: x (fp32) -> hi = bf16(x), lo = bf16(x - hi), so that x = hi + lo to 16 mantissa bits and
+// a . w ~= a_hi w_hi + a_hi w_lo + a_lo w_hi runs as three bf16 tcgen05 products with fp32 accumulation (conv_op).
+// Up to two sources ([rows][ld0], [rows][ld1], the first c0 / c1 columns of each) are written side by side into rows of
+// c0 + c1 columns: the concat of a skip connection costs nothing extra.
+__global__ void split_bf16x2_kernel(const float* __restrict__ s0, int ld0, int c0, const float* __restrict__ s1, int ld1,
+                                    int c1, long rows, __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+  const int per_row = (c0 + c1) >> 3;   // 8-column units per output row
+  const long total = rows * per_row;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const long r = i / per_row;
+    const int c = static_cast<int>(i - r * per_row) << 3;
+    const float* src = c < c0 ? s0 + r * ld0 + c : s1 + r * ld1 + (c - c0);
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+    const float x[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    __nv_bfloat162 h[4], l[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const __nv_bfloat16 h0 = __float2bfloat16_rn(x[2 * k]), h1 = __float2bfloat16_rn(x[2 * k + 1]);
+      h[k] = __halves2bfloat162(h0, h1);
+      l[k] = __floats2bfloat162_rn(x[2 * k] - __bfloat162float(h0), x[2 * k + 1] - __bfloat162float(h1));
+    }
+    const long o = r * (c0 + c1) + c;
+    *reinterpret_cast<uint4*>(hi + o) = *reinterpret_cast<const uint4*>(h);
+    *reinterpret_cast<uint4*>(lo + o) = *reinterpret_cast<const uint4*>(l);
+  }
+}
+
+cudaError_t launch_split_bf16x2(const float* s0, int ld0, int c0, const float* s1, int ld1, int c1, long rows,
+                                void* hi, void* lo, cudaStream_t st) {
+  if ((c0 | c1 | ld0 | ld1) & 7) return cudaErrorInvalidValue;
+  const long total = rows * ((c0 + c1) >> 3);
+  const int grid = static_cast<int>(std::min<long>((total + 255) / 256, 148L * 16));
+  split_bf16x2_kernel<<<std::max(grid, 1), 256, 0, st>>>(s0, ld0, c0, s1, ld1, c1, rows, static_cast<__nv_bfloat16*>(hi),
+                                                         static_cast<__nv_bfloat16*>(lo));
+  return cudaGetLastError();
+}
 
 }  // namespace mb

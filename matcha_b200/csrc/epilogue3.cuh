@@ -44,7 +44,7 @@ __host__ inline uint32_t epi_features(const EpiParams& e) {
   if (e.ln_out) f |= kF_LN;
   if (e.out1) f |= kF_OUT1 | kF_SLOPE;
   if (e.scale != 1.f) f |= kF_SCALE;
-  if (e.out0_f32 || e.resid_f32 || e.resid2_f32) f |= kF_F32;
+  if (e.out0_f32 || e.resid_f32 || e.resid2_f32 || e.all_f32) f |= kF_F32;
   if (e.out0_slope != 1.f) f |= kF_SLOPE;
   return f;
 }
@@ -126,6 +126,11 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 // The profile of this function is flat and latency-bound (two epilogue warps per scheduler), so the code is organised
 // to keep the instruction count per 32x32 item low: options are tested once per item (feature-major, row-minor loops),
 // row offsets are 32-bit element indices computed once, and memory operations are predicated rather than branched.
+#ifdef MB200_PROBE   // probe_wait[0] = wait for the accumulator; [1..5] = item header, TMEM load, staging, arithmetic, stores
+#define EP_MARK(k) do { if (probe_wait) { const long long ep_now = clock64(); probe_wait[k] += ep_now - ep_last; ep_last = ep_now; } } while (0)
+#else
+#define EP_MARK(k) do {} while (0)
+#endif
 template <int NTILE, int MB, int EG, typename T, uint32_t F = kF_ALL>
 __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b, const int t0, const int T_out,
                                                const int phase, const int nbase, const uint32_t tmem_tile,
@@ -146,13 +151,15 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
   if constexpr (!(F & kF_LN)) e.ln_out = nullptr;
   if constexpr (!(F & kF_OUT1)) e.out1 = nullptr;
   if constexpr (!(F & kF_SCALE)) e.scale = 1.f;
-  if constexpr (!(F & kF_F32)) { e.out0_f32 = 0; e.resid_f32 = 0; e.resid2_f32 = 0; }
+  if constexpr (!(F & kF_F32)) { e.out0_f32 = 0; e.resid_f32 = 0; e.resid2_f32 = 0; e.all_f32 = 0; }
+  if (e.all_f32) { e.out0_f32 = 1; e.resid_f32 = 1; e.resid2_f32 = 1; }
+  const int af = e.all_f32;
   if constexpr (!(F & kF_SLOPE)) e.out0_slope = 1.f;
   const int p = lane & 3, rq = lane >> 2;
   const int row_base = b * e.T_o + phase * e.o_phase_step;   // tensors on this path stay below 2^31 elements
   const int tw0 = t0 + lane_grp * 32 + rq;  // this lane's first row of block 0
   // stream A = the first half-precision input stream; it is requested one item ahead
-  const T* inA = reinterpret_cast<const T*>(e.gn_raw ? e.gn_raw : (e.resid_f32 ? nullptr : e.resid));
+  const T* inA = af ? nullptr : reinterpret_cast<const T*>(e.gn_raw ? e.gn_raw : (e.resid_f32 ? nullptr : e.resid));
   const int ldA = e.gn_raw ? e.gn_ld : e.resid_ld;
   const bool resid_is_A = (e.gn_raw == nullptr) && (inA != nullptr);
   const int n_valid = e.n_valid, o_mul = e.o_mul;
@@ -179,6 +186,9 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
     mbar_wait(t_full, t_parity);
   }
   tc_fence_after();
+#ifdef MB200_PROBE
+  long long ep_last = clock64();
+#endif
 
   const bool do_ln = (NTILE == 256) && (e.ln_out != nullptr);
   // fp16 layers whose epilogue is only bias / residuals / scale / LeakyReLU (every HiFi-GAN conv) finish in packed half
@@ -221,10 +231,12 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
 
     // ---- accumulators: TMEM -> registers (row per lane) -> staging -> coalesced layout
     float v[4][8];
+    EP_MARK(1);
     {
       float acc[32];
       tmem_ld_32x32(tmem_tile + i * NTILE + c * 32, acc);
       tmem_ld_wait();
+      EP_MARK(2);
       float4* srow = reinterpret_cast<float4*>(stg + lane * kStagePitch);
 #pragma unroll
       for (int j = 0; j < 8; ++j) srow[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
@@ -238,6 +250,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
       }
       __syncwarp();
     }
+    EP_MARK(3);
     if (fast) {
       // ---- packed-half path: bias + residual(s) + scale + LeakyReLU copies, two channels per instruction
       if constexpr (std::is_same<T, __half>::value) {
@@ -343,7 +356,13 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         float r[8];
-        unpack8<T>(cur[k], r);
+        if (af) {
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) r[ch] = 0.f;
+          if (ok[k]) load8<T>(e.gn_raw, static_cast<long>(grow[k]) * e.gn_ld + n0, 1, r);
+        } else {
+          unpack8<T>(cur[k], r);
+        }
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) v[k][ch] += mish_fast(fmaf(r[ch], pa[ch], pb[ch])) * m[k];
       }
@@ -437,6 +456,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) { ln_s[k] += v[k][ch]; ln_ss[k] = fmaf(v[k][ch], v[k][ch], ln_ss[k]); }
     }
+    EP_MARK(4);
     if (e.out0) {
       const int ld = e.out0_ld, f32 = e.out0_f32;
       const float sl = e.out0_slope;
@@ -462,9 +482,10 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
         float o[8];
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) o[ch] = fmaxf(v[k][ch], v[k][ch] * sl);
-        if (ok[k]) store8<T>(e.out1, static_cast<long>(grow[k]) * ld + n0, 0, o);
+        if (ok[k]) store8<T>(e.out1, static_cast<long>(grow[k]) * ld + n0, af, o);
       }
     }
+    EP_MARK(5);
   }
 
   if (do_ln) {
@@ -503,10 +524,10 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
         if (t < T_out) {
           const long row = row_base + t * o_mul;
           float x[8];
-          load8<T>(e.out0, row * e.out0_ld + n0, 0, x);
+          load8<T>(e.out0, row * e.out0_ld + n0, af, x);
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) x[ch] = fmaf((x[ch] - mean[k]) * rstd[k], ga[ch], be[ch]);
-          store8<T>(e.ln_out, row * e.ln_ld + n0, 0, x);
+          store8<T>(e.ln_out, row * e.ln_ld + n0, af, x);
         }
       }
     }

@@ -102,6 +102,7 @@ void Plan::estimator_buffers(int B, int T) {
   const size_t rows = static_cast<size_t>(B) * T;
   const int cpad = (cfg.c_in + 63) / 64 * 64;
   ensure(ws_est_[XIN], rows * cpad * es);
+  reserve_split(rows * 1024);          // widest conv input: the feed-forward down projection (1024 channels)
   for (int b : {RAW, H1, RAW2, RES, LN, HID, YA, YB, SKIP0}) ensure(ws_est_[b], rows * 256 * es);
   ensure(ws_est_[SKIP1], rows / 2 * 256 * es);
   ensure(ws_est_[QKV], rows * 384 * es);

@@ -69,6 +69,8 @@ cudaError_t launch_gn_mish(const T* raw, const float* stats, const float* gamma,
                            int tadd_bstride, const float* mask, T* out, int B, int Tn, cudaStream_t st);
 template <typename T>
 cudaError_t launch_layernorm(const T* in, const float* g, const float* b, T* out, long rows, cudaStream_t st);
+cudaError_t launch_split_bf16x2(const float* s0, int ld0, int c0, const float* s1, int ld1, int c1, long rows, void* hi, void* lo,
+                                cudaStream_t st);   // fp32 -> bf16 hi / lo (split-precision fp32 mode), optional concat
 cudaError_t launch_bct_to_btc(const float* in, float* out, int B, int C, int Tn, cudaStream_t st);
 cudaError_t launch_btc_to_bct(const float* in, float* out, int B, int C, int Tn, cudaStream_t st);
 template <typename T>

@@ -53,6 +53,9 @@ struct PackedW {
   int N = 0, n_valid = 0, K_total = 0, k_real = 0, n_taps = 0, n_phases = 1;
   int ntile = 0, kc = 0;
   CUtensorMap tm{};          // valid in tensor-core modes
+  // split-precision fp32 mode: [n_phases * N][2 * K_total] bf16 = (hi | lo) halves of every row, and its tensor map
+  void* w3 = nullptr;
+  CUtensorMap tm3{};
   // tap table (source row offset, channel base in the source view) per phase
   int tap_row[kMaxPhases][kMaxTaps] = {};
   int tap_ch[kMaxPhases][kMaxTaps] = {};
@@ -177,6 +180,9 @@ class Plan {
   long long launches = 0;
   long long bytes_allocated = 0;
   // built-in profiler: when on, programs run eagerly with an event pair around every op
+  // fp32 plans: convolutions as three bf16 tcgen05 products (hi/lo split operands, fp32 accumulation and epilogue)
+  // instead of the FFMA kernel.  MB200_FP32=simt keeps the FFMA kernel (A/B and debugging).
+  bool fp32_split = true;
   int kernel_version = 2;   // 2 = persistent conv_gemm2.cu (default), 1 = first non-persistent kernel (MB200_KERNEL=1)
   long long* probe_out = nullptr;   // developer probe (MB200_DBG): cycle counters of the last conv_op built
   int num_sms = 148;
@@ -197,8 +203,10 @@ class Plan {
   float* upload_f32(const float* host, size_t n);   // plan-owned
   void* ensure(DevBuf& b, size_t bytes);            // grow-only workspace
   void* upload_operand(const std::vector<float>& host);  // fp32 host -> plan dtype device
-  CUtensorMap tmap_act(const void* p, int ld, int rows, int B, int kc, int box_rows = 128) const;
-  CUtensorMap tmap_w(const void* p, int K_total, int rows, int kc, int ntile) const;
+  CUtensorMap tmap_act(const void* p, int ld, int rows, int B, int kc, int box_rows = 128, int dtype = -1) const;   // dtype -1: the plan's
+  CUtensorMap tmap_w(const void* p, int K_total, int rows, int kc, int ntile, int dtype = -1) const;
+  bool split_mode() const { return cfg.dtype == MB200_F32 && !cfg.force_simt && fp32_split; }
+  void reserve_split(size_t elems);                 // scratch for the hi / lo operand copies of the largest conv input
   // Generic weight repack. weight(n, c, j) with c the concatenated real input channel; segs = (real, padded) channels of
   // each source; taps_j[phase][tap] = kernel index j.
   PackedW pack_conv(const std::function<float(int, int, int)>& weight, const float* bias, int n_real, int n_pad,
@@ -252,6 +260,7 @@ class Plan {
   // workspaces
   DevBuf ws_est_[28];
   DevBuf ws_voc_[8];
+  DevBuf ws_split_[2];      // split-precision fp32 mode: bf16 hi / lo copies of the current conv's input
   DevBuf ws_io_[8];
   unsigned long long use_clock_ = 0;
   float train_dropout_p_ = 0.f;

@@ -44,6 +44,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_FUSE_FF")) fuse_ff = std::atoi(v);
   if (const char* v = std::getenv("MB200_FUSE_RQ")) fuse_rq = std::atoi(v);
   if (const char* v = std::getenv("MB200_ATTN")) attn_umma = std::strcmp(v, "mma") != 0;
+  if (const char* v = std::getenv("MB200_FP32")) fp32_split = std::strcmp(v, "simt") != 0;
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -109,6 +110,12 @@ void* Plan::ensure(DevBuf& b, size_t bytes) {
   return b.p;
 }
 
+void Plan::reserve_split(size_t elems) {
+  if (!split_mode()) return;
+  ensure(ws_split_[0], elems * 2);
+  ensure(ws_split_[1], elems * 2);
+}
+
 void* Plan::upload_operand(const std::vector<float>& host) {
   const size_t n = host.size();
   if (cfg.dtype == MB200_F32) return upload_f32(host.data(), n);
@@ -125,9 +132,10 @@ void* Plan::upload_operand(const std::vector<float>& host) {
 
 // Activation view [B][rows][ld] (channels contiguous): 3-D map, box = kc channels x 128 rows x 1 batch element.
 // Rows outside [0, rows) are zero-filled by TMA: that IS the conv's zero padding at the utterance edges.
-CUtensorMap Plan::tmap_act(const void* p, int ld, int rows, int B, int kc, int box_rows) const {
+CUtensorMap Plan::tmap_act(const void* p, int ld, int rows, int B, int kc, int box_rows, int dtype) const {
   CUtensorMap m;
-  const CUtensorMapDataType dt = cfg.dtype == MB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  if (dtype < 0) dtype = cfg.dtype;
+  const CUtensorMapDataType dt = dtype == MB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   cuuint64_t dims[3] = {static_cast<cuuint64_t>(ld), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(B)};
   cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 2, static_cast<cuuint64_t>(ld) * 2 * rows};
   cuuint32_t box[3] = {static_cast<cuuint32_t>(kc), static_cast<cuuint32_t>(box_rows), 1};
@@ -139,9 +147,10 @@ CUtensorMap Plan::tmap_act(const void* p, int ld, int rows, int B, int kc, int b
   return m;
 }
 
-CUtensorMap Plan::tmap_w(const void* p, int K_total, int rows, int kc, int ntile) const {
+CUtensorMap Plan::tmap_w(const void* p, int K_total, int rows, int kc, int ntile, int dtype) const {
   CUtensorMap m;
-  const CUtensorMapDataType dt = cfg.dtype == MB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  if (dtype < 0) dtype = cfg.dtype;
+  const CUtensorMapDataType dt = dtype == MB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(K_total), static_cast<cuuint64_t>(rows)};
   cuuint64_t strides[1] = {static_cast<cuuint64_t>(K_total) * 2};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(kc), static_cast<cuuint32_t>(ntile)};
@@ -190,6 +199,20 @@ PackedW Plan::pack_conv(const std::function<float(int, int, int)>& weight, const
     W.bias = upload_f32(bp.data(), n_pad);
   }
   if (tensor_core()) W.tm = tmap_w(W.w, W.K_total, W.n_phases * n_pad, W.kc, W.ntile);
+  if (split_mode()) {   // (hi | lo) bf16 halves of every weight row
+    const size_t rows = static_cast<size_t>(W.n_phases) * n_pad, K = W.K_total;
+    std::vector<uint16_t> hl(rows * 2 * K);
+    for (size_t r = 0; r < rows; ++r)
+      for (size_t k = 0; k < K; ++k) {
+        const float x = host[r * K + k];
+        const __nv_bfloat16 h = __float2bfloat16_rn(x), l = __float2bfloat16_rn(x - __bfloat162float(h));
+        std::memcpy(&hl[r * 2 * K + k], &h, 2);
+        std::memcpy(&hl[r * 2 * K + K + k], &l, 2);
+      }
+    W.w3 = dalloc(hl.size() * 2);
+    MB_CUDA(cudaMemcpy(W.w3, hl.data(), hl.size() * 2, cudaMemcpyHostToDevice));
+    W.tm3 = tmap_w(W.w3, 2 * W.K_total, W.n_phases * n_pad, W.kc, W.ntile, MB200_BF16);
+  }
   return W;
 }
 
@@ -252,10 +275,36 @@ PackedW Plan::pack_convT(const HostTensor& w, const float* bias, int stride) {
 Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, EpiParams e) {
   ConvLaunch L{};
   ConvGeom& g = L.g;
+  // Split-precision fp32 mode: the fp32 source(s) are first copied into bf16 hi / lo buffers (one row = the concat of the
+  // sources), and the GEMM runs on the bf16 tcgen05 kernel as a_hi w_hi + a_hi w_lo + a_lo w_hi with the fp32 epilogue.
+  const bool split = split_mode() && W.w3 != nullptr;
+  const Src f0 = s0;                       // the fp32 views
+  const Src f1 = s1 ? *s1 : Src{nullptr, 0, 0, 0};
+  const bool concat = s1 != nullptr;
+  Src lo_src{};
+  int split_c0 = 0, split_c1 = 0;
+  if (split) {
+    if (concat) {
+      for (int tp = 0; tp < W.n_taps; ++tp)
+        if (W.tap_ch[0][tp] != 0) throw Error("conv_op(split): concat sources with channel-offset taps");
+      split_c0 = f0.ch; split_c1 = f1.ch;
+    } else {
+      split_c0 = f0.ld;                    // whole rows of the view: strided convs address channel bases inside them
+    }
+    const int chm = split_c0 + split_c1;
+    const size_t need = static_cast<size_t>(B) * f0.rows * chm * 2;
+    if (ws_split_[0].bytes < need || ws_split_[1].bytes < need) throw Error("conv_op(split): reserve_split() was not called for this shape");
+    const int per_tap_ch = concat ? chm : f0.ch;
+    s0 = Src{ws_split_[0].p, chm, per_tap_ch, f0.rows};
+    lo_src = Src{ws_split_[1].p, chm, per_tap_ch, f0.rows};
+    s1 = &lo_src;
+    e.all_f32 = 1;
+  }
   g.B = B; g.T_in = s0.rows; g.T_out = T_out;
   g.n_src = s1 ? 2 : 1;
   g.src_ch[0] = s0.ch; g.src_ld[0] = s0.ld;
   g.src_ch[1] = s1 ? s1->ch : 0; g.src_ld[1] = s1 ? s1->ld : 0;
+  if (split) g.src_ch[1] = 0;              // hi and lo carry the SAME channels: one tap spans src_ch[0] of them
   g.n_taps = W.n_taps; g.n_phases = W.n_phases;
   std::memcpy(g.tap_row, W.tap_row, sizeof(g.tap_row));
   std::memcpy(g.tap_ch, W.tap_ch, sizeof(g.tap_ch));
@@ -272,25 +321,34 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
   if (ntile == 256 && !e.ln_out && T_out > 128 && tile_policy == 1) ntile = 128;
   L.w = W.w; L.ntile = ntile; L.kc = W.kc;
   if (e.ln_out && (W.N != 256 || !tensor_core())) throw Error("conv_op: fused LayerNorm needs the tensor-core kernel and N == 256");
-  if (tensor_core()) {
-    L.tmA[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc);
-    L.tmA[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc) : L.tmA[0];
-    L.tmW = ntile == W.ntile ? W.tm : tmap_w(W.w, W.K_total, W.n_phases * W.N, W.kc, ntile);
+  if (tensor_core() || split) {
+    const int adt = split ? MB200_BF16 : -1;
+    const int Kw = split ? 2 * W.K_total : W.K_total;   // K extent of a packed weight row
+    L.tmA[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 128, adt);
+    L.tmA[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 128, adt) : L.tmA[0];
+    if (split) L.tmW = ntile == W.ntile ? W.tm3 : tmap_w(W.w3, Kw, W.n_phases * W.N, W.kc, ntile, MB200_BF16);
+    else L.tmW = ntile == W.ntile ? W.tm : tmap_w(W.w, W.K_total, W.n_phases * W.N, W.kc, ntile);
     // ---- persistent kernel geometry: A-load groups = (source, channel base); taps of a group share one halo tile
     ConvGeom2& g2 = L.g2;
-    g2.B = B; g2.T_in = s0.rows; g2.T_out = T_out; g2.N = W.N; g2.n_phases = W.n_phases; g2.K_total = W.K_total;
+    g2.B = B; g2.T_in = s0.rows; g2.T_out = T_out; g2.N = W.N; g2.n_phases = W.n_phases; g2.K_total = Kw;
     const int per_tap = g.src_ch[0] + g.src_ch[1];
     int ng = 0;
-    for (int s = 0; s < g.n_src; ++s) {
+    // normal: one pass per source.  split: three passes = the products (hi, w_hi), (hi, w_lo), (lo, w_hi); the w_lo half
+    // of a weight row starts at K_total.
+    const int n_pass = split ? 3 : g.n_src;
+    for (int pass = 0; pass < n_pass; ++pass) {
+      const int s = split ? (pass == 2 ? 1 : 0) : pass;
+      const int wbase = split ? (pass == 1 ? W.K_total : 0) : (s ? g.src_ch[0] : 0);
+      const int chs = split ? g.src_ch[0] : g.src_ch[s];
       std::vector<int> bases;
       for (int tp = 0; tp < W.n_taps; ++tp)
         if (std::find(bases.begin(), bases.end(), W.tap_ch[0][tp]) == bases.end()) bases.push_back(W.tap_ch[0][tp]);
       for (int cb : bases) {
         if (ng >= kMaxGroups) throw Error("conv_op: too many A-load groups");
-        g2.g_src[ng] = s; g2.g_ch[ng] = cb; g2.g_chunks[ng] = g.src_ch[s] / W.kc;
+        g2.g_src[ng] = s; g2.g_ch[ng] = cb; g2.g_chunks[ng] = chs / W.kc;
         int nt = 0;
         for (int tp = 0; tp < W.n_taps; ++tp)
-          if (W.tap_ch[0][tp] == cb) g2.g_wk[ng][nt++] = tp * per_tap + (s ? g.src_ch[0] : 0);
+          if (W.tap_ch[0][tp] == cb) g2.g_wk[ng][nt++] = tp * per_tap + wbase;
         g2.g_ntaps[ng] = nt;
         for (int ph = 0; ph < W.n_phases; ++ph) {
           int rmin = 1 << 30, rmax = -(1 << 30);
@@ -318,14 +376,15 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     // LayerNorm exchange.  Sixteen epilogue warps (eg = 4) when the rings still get their depth: the epilogue is
     // latency-bound, so more warps in flight is what speeds it up; layers with large rings keep eight.
     const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = ntile * W.kc * 2;
-    const long w_total = static_cast<long>(W.n_phases) * W.N * W.K_total * 2;
+    const long w_total = static_cast<long>(W.n_phases) * W.N * Kw * 2;
     g2.a_bytes = a_bytes;
     int max_taps = 1;
     for (int q = 0; q < ng; ++q) max_taps = std::max(max_taps, g2.g_ntaps[q]);
     auto layout = [&](int eg) -> bool {   // fills g2 ring fields + L.smem_bytes; false = rings too shallow for this eg
       const int tail_bytes = 1024 + 512 + 4 * eg * 4608 + 8192, budget = 227 * 1024 - tail_bytes;
       g2.eg = eg;
-      if (w_total <= 100 * 1024 && (budget - w_total) / a_bytes >= 2) {
+      // (split mode streams: the resident loader walks a weight row front to back, the three products revisit its hi half)
+      if (!split && w_total <= 100 * 1024 && (budget - w_total) / a_bytes >= 2) {
         g2.w_resident = 1;
         g2.wt = 1;
         g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
@@ -356,9 +415,22 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     g2.dbg = 0;
     g2.dbg_out = nullptr;
     if (const char* v = std::getenv("MB200_DBG")) {
-      g2.dbg = std::atoi(v);
-      g2.dbg_out = static_cast<long long*>(dalloc(148 * 16 * sizeof(long long)));
-      probe_out = g2.dbg_out;
+      static int op_index = 0;              // MB200_DBG_OP=n instruments only the n-th conv op built (developer probe)
+      const char* only = std::getenv("MB200_DBG_OP");
+      const bool hit = !only || std::atoi(only) == op_index;
+      if (hit) {
+        g2.dbg = std::atoi(v);
+        g2.dbg_out = static_cast<long long*>(dalloc(148 * 16 * sizeof(long long)));
+        probe_out = g2.dbg_out;
+      }
+      if (only && (hit || std::atoi(only) < 0)) {   // MB200_DBG_OP=-1 lists every op
+        {
+          std::fprintf(stderr, "[dbg op %d] B=%d T_out=%d K=%d N=%d taps=%d ntile=%d mb=%d eg=%d tiles=%d flags: gn=%d resid=%d snake=%d mask=%d stats=%d x=%d ln=%d out1=%d\n",
+                       op_index, B, T_out, W.K_total, W.N, W.n_taps, ntile, g2.mb, want_eg, g2.total_tiles, e.gn_raw != nullptr, e.resid != nullptr,
+                       e.snake_a != nullptr, e.mask != nullptr, e.stats_out != nullptr, e.x_state != nullptr, e.ln_out != nullptr, e.out1 != nullptr);
+        }
+      }
+      ++op_index;
     }
     // flat MMA issue schedule (see ConvGeom2::sched)
     {
@@ -389,15 +461,24 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
           }
       }
     }
-    L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8);
-    L.tmA8[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 8) : L.tmA8[0];
+    L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8, adt);
+    L.tmA8[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 8, adt) : L.tmA8[0];
     L.grid = std::min(g2.total_tiles, num_sms);
     L.pdl = use_pdl;
   }
   const int dtype = cfg.dtype;
   const bool tc = tensor_core();
   const bool v2 = kernel_version >= 2;
-  Launch op([L, dtype, tc, v2](cudaStream_t st) -> cudaError_t {
+  const long split_rows = static_cast<long>(B) * f0.rows;
+  void* const split_hi = ws_split_[0].p;
+  void* const split_lo = ws_split_[1].p;
+  Launch op([=](cudaStream_t st) -> cudaError_t {
+    if (split) {
+      cudaError_t err = launch_split_bf16x2(static_cast<const float*>(f0.p), f0.ld, split_c0, static_cast<const float*>(f1.p), f1.ld,
+                                            split_c1, split_rows, split_hi, split_lo, st);
+      if (err != cudaSuccess) return err;
+      return launch_conv_umma2<__nv_bfloat16>(L, st);
+    }
     if (dtype == MB200_F32) return launch_conv_simt<float>(L, st);
     if (dtype == MB200_BF16)
       return tc ? (v2 ? launch_conv_umma2<__nv_bfloat16>(L, st) : launch_conv_umma<__nv_bfloat16>(L, st))

@@ -312,6 +312,7 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
   const int C = E.C, C0 = E.C0;
   const int wide = std::max(E.filt, 3 * C);
   enum { X0, H0, H1, X, Y, Z, A, M, P, D1 };
+  reserve_split(rows * static_cast<size_t>(std::max(std::max(wide, C0), 2 * E.filt_dp)));
   float* x0 = static_cast<float*>(ensure(ws_enc_[X0], rows * C0 * 4));
   float* h0 = static_cast<float*>(ensure(ws_enc_[H0], rows * C0 * 4));
   float* h1 = static_cast<float*>(ensure(ws_enc_[H1], rows * C0 * 4));

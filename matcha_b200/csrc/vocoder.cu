@@ -89,6 +89,7 @@ void Plan::vocoder_buffers(int B, int L) {
   const size_t es = esize(cfg.dtype);
   const size_t bl = static_cast<size_t>(B) * L;
   ensure(ws_voc_[V_MEL], bl * 128 * es);
+  reserve_split(bl * 8192);            // every stage's activations are 8192 values per mel frame
   const bool single = tensor_core() && kernel_version >= 2 && cfg.dtype != MB200_F32;   // see build_vocoder
   for (int b : {V_A, V_X, V_XL, V_R, V_RL, V_C1, V_SUM})
     if (!(single && (b == V_X || b == V_R))) ensure(ws_voc_[b], bl * 8192 * es);

@@ -72,10 +72,12 @@ CONV_CASES = [  # (B, Cin, Cout, T, K, dilation, stride, transposed)
 ]
 
 
-@pytest.mark.parametrize("prec,simt", [("fp32", False), ("bf16", False), ("fp16", False), ("bf16", True)])
+@pytest.mark.parametrize("prec,simt", [("fp32", False), ("fp32", True), ("bf16", False), ("fp16", False), ("bf16", True)])
 def test_conv_gemm_matches_torch(prec, simt):
     """Every Conv1d / ConvTranspose1d / Linear shape class on the path, against torch in fp64 on the same
-    (operand-rounded) inputs: the kernels accumulate in fp32, so agreement is ~1e-6 in every mode."""
+    (operand-rounded) inputs: the kernels accumulate in fp32, so agreement is ~1e-6 in every mode.  fp32 on the tensor
+    cores is the split-precision product (bf16 hi/lo operands, three tcgen05 products): every a*w term carries 2^-16
+    relative error instead of fp32's 2^-24, hence the wider bound; fp32 with force_simt is the FFMA kernel."""
     plan = Plan(prec, 160, force_simt=simt, use_graph=False)
     g = torch.Generator().manual_seed(0)
     for (b, cin, cout, t, k, dil, stride, tr) in CONV_CASES:
@@ -89,7 +91,8 @@ def test_conv_gemm_matches_torch(prec, simt):
             ref = F.conv1d(xq, wq, bias.double(), stride=stride, dilation=dil, padding=dil * (k - 1) // 2)
         y = plan.test_conv1d(x, w, bias, dilation=dil, stride=stride, transposed=tr).cpu().double()
         assert y.shape == ref.shape
-        assert float((y - ref).abs().max()) < 5e-5, (prec, simt, b, cin, cout, t, k, dil, stride, tr)
+        tol = 1.5e-4 if (prec == "fp32" and not simt) else 5e-5
+        assert float((y - ref).abs().max()) < tol, (prec, simt, b, cin, cout, t, k, dil, stride, tr)
 
 
 @pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
