@@ -160,6 +160,10 @@ struct EpiParams {
   // Split-precision fp32 mode (bf16 hi/lo operands, fp32 everything else): EVERY activation stream of the epilogue
   // (gn_raw, resid, resid2, out0, out1, ln_out) is fp32, whatever the kernel's operand type T is.
   int all_f32;
+  // ... and an output whose *_lo pointer is set is stored as that split pair instead (bf16 hi at out, bf16 lo at out_lo):
+  // the next conv reads it directly (Src::lo) and no fp32 copy of the stream exists.
+  void* out0_lo;
+  void* out1_lo;
 };
 
 template <typename T> struct Elem;

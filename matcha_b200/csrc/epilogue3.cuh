@@ -44,7 +44,7 @@ __host__ inline uint32_t epi_features(const EpiParams& e) {
   if (e.ln_out) f |= kF_LN;
   if (e.out1) f |= kF_OUT1 | kF_SLOPE;
   if (e.scale != 1.f) f |= kF_SCALE;
-  if (e.out0_f32 || e.resid_f32 || e.resid2_f32 || e.all_f32) f |= kF_F32;
+  if (e.out0_f32 || e.resid_f32 || e.resid2_f32 || e.all_f32 || e.out0_lo || e.out1_lo) f |= kF_F32;
   if (e.out0_slope != 1.f) f |= kF_SLOPE;
   return f;
 }
@@ -105,6 +105,18 @@ __device__ __forceinline__ void load8(const void* base, long elem, int f32, floa
     unpack8<T>(*reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(base) + elem), f);
   }
 }
+// split-precision store: f = hi + lo with hi, lo in bf16 (16 mantissa bits kept)
+__device__ __forceinline__ void store8_split(void* hi_base, void* lo_base, long elem, const float* f) {
+  __nv_bfloat162 h[4], l[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(f[2 * k]), h1 = __float2bfloat16_rn(f[2 * k + 1]);
+    h[k] = __halves2bfloat162(h0, h1);
+    l[k] = __floats2bfloat162_rn(f[2 * k] - __bfloat162float(h0), f[2 * k + 1] - __bfloat162float(h1));
+  }
+  *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(hi_base) + elem) = *reinterpret_cast<const uint4*>(h);
+  *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(lo_base) + elem) = *reinterpret_cast<const uint4*>(l);
+}
 template <typename T>
 __device__ __forceinline__ void store8(void* base, long elem, int f32, const float* f) {
   if (f32) {
@@ -151,7 +163,7 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
   if constexpr (!(F & kF_LN)) e.ln_out = nullptr;
   if constexpr (!(F & kF_OUT1)) e.out1 = nullptr;
   if constexpr (!(F & kF_SCALE)) e.scale = 1.f;
-  if constexpr (!(F & kF_F32)) { e.out0_f32 = 0; e.resid_f32 = 0; e.resid2_f32 = 0; e.all_f32 = 0; }
+  if constexpr (!(F & kF_F32)) { e.out0_f32 = 0; e.resid_f32 = 0; e.resid2_f32 = 0; e.all_f32 = 0; e.out0_lo = nullptr; e.out1_lo = nullptr; }
   if (e.all_f32) { e.out0_f32 = 1; e.resid_f32 = 1; e.resid2_f32 = 1; }
   const int af = e.all_f32;
   if constexpr (!(F & kF_SLOPE)) e.out0_slope = 1.f;
@@ -460,7 +472,15 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
     if (e.out0) {
       const int ld = e.out0_ld, f32 = e.out0_f32;
       const float sl = e.out0_slope;
-      if (sl == 1.f) {
+      if (e.out0_lo) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float o[8];
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) o[ch] = fmaxf(v[k][ch], v[k][ch] * sl);   // sl == 1: the identity
+          if (ok[k]) store8_split(e.out0, e.out0_lo, static_cast<long>(grow[k]) * ld + n0, o);
+        }
+      } else if (sl == 1.f) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           if (ok[k]) store8<T>(e.out0, static_cast<long>(grow[k]) * ld + n0, f32, v[k]);
@@ -482,7 +502,10 @@ __device__ __forceinline__ void epilogue_tile3(const EpiParams& ep, const int b,
         float o[8];
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) o[ch] = fmaxf(v[k][ch], v[k][ch] * sl);
-        if (ok[k]) store8<T>(e.out1, static_cast<long>(grow[k]) * ld + n0, af, o);
+        if (ok[k]) {
+          if (e.out1_lo) store8_split(e.out1, e.out1_lo, static_cast<long>(grow[k]) * ld + n0, o);
+          else store8<T>(e.out1, static_cast<long>(grow[k]) * ld + n0, af, o);
+        }
       }
     }
     EP_MARK(5);

@@ -67,6 +67,7 @@ struct Src {
   int ld;       // row pitch of the view, elements
   int ch;       // channels consumed (padded)
   int rows;     // rows per batch element of the view
+  const void* lo = nullptr;   // split-precision fp32 mode: p / lo are the bf16 hi / lo halves a producer already wrote
 };
 
 // One enqueued operation of a program plus the bookkeeping the built-in profiler needs.

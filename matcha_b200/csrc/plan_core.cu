@@ -283,7 +283,13 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
   const bool concat = s1 != nullptr;
   Src lo_src{};
   int split_c0 = 0, split_c1 = 0;
-  if (split) {
+  const bool presplit = split && s0.lo != nullptr;
+  if (presplit) {
+    if (concat) throw Error("conv_op(split): a pre-split source cannot be concatenated");
+    lo_src = Src{f0.lo, f0.ld, f0.ch, f0.rows};
+    s1 = &lo_src;
+    e.all_f32 = 1;
+  } else if (split) {
     if (concat) {
       for (int tp = 0; tp < W.n_taps; ++tp)
         if (W.tap_ch[0][tp] != 0) throw Error("conv_op(split): concat sources with channel-offset taps");
@@ -473,6 +479,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
   void* const split_hi = ws_split_[0].p;
   void* const split_lo = ws_split_[1].p;
   Launch op([=](cudaStream_t st) -> cudaError_t {
+    if (split && presplit) return launch_conv_umma2<__nv_bfloat16>(L, st);
     if (split) {
       cudaError_t err = launch_split_bf16x2(static_cast<const float*>(f0.p), f0.ld, split_c0, static_cast<const float*>(f1.p), f1.ld,
                                             split_c1, split_rows, split_hi, split_lo, st);

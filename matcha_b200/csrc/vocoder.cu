@@ -107,12 +107,27 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
   if (cfg.dtype == MB200_F16) slope_stored = __half2float(__float2half_rn(0.1f));
   const float inv_slope = 1.f / slope_stored;
   auto buf = [&](int i) { return ws_voc_[i].p; };
+  // Split-precision fp32 mode: the streams that only convolutions read (A, XL, RL, C1) exist ONLY as bf16 hi / lo pairs
+  // (the two halves of the fp32-sized buffer), written by the producing epilogue and read by the next conv as they are;
+  // the residual streams (X, R, SUM) stay fp32.  No separate split pass, no fp32 copy of a conv input.
+  const bool sp = split_mode();
+  const size_t lo_off = static_cast<size_t>(B) * L * 8192 * 2;
+  auto lo_of = [&](int i) { return static_cast<void*>(static_cast<char*>(buf(i)) + lo_off); };
+  auto conv_in = [&](int i, int ld, int ch, int rows) { Src s{buf(i), ld, ch, rows}; if (sp) s.lo = lo_of(i); return s; };
+  auto to_conv0 = [&](EpiParams& e, int i, int ld, float slope) {   // out0 = a conv-input stream
+    e.out0 = buf(i); e.out0_ld = ld; e.out0_slope = slope;
+    if (sp) e.out0_lo = lo_of(i); else e.out0_f32 = f32;
+  };
+  auto to_conv1 = [&](EpiParams& e, int i, int ld, float slope) {   // out1 = a conv-input stream
+    e.out1 = buf(i); e.out1_ld = ld; e.out1_slope = slope;
+    if (sp) e.out1_lo = lo_of(i);
+  };
   int region = 1;
   auto add = [&](Launch l) { l.region = region; prog.ops.push_back(std::move(l)); prog.kernels++; };
   const GeneratorW& G = gen_;
   {  // conv_pre, then the first stage's leaky_relu(0.1) (models.py:182,184)
     EpiParams e = epi();
-    e.out0 = buf(V_A); e.out0_ld = 512; e.out0_f32 = f32; e.out0_slope = 0.1f;
+    to_conv0(e, V_A, 512, 0.1f);
     add(conv_op(G.conv_pre, Src{buf(V_MEL), 128, 128, L}, nullptr, B, L, e));
   }
   int ch = 512, len = L;
@@ -125,9 +140,9 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
         e.out0 = buf(V_XL); e.out0_ld = C; e.out0_slope = 0.1f;
       } else {
         e.out0 = buf(V_X); e.out0_ld = C; e.out0_f32 = f32;
-        e.out1 = buf(V_XL); e.out1_ld = C; e.out1_slope = 0.1f;
+        to_conv1(e, V_XL, C, 0.1f);
       }
-      add(conv_op(G.ups[i], Src{buf(V_A), ch, ch, len}, nullptr, B, len, e));
+      add(conv_op(G.ups[i], conv_in(V_A, ch, ch, len), nullptr, B, len, e));
     }
     len *= kRates[i];
     ch = C;
@@ -156,8 +171,8 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
         }
         {  // xt = lrelu(c1(lrelu(r)))   (models.py:92-94)
           EpiParams e = epi();
-          e.out0 = buf(V_C1); e.out0_ld = C; e.out0_f32 = f32; e.out0_slope = 0.1f;
-          add(conv_op(W1, Src{m == 0 ? buf(V_XL) : buf(V_RL), C, C, len}, nullptr, B, len, e));
+          to_conv0(e, V_C1, C, 0.1f);
+          add(conv_op(W1, conv_in(m == 0 ? V_XL : V_RL, C, C, len), nullptr, B, len, e));
         }
         EpiParams e = epi();  // r = c2(xt) + r   (models.py:95-96)
         if (single) {
@@ -170,7 +185,7 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
           e.out0 = buf(V_RL); e.out0_ld = C; e.out0_slope = 0.1f;
         } else if (m < 2) {
           e.out0 = buf(V_R); e.out0_ld = C; e.out0_f32 = f32;
-          e.out1 = buf(V_RL); e.out1_ld = C; e.out1_slope = 0.1f;
+          to_conv1(e, V_RL, C, 0.1f);
         } else if (j == 0) {
           e.out0 = buf(V_SUM); e.out0_ld = C; e.out0_f32 = f32;
         } else if (j == 1) {
@@ -179,9 +194,10 @@ void Plan::build_vocoder(Program& prog, int B, int L, float* /*wav*/) {
         } else {  // x = xs / 3, then the next consumer's leaky_relu: 0.1 inside the loop, 0.01 before conv_post (:192-193)
           e.resid2 = buf(V_SUM); e.resid2_ld = C; e.resid2_f32 = f32;
           e.scale = 1.f / 3.f;
-          e.out0 = buf(V_A); e.out0_ld = C; e.out0_f32 = f32; e.out0_slope = i == 3 ? 0.01f : 0.1f;
+          if (i == 3) { e.out0 = buf(V_A); e.out0_ld = C; e.out0_f32 = f32; e.out0_slope = 0.01f; }   // conv_post reads fp32
+          else to_conv0(e, V_A, C, 0.1f);
         }
-        add(conv_op(W2, Src{buf(V_C1), C, C, len}, nullptr, B, len, e));
+        add(conv_op(W2, conv_in(V_C1, C, C, len), nullptr, B, len, e));
       }
     }
   }
