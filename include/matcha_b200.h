@@ -19,10 +19,12 @@ typedef struct mb200_plan mb200_plan;
 enum { MB200_F32 = 0, MB200_BF16 = 1, MB200_F16 = 2 };
 
 typedef struct {
-  int dtype;       /* MB200_F32: FFMA kernels, fp32 everywhere.  MB200_BF16 / MB200_F16: tcgen05 tensor-core kernels,
-                      bf16 / f16 operands and activations, fp32 accumulation and statistics. */
+  int dtype;       /* MB200_F32: fp32 activations and epilogues; convolutions as split-precision tcgen05 products (bf16 hi/lo
+                      operands, ~2^-16 relative per term, fp32 accumulation), attention / norms in fp32 FFMA.
+                      MB200_BF16 / MB200_F16: tcgen05 tensor-core kernels, bf16 / f16 operands and activations, fp32
+                      accumulation and statistics. */
   int c_in;        /* estimator input channels: 160 (LJSpeech) or 224 (VCTK: + 64 speaker dims), flow_matching.py:130 */
-  int force_simt;  /* debugging: run the half-precision modes on the FFMA kernels instead of tcgen05 */
+  int force_simt;  /* debugging: run every mode's convolutions on the FFMA kernel instead of tcgen05 */
   int use_graph;   /* capture decode / vocoder launches into a CUDA graph per (B, T, n_steps) shape */
 } mb200_cfg;
 
