@@ -63,7 +63,7 @@ def main():
     json.dump({"source": out + "_summary.txt (ncu dram__bytes_read.sum + dram__bytes_write.sum, one eager cfg2 pass)",
                "kernel": "conv_gemm_umma2_kernel + resblock_pair_kernel + ff_fused_kernel + resqkv_fused_kernel (all instantiations)", "launches_per_step": n,
                "dram_bytes_per_launch": dram / n, "dram_bytes_per_step": dram, "share_of_step_time": ns / total},
-              open("profiles/r01_dram_traffic.json", "w"), indent=1)
+              open(sys.argv[4] if len(sys.argv) > 4 else "profiles/r02_dram_traffic.json", "w"), indent=1)
     print("\n".join(lines))
 
 
