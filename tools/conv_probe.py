@@ -22,6 +22,9 @@ CASES = {  # name: (B, C, T, K, dil)
     "e_ff1": (64, 256, 452, 1, 1, 1024),   # feed-forward up projection
     "e_ff2": (64, 1024, 452, 1, 1, 256),
     "e_c3_mid": (64, 256, 113, 3, 1),
+    "e_c3_b256": (256, 256, 452, 3, 1),     # same layer, 4x the tiles: steady-state cost per tile
+    "e_c3_b512": (512, 256, 452, 3, 1),
+    "e_c3_half": (64, 256, 226, 3, 1),      # T/2 level: 128 tiles, one per CTA
 }
 
 
