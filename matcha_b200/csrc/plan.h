@@ -257,7 +257,7 @@ class Plan {
   EstimatorW est_;
   GeneratorW gen_;
   TextEncW enc_;
-  DevBuf ws_enc_[10];
+  DevBuf ws_enc_[11];
   // workspaces
   DevBuf ws_est_[28];
   DevBuf ws_voc_[8];

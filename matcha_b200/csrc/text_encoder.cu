@@ -121,17 +121,24 @@ scale_q_tail_kernel(float* __restrict__ qkv, int C, int H, int Dh, long rows, fl
 // ---------------------------------------------------------------- multi-head attention, head dim D in {96, 128}
 // out[b, q, h*D ...] = softmax_k(mask[b,k] != 0 ? q . k : -1e4) v.  One thread per query row (q and the output row in
 // registers), K / V tiles of 32 keys broadcast from shared memory, online softmax in fp32 (as attention_simt_kernel).
+// A single long utterance has too few query rows to fill the GPU (2 heads x 2001 rows = 64 CTAs), so the KEYS can be split
+// over ks CTAs (blockIdx.x = query block * ks + split): each writes its unnormalised row, running maximum and sum to
+// `part` ([b][h][q][split][D + 2]) and text_attention_merge_kernel combines them.  ks == 1 writes `out` directly.
 template <int D>
 __global__ void __launch_bounds__(64)
-text_attention_kernel(const float* __restrict__ qkv, const float* __restrict__ mask, float* __restrict__ out, int L, int C) {
+text_attention_kernel(const float* __restrict__ qkv, const float* __restrict__ mask, float* __restrict__ out, int L, int C,
+                      int ks, float* __restrict__ part) {
   __shared__ __align__(16) float Ks[32][D];
   __shared__ __align__(16) float Vs[32][D];
   __shared__ float Ms[32];
   const int b = blockIdx.z, h = blockIdx.y;
   const int tid = threadIdx.x;
-  const int qi = blockIdx.x * 64 + tid;
+  const int split = blockIdx.x % ks;
+  const int qi = (blockIdx.x / ks) * 64 + tid;
   const bool qvalid = qi < L;
   const float* base = qkv + static_cast<long>(b) * L * 3 * C;
+  const int n_kt = (L + 31) / 32;                      // key tiles; this CTA takes [kt0, kt1)
+  const int kt0 = static_cast<int>(static_cast<long>(n_kt) * split / ks), kt1 = static_cast<int>(static_cast<long>(n_kt) * (split + 1) / ks);
   float q[D], o[D];
 #pragma unroll
   for (int d = 0; d < D; ++d) { o[d] = 0.f; q[d] = 0.f; }
@@ -141,7 +148,7 @@ text_attention_kernel(const float* __restrict__ qkv, const float* __restrict__ m
     for (int d4 = 0; d4 < D / 4; ++d4) { const float4 t = qp[d4]; q[4 * d4] = t.x; q[4 * d4 + 1] = t.y; q[4 * d4 + 2] = t.z; q[4 * d4 + 3] = t.w; }
   }
   float mrun = -INFINITY, lrun = 0.f;
-  for (int k0 = 0; k0 < L; k0 += 32) {
+  for (int k0 = kt0 * 32; k0 < min(L, kt1 * 32); k0 += 32) {
     __syncthreads();
     for (int i = tid; i < 32 * (D / 4); i += 64) {     // 32 keys x D/4 float4 of K and of V
       const int kj = i / (D / 4), d4 = i - kj * (D / 4);
@@ -202,12 +209,45 @@ text_attention_kernel(const float* __restrict__ qkv, const float* __restrict__ m
       }
     }
   }
-  if (qvalid) {
+  if (qvalid && ks == 1) {
     const float inv = 1.f / lrun;
     float4* op = reinterpret_cast<float4*>(out + (static_cast<long>(b) * L + qi) * C + h * D);
 #pragma unroll
     for (int d4 = 0; d4 < D / 4; ++d4) op[d4] = make_float4(o[4 * d4] * inv, o[4 * d4 + 1] * inv, o[4 * d4 + 2] * inv, o[4 * d4 + 3] * inv);
+  } else if (qvalid) {
+    float* pp = part + (((static_cast<long>(b) * gridDim.y + h) * L + qi) * ks + split) * (D + 2);
+#pragma unroll
+    for (int d = 0; d < D; ++d) pp[d] = o[d];
+    pp[D] = mrun;
+    pp[D + 1] = lrun;
   }
+}
+
+// out[b, q, h*D + d] = sum_s e^(m_s - m) o_s[d] / sum_s e^(m_s - m) l_s over the key splits, m = max_s m_s.  One thread per
+// (b, h, q, d); a split that saw no key has m_s = -inf and drops out.
+template <int D>
+__global__ void __launch_bounds__(256)
+text_attention_merge_kernel(const float* __restrict__ part, float* __restrict__ out, int L, int C, int H, int ks, long total) {
+  const long i = static_cast<long>(blockIdx.x) * 256 + threadIdx.x;
+  if (i >= total) return;
+  const int d = static_cast<int>(i % D);
+  const long row = i / D;                               // (b * H + h) * L + q
+  const int q = static_cast<int>(row % L);
+  const long bh = row / L;
+  const int h = static_cast<int>(bh % H);
+  const long b = bh / H;
+  const float* pp = part + row * ks * (D + 2);
+  float m = -INFINITY;
+  for (int s = 0; s < ks; ++s) m = fmaxf(m, pp[s * (D + 2) + D]);
+  float num = 0.f, den = 0.f;
+  for (int s = 0; s < ks; ++s) {
+    const float ms = pp[s * (D + 2) + D];
+    if (ms == -INFINITY) continue;
+    const float w = expf(ms - m);
+    num = fmaf(w, pp[s * (D + 2) + d], num);
+    den = fmaf(w, pp[s * (D + 2) + D + 1], den);
+  }
+  out[(b * L + q) * C + h * D + d] = num / den;
 }
 
 // (rows, 1) column 0 of a [rows][ld] buffer -> dense, times mask   (DurationPredictor.proj output, text_encoder.py:93-94)
@@ -311,7 +351,7 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
   const long rows = static_cast<long>(B) * Lx;
   const int C = E.C, C0 = E.C0;
   const int wide = std::max(E.filt, 3 * C);
-  enum { X0, H0, H1, X, Y, Z, A, M, P, D1 };
+  enum { X0, H0, H1, X, Y, Z, A, M, P, D1, APART };
   reserve_split(rows * static_cast<size_t>(std::max(std::max(wide, C0), 2 * E.filt_dp)));
   float* x0 = static_cast<float*>(ensure(ws_enc_[X0], rows * C0 * 4));
   float* h0 = static_cast<float*>(ensure(ws_enc_[H0], rows * C0 * 4));
@@ -324,6 +364,11 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
   float* p = static_cast<float*>(ensure(ws_enc_[P], rows * 80 * 4));
   float* d1 = static_cast<float*>(ensure(ws_enc_[D1], rows * 2 * E.filt_dp * 4));
   float* d2 = d1 + rows * E.filt_dp;
+  // key splits of the attention: enough CTAs for two per SM, at most 8 and at most one split per 4 key tiles
+  const int att_ctas = ((Lx + 63) / 64) * E.H * B;
+  int att_ks = std::min(8, (2 * num_sms + att_ctas - 1) / att_ctas);
+  att_ks = std::max(1, std::min(att_ks, ((Lx + 31) / 32) / 4));
+  float* att_part = att_ks > 1 ? static_cast<float*>(ensure(ws_enc_[APART], rows * E.H * att_ks * (E.Dh + 2) * 4)) : nullptr;
   const unsigned row_blocks = static_cast<unsigned>((rows + 7) / 8);
   auto grid1 = [](long n) { return static_cast<unsigned>((n + 255) / 256); };
   auto conv = [&](const PackedW& W, const float* in, int in_ch, EpiParams e) {
@@ -372,10 +417,17 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
     MB_CUDA(cudaGetLastError());
     scale_q_tail_kernel<<<grid1(rows * E.H * (E.Dh / 2)), 256, 0, st>>>(z, C, E.H, E.Dh, rows, q_scale);
     MB_CUDA(cudaGetLastError());
-    dim3 ag((Lx + 63) / 64, E.H, B);
-    if (E.Dh == 96) text_attention_kernel<96><<<ag, 64, 0, st>>>(z, m, a, Lx, C);
-    else text_attention_kernel<128><<<ag, 64, 0, st>>>(z, m, a, Lx, C);
+    dim3 ag(((Lx + 63) / 64) * att_ks, E.H, B);
+    if (E.Dh == 96) text_attention_kernel<96><<<ag, 64, 0, st>>>(z, m, a, Lx, C, att_ks, att_part);
+    else text_attention_kernel<128><<<ag, 64, 0, st>>>(z, m, a, Lx, C, att_ks, att_part);
     MB_CUDA(cudaGetLastError());
+    if (att_ks > 1) {
+      const long total = rows * E.H * E.Dh;
+      if (E.Dh == 96) text_attention_merge_kernel<96><<<grid1(total), 256, 0, st>>>(att_part, a, Lx, C, E.H, att_ks, total);
+      else text_attention_merge_kernel<128><<<grid1(total), 256, 0, st>>>(att_part, a, Lx, C, E.H, att_ks, total);
+      MB_CUDA(cudaGetLastError());
+      launches += 1;
+    }
     launches += 3;
     e = epi_f32();                       // x = LayerNorm(x + conv_o(attn))
     e.resid = x; e.resid_ld = C; e.resid_f32 = 1;
