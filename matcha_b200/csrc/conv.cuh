@@ -54,6 +54,7 @@ struct ConvGeom2 {
   int wt;                                          // taps per streamed weight stage (1 or 2): longer steps per handshake
   int m_tiles, n_tiles, total_tiles;
   int mb;                                          // 128-row blocks per tile (1, 2 or 4): narrow-N layers amortise per-tile costs
+  int pair;                                        // CTA pairs (cta_group::2): each CTA holds half of the weight tile's rows
   int a_bytes;                                     // bytes of one A ring stage: (128*mb + 64) rows
   // Flat MMA issue schedule, [phase][n_steps]: one entry per (group, K chunk, tap) in issue order.
   //   bits 0-15  tap's row shift inside the halo tile, in 16-byte units (shift * row bytes / 16)

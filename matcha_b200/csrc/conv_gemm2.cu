@@ -34,7 +34,10 @@ namespace mb {
 constexpr int kMaxRing = 8;
 constexpr int kBarBytes = 512;   // mbarriers + TMEM slot
 
-template <int NTILE, int KC, int MB, int EG, typename T, uint32_t F>
+// PAIR: two CTAs of a cluster work as one tcgen05 cta_group::2 unit.  Each computes its own 128-row tile, but the MMAs
+// (issued by the even CTA for both) read the weight tile HALF from each CTA's shared memory, so a CTA streams only
+// NTILE / 2 weight rows per K step from L2: the N = 256 estimator layers are bound by that stream.
+template <int NTILE, int KC, int MB, int EG, typename T, uint32_t F, bool PAIR = false>
 __global__ void __launch_bounds__(64 + 128 * EG, 1)
 conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                        const __grid_constant__ CUtensorMap tmA0x, const __grid_constant__ CUtensorMap tmA1x,
@@ -44,7 +47,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   const long long probe_k0 = clock64();
 #endif
   constexpr int ROWB = KC * 2;
-  constexpr int W_TILE = NTILE * ROWB;
+  constexpr int W_TILE = (PAIR ? NTILE / 2 : NTILE) * ROWB;   // weight rows of one K chunk held by THIS CTA
   constexpr int TMEM_COLS = 512;   // one CTA per SM: take all of TMEM
   constexpr int SLOT_COLS = MB * NTILE;
   constexpr int NACC = (512 / SLOT_COLS) < 4 ? (512 / SLOT_COLS) : 4;
@@ -75,17 +78,18 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int np = g.n_tiles * g.n_phases;
+  const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;   // 0 = the pair's leader (issues the MMAs)
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmA0x); tma_prefetch_desc(&tmW);
     for (int s = 0; s < kMaxRing; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    for (int s = 0; s < 4; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4 * EG); }
+    for (int s = 0; s < 4; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], (PAIR ? 8 : 4) * EG); }   // pair: both CTAs' epilogue warps
     mbar_init(wres, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if (warp == 1) { if constexpr (PAIR) tmem_alloc_pair<TMEM_COLS>(tmem_slot); else tmem_alloc<TMEM_COLS>(tmem_slot); }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();   // pair: the peer's barriers are initialised before anything arrives on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 #ifdef MB200_PROBE
@@ -111,7 +115,10 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0;
     MB_T0();
-    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
+    // pair: both CTAs run the same number of iterations; the odd CTA of the last pair may have no tile of its own
+    // ("ghost"): it repeats the last tile's loads so that the leader's byte counts hold, and stores nothing.
+    for (int tl = PAIR ? (blockIdx.x >> 1) : blockIdx.x; (PAIR ? 2 * tl : tl) < g.total_tiles; tl += PAIR ? (gridDim.x >> 1) : gridDim.x) {
+      const int tile = min(PAIR ? 2 * tl + rank : tl, g.total_tiles - 1);
       const int nn = tile % np, mm = tile / np;
       const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
       const int t0 = (mm % g.m_tiles) * TROWS, b = mm / g.m_tiles;
@@ -127,6 +134,11 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
             const int ch = g.g_ch[q] + c * KC;
             if (MB_DBG(2)) {
               mbar_arrive(&a_full[as]);
+            } else if constexpr (PAIR) {   // the leader's barrier counts both CTAs' bytes
+              if (rank == 0) mbar_expect_tx(&a_full[as], 2 * (TROWS + 8 * extra) * ROWB);
+#pragma unroll
+              for (int i = 0; i < MB; ++i) tma_load_3d_pair(dst + i * 128 * ROWB, m128, &a_full[as], ch, row0 + 128 * i, b);
+              for (int x = 0; x < extra; ++x) tma_load_3d_pair(dst + (TROWS + 8 * x) * ROWB, m8, &a_full[as], ch, row0 + TROWS + 8 * x, b);
             } else {
               mbar_expect_tx(&a_full[as], (TROWS + 8 * extra) * ROWB);
 #pragma unroll
@@ -143,6 +155,11 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
               if (elect_one()) {
                 if (MB_DBG(1)) {
                   mbar_arrive(&w_full[ws]);
+                } else if constexpr (PAIR) {   // this CTA's half of the weight rows
+                  if (rank == 0) mbar_expect_tx(&w_full[ws], 2 * nt * W_TILE);
+                  for (int j = 0; j < nt; ++j)
+                    tma_load_2d_pair(w_base + ws * W_STAGE + j * W_TILE, &tmW, &w_full[ws], g.g_wk[q][tp + j] + c * KC,
+                                     phase * g.N + n_tile * NTILE + rank * (NTILE / 2));
                 } else {
                   mbar_expect_tx(&w_full[ws], nt * W_TILE);
                   for (int j = 0; j < nt; ++j)
@@ -159,8 +176,13 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     }
     MB_TEND(0);
   } else if (warp == 1) {
-    // ================================================================= MMA issuer (converged warp, elected issue)
-    constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 128, NTILE);
+    // ================================================================= MMA issuer (converged warp, elected issue; pair: leader only)
+    if (rank == 0) {
+    constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, PAIR ? 256 : 128, NTILE);
+    auto mma = [](uint32_t d, uint32_t a, uint32_t b, uint32_t hi, uint32_t id, uint32_t acc) {
+      if constexpr (PAIR) umma_f16_lohi_pair(d, a, b, hi, id, acc); else umma_f16_lohi(d, a, b, hi, id, acc);
+    };
+    auto commit = [](uint64_t* bar) { if constexpr (PAIR) umma_commit_pair(bar); else umma_commit(bar); };
     constexpr uint32_t W16 = W_TILE >> 4, BLK16 = (128 * ROWB) >> 4;
     const uint32_t desc_hi = static_cast<uint32_t>(umma_smem_desc<ROWB>(0) >> 32);
     const uint32_t a_lo0 = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(a_ring)));
@@ -172,7 +194,8 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     int as = 0, ws = 0, slot = 0;
     uint32_t aph = 0, wph = 0, tph = 0;
     MB_T0();
-    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
+    for (int tl = PAIR ? (blockIdx.x >> 1) : blockIdx.x; (PAIR ? 2 * tl : tl) < g.total_tiles; tl += PAIR ? (gridDim.x >> 1) : gridDim.x) {
+      const int tile = PAIR ? 2 * tl : tl;   // pair: both tiles share (n tile, phase) (np == 1 in pair mode)
       const int nn = tile % np;
       const uint32_t* sch = g.sched + (nn / g.n_tiles) * n_steps;
       MB_WAIT(mbar_wait(&t_empty[slot], tph ^ 1));
@@ -212,20 +235,20 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
           for (int k = 0; k < KC / 16; ++k) {
 #pragma unroll
             for (int i = 0; i < MB; ++i)
-              if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a0 + i * BLK16 + 2 * k, w_lo_0 + 2 * k, desc_hi, idesc, k == 0 ? acc0 : 1u);
+              if (!MB_DBG(4)) mma(dtm + i * NTILE, a0 + i * BLK16 + 2 * k, w_lo_0 + 2 * k, desc_hi, idesc, k == 0 ? acc0 : 1u);
           }
-          if (!resident && (en0 & kSchedWLast)) umma_commit(&w_empty[ws]);
+          if (!resident && (en0 & kSchedWLast)) commit(&w_empty[ws]);
           if (two) {
 #pragma unroll
             for (int k = 0; k < KC / 16; ++k) {
 #pragma unroll
               for (int i = 0; i < MB; ++i)
-                if (!MB_DBG(4)) umma_f16_lohi(dtm + i * NTILE, a1 + i * BLK16 + 2 * k, w_lo_1 + 2 * k, desc_hi, idesc, 1u);
+                if (!MB_DBG(4)) mma(dtm + i * NTILE, a1 + i * BLK16 + 2 * k, w_lo_1 + 2 * k, desc_hi, idesc, 1u);
             }
-            if (!resident && (en1 & kSchedWLast)) umma_commit(&w_empty[ws1]);
+            if (!resident && (en1 & kSchedWLast)) commit(&w_empty[ws1]);
           }
-          if ((en0 | en1) & kSchedLast) umma_commit(&a_empty[as]);
-          if (s + 2 >= n_steps) umma_commit(&t_full[slot]);
+          if ((en0 | en1) & kSchedLast) commit(&a_empty[as]);
+          if (s + 2 >= n_steps) commit(&t_full[slot]);
         }
         __syncwarp();
         if (!resident) {
@@ -237,6 +260,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       if (++slot == NACC) { slot = 0; tph ^= 1; }
     }
     MB_TEND(1);
+    }
   } else {
     // ================================================================= epilogue: warps 2-5 (group 0), 6-9 (group 1)
     const int grp = (warp - 2) >> 2;
@@ -246,25 +270,32 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     int slot = 0, it = 0;
     uint32_t tph = 0;
     MB_T0E();
-    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++it) {
+    for (int tl = PAIR ? (blockIdx.x >> 1) : blockIdx.x; (PAIR ? 2 * tl : tl) < g.total_tiles; tl += PAIR ? (gridDim.x >> 1) : gridDim.x, ++it) {
+      const int tile_raw = PAIR ? 2 * tl + rank : tl;
+      const bool ghost = tile_raw >= g.total_tiles;   // pair only: this CTA has no tile in the last round
+      const int tile = ghost ? g.total_tiles - 1 : tile_raw;
       const int nn = tile % np, mm = tile / np;
       const int n_tile = nn % g.n_tiles, phase = nn / g.n_tiles;
       const int t0 = (mm % g.m_tiles) * TROWS, b = mm / g.m_tiles;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + slot * SLOT_COLS;
 #ifdef MB200_PROBE
-      if (MB_DBG(8)) {
+      if (MB_DBG(8) || (PAIR && ghost)) {
         MB_WAIT(mbar_wait(&t_full[slot], tph));
       } else {
         epilogue_tile3<NTILE, MB, EG, T, F>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
                                  lane_grp, grp, &t_full[slot], tph, probe_e);
       }
 #else
-      epilogue_tile3<NTILE, MB, EG, T, F>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
-                               lane_grp, grp, &t_full[slot], tph);
+      if (PAIR && ghost) {
+        mbar_wait(&t_full[slot], tph);     // consume the phase; the accumulator holds a copy of the last tile: nothing to store
+      } else {
+        epilogue_tile3<NTILE, MB, EG, T, F>(e, b, t0, g.T_out, phase, n_tile * NTILE, taddr, stg, lnx + (it & 1) * (EG * 128), lane,
+                                 lane_grp, grp, &t_full[slot], tph);
+      }
 #endif
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&t_empty[slot]);
+      if (lane == 0) { if constexpr (PAIR) mbar_arrive_leader(&t_empty[slot]); else mbar_arrive(&t_empty[slot]); }
       if (++slot == NACC) { slot = 0; tph ^= 1; }
     }
     if constexpr ((F & kF_STATS) != 0) {
@@ -277,19 +308,19 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     if (warp == 6) { MB_TEND(3); }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();   // pair: nothing of the peer's may still be in flight towards this CTA
   if constexpr ((F & kF_STATS) != 0) {
     if (e.stats_out) gn_stats_finish(e, g.B, gridDim.x, reinterpret_cast<int*>(tmem_slot + 1));   // ordered GroupNorm sums by the last CTA to get here
   }
 #ifdef MB200_PROBE
   if (threadIdx.x == 0 && g.dbg_out) { g.dbg_out[blockIdx.x * 16 + 8] = clock64() - probe_k0; g.dbg_out[blockIdx.x * 16 + 9] = probe_k1 - probe_k0; }
 #endif
-  if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+  if (warp == 1) { if constexpr (PAIR) tmem_dealloc_pair<TMEM_COLS>(tmem_base); else tmem_dealloc<TMEM_COLS>(tmem_base); }
 }
 
-template <int NTILE, int KC, int MB, int EG, typename T, uint32_t F>
+template <int NTILE, int KC, int MB, int EG, typename T, uint32_t F, bool PAIR = false>
 static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
-  auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, EG, T, F>;
+  auto kern = conv_gemm_umma2_kernel<NTILE, KC, MB, EG, T, F, PAIR>;
   static PerDeviceOnce configured;
   if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -302,11 +333,20 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
   cfg.blockDim = dim3(64 + 128 * EG);
   cfg.dynamicSmemBytes = L.smem_bytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (L.pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (PAIR) {   // CTA pairs: clusters of two (grid is even)
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = L.pdl ? 1 : 0;
+  cfg.numAttrs = na;
   return cudaLaunchKernelEx(&cfg, kern, L.tmA[0], L.tmA[two ? 1 : 0], L.tmA8[0], L.tmA8[two ? 1 : 0], L.tmW, L.g2, L.e);
 }
 
@@ -314,6 +354,15 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
 template <int NTILE, int KC, int MB, int EG, typename T>
 static cudaError_t launch_umma2_feat(const ConvLaunch& L, cudaStream_t st) {
   const uint32_t need = epi_features(L.e);
+  if constexpr (NTILE == 256 && MB == 1) {
+    if (L.g2.pair) {
+#define MB_TRYP(CLS) if ((need & ~(CLS)) == 0) return launch_umma2_inst<NTILE, KC, MB, EG, T, (CLS), true>(L, st)
+      if constexpr (EG == 3) { MB_TRYP(kFC_STATS); MB_TRYP(kFC_SNAKE); MB_TRYP(kFC_RESLN); MB_TRYP(kFC_GNLN); }
+      if constexpr (EG == 2) { MB_TRYP(kFC_VOC); MB_TRYP(kFC_RESMASK); }
+#undef MB_TRYP
+      return launch_umma2_inst<NTILE, KC, MB, EG, T, kF_ALL, true>(L, st);
+    }
+  }
 #define MB_TRY(CLS) if ((need & ~(CLS)) == 0) return launch_umma2_inst<NTILE, KC, MB, EG, T, (CLS)>(L, st)
   if constexpr (NTILE == 256 && MB == 1 && EG == 3) { MB_TRY(kFC_STATS); MB_TRY(kFC_SNAKE); MB_TRY(kFC_RESLN); MB_TRY(kFC_GNLN); }
   if constexpr (EG == 2) { MB_TRY(kFC_VOC); }

@@ -45,6 +45,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_FUSE_RQ")) fuse_rq = std::atoi(v);
   if (const char* v = std::getenv("MB200_ATTN")) attn_umma = std::strcmp(v, "mma") != 0;
   if (const char* v = std::getenv("MB200_FP32")) fp32_split = std::strcmp(v, "simt") != 0;
+  if (const char* v = std::getenv("MB200_PAIR")) use_pair = std::atoi(v) != 0;
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -332,8 +333,14 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     const int Kw = split ? 2 * W.K_total : W.K_total;   // K extent of a packed weight row
     L.tmA[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 128, adt);
     L.tmA[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 128, adt) : L.tmA[0];
-    if (split) L.tmW = ntile == W.ntile ? W.tm3 : tmap_w(W.w3, Kw, W.n_phases * W.N, W.kc, ntile, MB200_BF16);
-    else L.tmW = ntile == W.ntile ? W.tm : tmap_w(W.w, W.K_total, W.n_phases * W.N, W.kc, ntile);
+    // CTA pairs (cta_group::2) for the N = 256 layers with streamed weights: each CTA of a pair fetches half of the weight
+    // rows (conv_gemm2.cu).  Needs one N tile and one phase (both CTAs of a pair then always want the same weights).
+    const long w_total_bytes = static_cast<long>(W.n_phases) * W.N * Kw * 2;
+    const bool pair = use_pair && kernel_version >= 2 && ntile == 256 && W.N == 256 && W.n_phases == 1 && W.kc == 64 &&
+                      (split || w_total_bytes > 100 * 1024) && static_cast<long>(B) * ((T_out + 127) / 128) >= 2;
+    const int wbox = pair ? ntile / 2 : ntile;
+    if (split) L.tmW = (ntile == W.ntile && !pair) ? W.tm3 : tmap_w(W.w3, Kw, W.n_phases * W.N, W.kc, wbox, MB200_BF16);
+    else L.tmW = (ntile == W.ntile && !pair) ? W.tm : tmap_w(W.w, W.K_total, W.n_phases * W.N, W.kc, wbox);
     // ---- persistent kernel geometry: A-load groups = (source, channel base); taps of a group share one halo tile
     ConvGeom2& g2 = L.g2;
     g2.B = B; g2.T_in = s0.rows; g2.T_out = T_out; g2.N = W.N; g2.n_phases = W.n_phases; g2.K_total = Kw;
@@ -381,7 +388,8 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     // shared memory: A ring | weights | 1 KB alignment slack, 512 B barriers, 4.5 KB epilogue staging per epilogue warp,
     // LayerNorm exchange.  Sixteen epilogue warps (eg = 4) when the rings still get their depth: the epilogue is
     // latency-bound, so more warps in flight is what speeds it up; layers with large rings keep eight.
-    const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = ntile * W.kc * 2;
+    const int a_bytes = (128 * g2.mb + 64) * W.kc * 2, w_tile = wbox * W.kc * 2;   // weight rows of one K chunk in ONE CTA
+    g2.pair = pair ? 1 : 0;
     const long w_total = static_cast<long>(W.n_phases) * W.N * Kw * 2;
     g2.a_bytes = a_bytes;
     int max_taps = 1;
@@ -390,7 +398,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
       const int tail_bytes = 1024 + 512 + 4 * eg * 4608 + 8192, budget = 227 * 1024 - tail_bytes;
       g2.eg = eg;
       // (split mode streams: the resident loader walks a weight row front to back, the three products revisit its hi half)
-      if (!split && w_total <= 100 * 1024 && (budget - w_total) / a_bytes >= 2) {
+      if (!split && !pair && w_total <= 100 * 1024 && (budget - w_total) / a_bytes >= 2) {
         g2.w_resident = 1;
         g2.wt = 1;
         g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
@@ -400,6 +408,8 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
       }
       g2.w_resident = 0;
       g2.a_stages = (ntile == 256 || g2.mb > 1) ? 2 : 3;
+      // pair: half-size weight stages leave room; 1x1 convs (one 512-cycle MMA group per A stage) want the deeper A ring
+      if (pair) { g2.a_stages = max_taps == 1 ? 4 : 2; if (const char* v = std::getenv("MB200_PAIR_A")) g2.a_stages = std::atoi(v); }
       // narrow tiles pair two taps per ring stage: half as many producer/issuer handshakes per tensor-pipe cycle
       g2.wt = (w_tile <= 16 * 1024 && max_taps >= 2) ? 2 : 1;
       g2.w_stages = std::min(8, (budget - g2.a_stages * a_bytes) / (g2.wt * w_tile));
@@ -469,7 +479,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     }
     L.tmA8[0] = tmap_act(s0.p, s0.ld, s0.rows, B, W.kc, 8, adt);
     L.tmA8[1] = s1 ? tmap_act(s1->p, s1->ld, s1->rows, B, W.kc, 8, adt) : L.tmA8[0];
-    L.grid = std::min(g2.total_tiles, num_sms);
+    L.grid = pair ? 2 * std::min((g2.total_tiles + 1) / 2, num_sms / 2) : std::min(g2.total_tiles, num_sms);
     L.pdl = use_pdl;
   }
   const int dtype = cfg.dtype;
