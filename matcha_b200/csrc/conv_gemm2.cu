@@ -354,11 +354,12 @@ static cudaError_t launch_umma2_inst(const ConvLaunch& L, cudaStream_t st) {
 template <int NTILE, int KC, int MB, int EG, typename T>
 static cudaError_t launch_umma2_feat(const ConvLaunch& L, cudaStream_t st) {
   const uint32_t need = epi_features(L.e);
-  if constexpr (NTILE == 256 && MB == 1) {
+  if constexpr ((NTILE == 256 && MB == 1) || (NTILE == 128 && MB == 2 && EG == 2)) {
     if (L.g2.pair) {
 #define MB_TRYP(CLS) if ((need & ~(CLS)) == 0) return launch_umma2_inst<NTILE, KC, MB, EG, T, (CLS), true>(L, st)
-      if constexpr (EG == 3) { MB_TRYP(kFC_STATS); MB_TRYP(kFC_SNAKE); MB_TRYP(kFC_RESLN); MB_TRYP(kFC_GNLN); }
-      if constexpr (EG == 2) { MB_TRYP(kFC_VOC); MB_TRYP(kFC_RESMASK); }
+      if constexpr (NTILE == 256 && EG == 3) { MB_TRYP(kFC_STATS); MB_TRYP(kFC_SNAKE); MB_TRYP(kFC_RESLN); MB_TRYP(kFC_GNLN); }
+      if constexpr (EG == 2) { MB_TRYP(kFC_VOC); }
+      if constexpr (NTILE == 256 && EG == 2) { MB_TRYP(kFC_RESMASK); }
 #undef MB_TRYP
       return launch_umma2_inst<NTILE, KC, MB, EG, T, kF_ALL, true>(L, st);
     }

@@ -45,7 +45,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_FUSE_RQ")) fuse_rq = std::atoi(v);
   if (const char* v = std::getenv("MB200_ATTN")) attn_umma = std::strcmp(v, "mma") != 0;
   if (const char* v = std::getenv("MB200_FP32")) fp32_split = std::strcmp(v, "simt") != 0;
-  if (const char* v = std::getenv("MB200_PAIR")) use_pair = std::atoi(v) != 0;
+  if (const char* v = std::getenv("MB200_PAIR")) use_pair = std::atoi(v);   // 0 off, 1 N = 256 layers only, 2 (default) also the N = 128 layers
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
 
@@ -336,7 +336,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     // CTA pairs (cta_group::2) for the N = 256 layers with streamed weights: each CTA of a pair fetches half of the weight
     // rows (conv_gemm2.cu).  Needs one N tile and one phase (both CTAs of a pair then always want the same weights).
     const long w_total_bytes = static_cast<long>(W.n_phases) * W.N * Kw * 2;
-    const bool pair = use_pair && kernel_version >= 2 && ntile == 256 && W.N == 256 && W.n_phases == 1 && W.kc == 64 &&
+    const bool pair = use_pair && kernel_version >= 2 && (ntile == 256 || (ntile == 128 && T_out >= 2048 && use_pair > 1)) && W.N == ntile && W.n_phases == 1 && W.kc == 64 &&
                       (split || w_total_bytes > 100 * 1024) && static_cast<long>(B) * ((T_out + 127) / 128) >= 2;
     const int wbox = pair ? ntile / 2 : ntile;
     if (split) L.tmW = (ntile == W.ntile && !pair) ? W.tm3 : tmap_w(W.w3, Kw, W.n_phases * W.N, W.kc, wbox, MB200_BF16);
