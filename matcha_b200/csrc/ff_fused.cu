@@ -39,7 +39,11 @@ constexpr int kFFBarBytes = 512;
 
 int ff_fused_smem_bytes() { return 1024 + kFFXBytes + 2 * kFFMidBytes + kFFStages * kFFStage + kFFBarBytes; }
 
-template <typename T>
+// PAIR: two CTAs of a cluster run as one tcgen05 cta_group::2 unit (see conv_gemm2.cu): each keeps its own x tile, mid
+// chunks and accumulators, but every weight box is split between the two CTAs' shared memories (W1: 64 of the chunk's 128
+// hidden channels each, W2 / Wo: 128 of the 256 output channels each), so a CTA streams half of the 1 MB of weights a tile
+// needs from L2.  The even CTA issues all MMAs (M = 256); barriers the issuer waits on collect arrivals from both CTAs.
+template <typename T, bool PAIR>
 __global__ void __launch_bounds__(320, 1)
 ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
                 const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmWo,
@@ -49,6 +53,8 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   uint8_t* x_tile = smem;
   uint8_t* mid = x_tile + kFFXBytes;
   uint8_t* w_ring = mid + 2 * kFFMidBytes;
+  constexpr int STAGE = PAIR ? kFFStage / 2 : kFFStage;   // this CTA's share of one weight ring stage
+  constexpr uint32_t WBOX16 = (STAGE / 2) >> 4;            // second W1 box of a stage, in descriptor units
   uint64_t* bars = reinterpret_cast<uint64_t*>(w_ring + kFFStages * kFFStage);
   uint64_t* x_full = bars;             // [1]
   uint64_t* x_empty = bars + 1;        // [1]
@@ -67,27 +73,43 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   const bool pre = g.pre != 0;         // tmX then maps the attention output [rows][128] instead of the LayerNorm output
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nt_cta = (g.total_tiles > static_cast<int>(blockIdx.x))
-                         ? (g.total_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+  const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
+  // work units: tiles, or pairs of tiles (2u, 2u + 1); the odd CTA of the last pair may get a tile past the end, which is
+  // all padding (TMA zero fill, every global access is bounded by g.rows)
+  const int units = PAIR ? (g.total_tiles + 1) / 2 : g.total_tiles;
+  const int u0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int ustep = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int nt_cta = units > u0 ? (units - 1 - u0) / ustep + 1 : 0;
+  auto tile_of = [&](int n) { const int u = u0 + n * ustep; return PAIR ? 2 * u + rank : u; };
+  auto arrive_mma = [](uint64_t* bar) { if constexpr (PAIR) mbar_arrive_leader(bar); else mbar_arrive(bar); };   // barriers the issuer waits on
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
     tma_prefetch_desc(&tmWo);
-    mbar_init(x_full, pre ? 8 : 1); mbar_init(x_empty, 1);
+    constexpr int EW = PAIR ? 16 : 8;   // epilogue warps that arrive on an issuer-side barrier
+    mbar_init(x_full, pre ? EW : 1); mbar_init(x_empty, 1);
     mbar_init(att_full, 1); mbar_init(att_empty, 1); mbar_init(t0_full, 1);
     for (int s = 0; s < kFFStages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], 8);
-      mbar_init(&mid_full[s], 8); mbar_init(&mid_empty[s], 1);
+      mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], EW);
+      mbar_init(&mid_full[s], EW); mbar_init(&mid_empty[s], 1);
     }
-    mbar_init(t2_full, 1); mbar_init(t2_empty, 8);
+    mbar_init(t2_full, 1); mbar_init(t2_empty, EW);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  if (warp == 1) { if constexpr (PAIR) tmem_alloc_pair<512>(tmem_slot); else tmem_alloc<512>(tmem_slot); }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // loads: in a pair the bytes of both CTAs are counted on the leader's barrier, which only the leader arms
+  auto expect = [&](uint64_t* bar, uint32_t bytes) { if constexpr (PAIR) { if (rank == 0) mbar_expect_tx(bar, 2 * bytes); } else mbar_expect_tx(bar, bytes); };
+  auto load2 = [](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+    if constexpr (PAIR) tma_load_2d_pair(dst, m, bar, c0, c1); else tma_load_2d(dst, m, bar, c0, c1);
+  };
+  auto load3 = [](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+    if constexpr (PAIR) tma_load_3d_pair(dst, m, bar, c0, c1, c2); else tma_load_3d(dst, m, bar, c0, c1, c2);
+  };
 
   if (warp == 0) {
     // ================================================================= TMA producer
@@ -96,12 +118,12 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
     long long pw[2] = {0, 0};
     const long long pt0 = clock64();
     auto load_X = [&](int n) {
-      const int tile = blockIdx.x + n * gridDim.x;
+      const int tile = tile_of(n);
       FW(mbar_wait(x_empty, (n & 1) ^ 1), pw[0]);
       if (elect_one()) {
-        mbar_expect_tx(x_full, kFFXBytes);
+        expect(x_full, kFFXBytes);
 #pragma unroll
-        for (int kc = 0; kc < 4; ++kc) tma_load_3d(x_tile + kc * 16384, &tmX, x_full, kc * 64, tile * 128, 0);
+        for (int kc = 0; kc < 4; ++kc) load3(x_tile + kc * 16384, &tmX, x_full, kc * 64, tile * 128, 0);
       }
       __syncwarp();
     };
@@ -109,9 +131,10 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       for (int s = 0; s < 2; ++s) {
         FW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
         if (elect_one()) {
-          mbar_expect_tx(&w_full[ws], kFFStage);
-          tma_load_2d(w_ring + ws * kFFStage, &tmW1, &w_full[ws], (2 * s) * 64, j * 128);
-          tma_load_2d(w_ring + ws * kFFStage + 16384, &tmW1, &w_full[ws], (2 * s + 1) * 64, j * 128);
+          expect(&w_full[ws], STAGE);        // pair: this CTA's 64 of the chunk's 128 hidden channels
+          const int n0 = j * 128 + (PAIR ? rank * 64 : 0);
+          load2(w_ring + ws * STAGE, &tmW1, &w_full[ws], (2 * s) * 64, n0);
+          load2(w_ring + ws * STAGE + STAGE / 2, &tmW1, &w_full[ws], (2 * s + 1) * 64, n0);
         }
         __syncwarp();
         if (++ws == kFFStages) { ws = 0; wph ^= 1; }
@@ -121,27 +144,27 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       for (int s = 0; s < 2; ++s) {
         FW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
         if (elect_one()) {
-          mbar_expect_tx(&w_full[ws], kFFStage);
-          tma_load_2d(w_ring + ws * kFFStage, &tmW2, &w_full[ws], j * 128 + s * 64, 0);
+          expect(&w_full[ws], STAGE);        // pair: this CTA's 128 of the 256 output channels
+          load2(w_ring + ws * STAGE, &tmW2, &w_full[ws], j * 128 + s * 64, PAIR ? rank * 128 : 0);
         }
         __syncwarp();
         if (++ws == kFFStages) { ws = 0; wph ^= 1; }
       }
     };
     auto load_pre = [&](int n) {   // attention tile [128][128] -> mid[0] (two K chunks), Wo [256][128] -> two ring stages
-      const int tile = blockIdx.x + n * gridDim.x;
+      const int tile = tile_of(n);
       FW(mbar_wait(att_empty, (n & 1) ^ 1), pw[0]);
       if (elect_one()) {
-        mbar_expect_tx(att_full, kFFMidBytes);
-        tma_load_3d(mid, &tmX, att_full, 0, tile * 128, 0);
-        tma_load_3d(mid + 16384, &tmX, att_full, 64, tile * 128, 0);
+        expect(att_full, kFFMidBytes);
+        load3(mid, &tmX, att_full, 0, tile * 128, 0);
+        load3(mid + 16384, &tmX, att_full, 64, tile * 128, 0);
       }
       __syncwarp();
       for (int s = 0; s < 2; ++s) {
         FW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
         if (elect_one()) {
-          mbar_expect_tx(&w_full[ws], kFFStage);
-          tma_load_2d(w_ring + ws * kFFStage, &tmWo, &w_full[ws], s * 64, 0);
+          expect(&w_full[ws], STAGE);
+          load2(w_ring + ws * STAGE, &tmWo, &w_full[ws], s * 64, PAIR ? rank * 128 : 0);
         }
         __syncwarp();
         if (++ws == kFFStages) { ws = 0; wph ^= 1; }
@@ -156,9 +179,15 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
     }
     if (g.dbg_out && lane == 0) { long long* o = g.dbg_out + blockIdx.x * 16; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; }
   } else if (warp == 1) {
-    // ================================================================= MMA issuer
+    // ================================================================= MMA issuer (pair: the leader's only)
+    if (rank == 0) {
     constexpr int fmt = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
-    constexpr uint32_t idesc1 = umma_idesc_f16(fmt, 128, 128), idesc2 = umma_idesc_f16(fmt, 128, 256);
+    constexpr int MM = PAIR ? 256 : 128;
+    constexpr uint32_t idesc1 = umma_idesc_f16(fmt, MM, 128), idesc2 = umma_idesc_f16(fmt, MM, 256);
+    auto umma_f16_lohi = [](uint32_t d, uint32_t a, uint32_t b, uint32_t hi, uint32_t id, uint32_t acc) {
+      if constexpr (PAIR) mb::umma_f16_lohi_pair(d, a, b, hi, id, acc); else mb::umma_f16_lohi(d, a, b, hi, id, acc);
+    };
+    auto umma_commit = [](uint64_t* bar) { if constexpr (PAIR) mb::umma_commit_pair(bar); else mb::umma_commit(bar); };
     const uint32_t desc_hi = static_cast<uint32_t>(umma_smem_desc<128>(0) >> 32);
     const uint32_t x_lo = static_cast<uint32_t>(umma_smem_desc<128>(smem_u32(x_tile)));
     const uint32_t mid_lo = static_cast<uint32_t>(umma_smem_desc<128>(smem_u32(mid)));
@@ -177,7 +206,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
           FW(mbar_wait(&w_full[ws], wph), iw[2]);
           tc_fence_after();
           if (elect_one()) {
-            const uint32_t w = w_lo0 + ws * (kFFStage >> 4), a = mid_lo + s * 1024u;
+            const uint32_t w = w_lo0 + ws * (STAGE >> 4), a = mid_lo + s * 1024u;
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_f16_lohi(tmem_base, a + 2 * k, w + 2 * k, desc_hi, idesc2, (s | k) != 0 ? 1u : 0u);
             umma_commit(&w_empty[ws]);
@@ -198,10 +227,10 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
             FW(mbar_wait(&w_full[ws], wph), iw[2]);
             tc_fence_after();
             if (elect_one()) {
-              const uint32_t w = w_lo0 + ws * (kFFStage >> 4);
+              const uint32_t w = w_lo0 + ws * (STAGE >> 4);
 #pragma unroll
               for (int c = 0; c < 2; ++c) {
-                const uint32_t a = x_lo + (2 * s + c) * 1024u, wc = w + c * 1024u;
+                const uint32_t a = x_lo + (2 * s + c) * 1024u, wc = w + c * WBOX16;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_f16_lohi(dtm, a + 2 * k, wc + 2 * k, desc_hi, idesc1, (s | c | k) != 0 ? 1u : 0u);
               }
@@ -221,7 +250,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
             FW(mbar_wait(&w_full[ws], wph), iw[2]);
             tc_fence_after();
             if (elect_one()) {
-              const uint32_t w = w_lo0 + ws * (kFFStage >> 4);
+              const uint32_t w = w_lo0 + ws * (STAGE >> 4);
               const uint32_t a = mid_lo + ms * (kFFMidBytes >> 4) + s * 1024u;
 #pragma unroll
               for (int k = 0; k < 4; ++k) umma_f16_lohi(dtm, a + 2 * k, w + 2 * k, desc_hi, idesc2, (jm | s | k) != 0 ? 1u : 0u);
@@ -235,6 +264,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       }
     }
     if (g.dbg_out && lane == 0) { long long* o = g.dbg_out + blockIdx.x * 16; o[3] = clock64() - it0; for (int i = 0; i < 5; ++i) o[4 + i] = iw[i]; }
+    }
   } else {
     // ================================================================= E1 (SnakeBeta -> mid) and E2 (-> global)
     const int lane_grp = warp & 3, half = (warp - 2) >> 2;
@@ -263,7 +293,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       pp[4] = __ldg(g.snake_invb + col + lane); pp[5] = __ldg(g.snake_invb + col + 32 + lane);
     };
     for (int n = 0; n < nt_cta; ++n) {
-      const int tile = blockIdx.x + n * gridDim.x;
+      const int tile = tile_of(n);
       if (pre) {
         // ---- E0: hid = att Wo^T + bo + res -> global; x = LayerNorm(hid) -> x tile (A operand of M1).  Same arithmetic as
         // the unfused out-projection epilogue: row sums from the fp32 values, normalisation of the ROUNDED stored values.
@@ -311,7 +341,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         __syncwarp();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) { mbar_arrive(&t1_empty[0]); mbar_arrive(&t1_empty[1]); }   // TMEM columns 0..255 are free again
+        if (lane == 0) { arrive_mma(&t1_empty[0]); arrive_mma(&t1_empty[1]); }   // TMEM columns 0..255 are free again
         // row statistics: the other half of the row belongs to the partner warp (same TMEM lane quarter); mid[0] (the
         // attention tile, dead once M0 completed) carries the exchange
         float2* xch = reinterpret_cast<float2*>(mid);
@@ -336,7 +366,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         }
         fence_proxy_async();
         __syncwarp();
-        if (lane == 0) mbar_arrive(x_full);
+        if (lane == 0) arrive_mma(x_full);
       }
 #pragma unroll 1
       for (int j = 0; j < 8; ++j) {
@@ -380,7 +410,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         tc_fence_before();
         fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async-proxy reads
         __syncwarp();
-        if (lane == 0) { mbar_arrive(&t1_empty[slot]); mbar_arrive(&mid_full[slot]); }
+        if (lane == 0) { arrive_mma(&t1_empty[slot]); arrive_mma(&mid_full[slot]); }
       }
       // ---- E2: this warp's 128 output channels [128 half, +128) of the lane's row.  The residual row segment (256 B)
       // is requested before the accumulator barrier, so its latency hides behind the last chunk's MMAs.
@@ -424,7 +454,7 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(t2_empty);     // the accumulators are read: the next tile's MMAs may start
+        if (lane == 0) arrive_mma(t2_empty);     // the accumulators are read: the next tile's MMAs may start
         warp_rows_s2g<T>(x_tile, reinterpret_cast<T*>(g.out), row0, g.rows, r0, half, lane);
         __syncwarp();
         continue;
@@ -461,26 +491,40 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(t2_empty);
+      if (lane == 0) arrive_mma(t2_empty);
     }
     if (g.dbg_out && warp == 2 && lane == 0) { long long* o = g.dbg_out + blockIdx.x * 16; o[9] = clock64() - et0; for (int i = 0; i < 3; ++i) o[10 + i] = ew[i]; o[13] = nt_cta; }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<512>(tmem_base);
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
+  if (warp == 1) { if constexpr (PAIR) tmem_dealloc_pair<512>(tmem_base); else tmem_dealloc<512>(tmem_base); }
 }
 
-template <typename T>
-cudaError_t launch_ff_fused(const FFLaunch& L, cudaStream_t st) {
-  auto kern = ff_fused_kernel<T>;
+template <typename T, bool PAIR>
+static cudaError_t launch_ff_fused_inst(const FFLaunch& L, cudaStream_t st) {
+  auto kern = ff_fused_kernel<T, PAIR>;
   static PerDeviceOnce configured;
   if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (err != cudaSuccess) return err;
     configured.mark();
   }
-  kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmX, L.tmW1, L.tmW2, L.tmWo, L.g);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(L.grid);
+  cfg.blockDim = dim3(320);
+  cfg.dynamicSmemBytes = L.smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = PAIR ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, L.tmX, L.tmW1, L.tmW2, L.tmWo, L.g);
+}
+
+template <typename T>
+cudaError_t launch_ff_fused(const FFLaunch& L, cudaStream_t st) {
+  return L.pair ? launch_ff_fused_inst<T, true>(L, st) : launch_ff_fused_inst<T, false>(L, st);
 }
 template cudaError_t launch_ff_fused<__nv_bfloat16>(const FFLaunch&, cudaStream_t);
 template cudaError_t launch_ff_fused<__half>(const FFLaunch&, cudaStream_t);

@@ -48,6 +48,7 @@ struct FFLaunch {
   CUtensorMap tmX, tmW1, tmW2, tmWo;   // tmX: LayerNorm output [rows][256], or the attention output [rows][128] with the pre-stage
   FFGeom g;
   int smem_bytes, grid;
+  int pair;                            // CTA pairs (cta_group::2): weight boxes split between the two CTAs of a cluster
 };
 struct RQLaunch {
   CUtensorMap tmA0, tmA1, tmWres, tmWqkv;

@@ -45,6 +45,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_FUSE_RQ")) fuse_rq = std::atoi(v);
   if (const char* v = std::getenv("MB200_ATTN")) attn_umma = std::strcmp(v, "mma") != 0;
   if (const char* v = std::getenv("MB200_FP32")) fp32_split = std::strcmp(v, "simt") != 0;
+  if (const char* v = std::getenv("MB200_FF_PAIR")) ff_pair = std::atoi(v) != 0;
   if (const char* v = std::getenv("MB200_PAIR")) use_pair = std::atoi(v);   // 0 off, 1 N = 256 layers only, 2 (default) also the N = 128 layers
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
@@ -599,21 +600,22 @@ Launch Plan::ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, c
       std::fprintf(stderr, "[ff probe] rows=%ld tiles=%d\n", rows, L.g.total_tiles);
     }
   }
-  L.tmW1 = tmap_w(W1.w, 256, 1024, 64, 128);
-  L.tmW2 = tmap_w(W2.w, 1024, 256, 64, 256);
+  L.pair = (ff_pair && L.g.total_tiles >= 2) ? 1 : 0;
+  L.tmW1 = tmap_w(W1.w, 256, 1024, 64, L.pair ? 64 : 128);
+  L.tmW2 = tmap_w(W2.w, 1024, 256, 64, L.pair ? 128 : 256);
   if (Wo) {
     if (Wo->N != 256 || Wo->K_total != 128 || Wo->kc != 64 || Wo->n_phases != 1 || !Wo->bias || !res_in || !ln_g || !ln_b)
       throw Error("ff_op: the pre-stage needs a packed 128 -> 256 projection with bias, its residual and LayerNorm parameters");
     L.g.pre = 1; L.g.bias_o = Wo->bias; L.g.res_in = res_in; L.g.hid_out = resid; L.g.ln_g = ln_g; L.g.ln_b = ln_b;
     L.tmX = tmap_act(x, 128, static_cast<int>(rows), 1, 64);
-    L.tmWo = tmap_w(Wo->w, 128, 256, 64, 256);
+    L.tmWo = tmap_w(Wo->w, 128, 256, 64, L.pair ? 128 : 256);
   } else {
     L.g.pre = 0;
     L.tmX = tmap_act(x, 256, static_cast<int>(rows), 1, 64);
     L.tmWo = L.tmW2;
   }
   L.smem_bytes = ff_fused_smem_bytes();
-  L.grid = std::min(L.g.total_tiles, num_sms);
+  L.grid = L.pair ? 2 * std::min((L.g.total_tiles + 1) / 2, num_sms / 2) : std::min(L.g.total_tiles, num_sms);
   const int dtype = cfg.dtype;
   Launch op([L, dtype](cudaStream_t st) -> cudaError_t {
     return dtype == MB200_BF16 ? launch_ff_fused<__nv_bfloat16>(L, st) : launch_ff_fused<__half>(L, st);
