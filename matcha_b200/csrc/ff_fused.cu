@@ -286,6 +286,15 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (tid & 7) * 32));
       }
     }
+    // Pair mode has 48 KB of shared memory to spare (half-size weight stages): the 3 x 1024 per-channel SnakeBeta parameters
+    // live there for the whole kernel and E1 reads them with broadcast LDS.128 (6 per 8 channels) instead of three warp
+    // shuffles per element (192 per chunk and lane: the shuffle pipe, not the MMAs, set E1's pace).
+    float* ptab = reinterpret_cast<float*>(w_ring + kFFStages * STAGE);
+    if constexpr (PAIR) {
+      const int tid = threadIdx.x - 64;
+      for (int i = tid; i < 3 * 1024; i += 256) ptab[i] = __ldg((i < 1024 ? g.bias1 : i < 2048 ? g.snake_a : g.snake_invb) + (i & 1023));
+      named_bar_sync(5, 256);
+    }
     float pc[6], pn[6];
     auto ldpar = [&](int col, float (&pp)[6]) {   // lane l: channels col + l and col + 32 + l of the three arrays
       pp[0] = __ldg(g.bias1 + col + lane); pp[1] = __ldg(g.bias1 + col + 32 + lane);
@@ -378,8 +387,10 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         // 48 broadcast LDG.128 per chunk issued one 8-channel group ahead, these loads were the kernel's dominant stall
         // (long scoreboard: half of all warp-stall samples, profiles/r01_ncu_full_ff_fused.txt) - with ~226 KB of the SM
         // carved out as shared memory the L1 does not hold even 13 KB of parameters.
-        if (j == 0 && n == 0) ldpar(nb, pc);
-        ldpar(((j + 1) & 7) * 128 + half * 64, pn);
+        if constexpr (!PAIR) {
+          if (j == 0 && n == 0) ldpar(nb, pc);
+          ldpar(((j + 1) & 7) * 128 + half * 64, pn);
+        }
         FW(mbar_wait(&t1_full[slot], (jj >> 1) & 1), ew[0]);
         tc_fence_after();
         float acc[2][32];
@@ -391,22 +402,38 @@ ff_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         for (int q = 0; q < 8; ++q) {
           float v[8];
           const float* a = acc[q >> 2] + 8 * (q & 3);
+          if constexpr (PAIR) {
+            const float4* tb = reinterpret_cast<const float4*>(ptab + nb + 8 * q);
+            const float4 b0 = tb[0], b1 = tb[1], a0 = tb[256], a1 = tb[257], i0 = tb[512], i1 = tb[513];
+            const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            const float pa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float pb[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            const int src = (8 * q + ch) & 31;
-            const float bv = __shfl_sync(0xffffffffu, pc[q >> 2], src);
-            const float pa = __shfl_sync(0xffffffffu, pc[2 + (q >> 2)], src);
-            const float pb = __shfl_sync(0xffffffffu, pc[4 + (q >> 2)], src);
-            v[ch] = a[ch] + bv;
-            const float sn = __sinf(v[ch] * pa);
-            v[ch] = fmaf(pb * sn, sn, v[ch]);
+            for (int ch = 0; ch < 8; ++ch) {
+              v[ch] = a[ch] + bv[ch];
+              const float sn = __sinf(v[ch] * pa[ch]);
+              v[ch] = fmaf(pb[ch] * sn, sn, v[ch]);
+            }
+          } else {
+#pragma unroll
+            for (int ch = 0; ch < 8; ++ch) {
+              const int src = (8 * q + ch) & 31;
+              const float bv = __shfl_sync(0xffffffffu, pc[q >> 2], src);
+              const float pa = __shfl_sync(0xffffffffu, pc[2 + (q >> 2)], src);
+              const float pb = __shfl_sync(0xffffffffu, pc[4 + (q >> 2)], src);
+              v[ch] = a[ch] + bv;
+              const float sn = __sinf(v[ch] * pa);
+              v[ch] = fmaf(pb * sn, sn, v[ch]);
+            }
           }
           uint32_t off = static_cast<uint32_t>(r * 128 + q * 16);
           off ^= ((off >> 7) & 7u) << 4;
           *reinterpret_cast<uint4*>(mid_c + off) = pack8<T>(v);
         }
+        if constexpr (!PAIR) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) pc[k] = pn[k];
+          for (int k = 0; k < 6; ++k) pc[k] = pn[k];
+        }
         tc_fence_before();
         fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async-proxy reads
         __syncwarp();
