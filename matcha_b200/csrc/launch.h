@@ -42,6 +42,7 @@ struct PairLaunch {
   PairGeom g;
   EpiParams e;        // c2's epilogue (bias2, residual, branch sum, scale, output)
   int C, mb, smem_bytes, grid;
+  int cta_pair;       // CTA pairs (cta_group::2): weight tiles split between the two CTAs of a cluster
 };
 
 struct FFLaunch {

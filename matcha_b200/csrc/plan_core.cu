@@ -46,6 +46,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_ATTN")) attn_umma = std::strcmp(v, "mma") != 0;
   if (const char* v = std::getenv("MB200_FP32")) fp32_split = std::strcmp(v, "simt") != 0;
   if (const char* v = std::getenv("MB200_FF_PAIR")) ff_pair = std::atoi(v) != 0;
+  if (const char* v = std::getenv("MB200_RES_PAIR")) res_pair = std::atoi(v) != 0;
   if (const char* v = std::getenv("MB200_PAIR")) use_pair = std::atoi(v);   // 0 off, 1 N = 256 layers only, 2 (default) also the N = 128 layers
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
@@ -518,7 +519,7 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
   PairLaunch L{};
   L.C = C;
   L.mb = C == 64 ? 2 : 4;
-  const int R = 128 * L.mb, rowb = C * 2, w_tile = C * rowb;
+  const int R = 128 * L.mb, rowb = C * 2, w_tile_full = C * rowb;
   PairGeom& g = L.g;
   g.B = B; g.T = T; g.K = K; g.dil = dil;
   g.S = R - (K - 1);
@@ -543,6 +544,9 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
   // The mid tile is double-buffered when that still leaves two x stages and a usable weight ring: E1 of tile n+1 then
   // overlaps c2 of tile n (the short-kernel steps are bound by that chain).
   const int tail_bytes = 1024 + 512 + 8 * 4608;
+  // CTA pairs (cta_group::2): each CTA of a 2-CTA cluster holds half of every weight tile's output channels
+  L.cta_pair = (res_pair && g.total_tiles >= 2) ? 1 : 0;
+  const int w_tile = L.cta_pair ? w_tile_full / 2 : w_tile_full;
   const int w_all = 2 * K * w_tile;
   int want_mid = 2;
   if (const char* v = std::getenv("MB200_PAIR_MID")) want_mid = std::atoi(v) == 1 ? 1 : 2;
@@ -567,9 +571,9 @@ Launch Plan::pair_op(const PackedW& W1, const PackedW& W2, int dil, const void* 
   L.e = e;
   L.tmA = tmap_act(in, C, T, B, C);
   L.tmA8 = tmap_act(in, C, T, B, C, 8);
-  L.tmW1 = W1.tm;
-  L.tmW2 = W2.tm;
-  L.grid = std::min(g.total_tiles, num_sms);
+  L.tmW1 = L.cta_pair ? tmap_w(W1.w, W1.K_total, C, C, C / 2) : W1.tm;
+  L.tmW2 = L.cta_pair ? tmap_w(W2.w, W2.K_total, C, C, C / 2) : W2.tm;
+  L.grid = L.cta_pair ? 2 * std::min((g.total_tiles + 1) / 2, num_sms / 2) : std::min(g.total_tiles, num_sms);
   const int dtype = cfg.dtype;
   Launch op([L, dtype](cudaStream_t st) -> cudaError_t {
     return dtype == MB200_BF16 ? launch_resblock_pair<__nv_bfloat16>(L, st) : launch_resblock_pair<__half>(L, st);

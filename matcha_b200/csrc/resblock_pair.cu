@@ -29,13 +29,15 @@ constexpr int kPairBarBytes = 512;
 #define PW(stmt, acc) do { if (g.dbg_out) { const long long pw_a = clock64(); stmt; acc += clock64() - pw_a; } else { stmt; } } while (0)
 }
 
-template <int C, int MB, typename T>
+// PAIR: two CTAs of a cluster as one tcgen05 cta_group::2 unit (conv_gemm2.cu): each CTA runs its own tile, every weight
+// tile is split between the two CTAs (C / 2 output channels each), the even CTA issues all MMAs with M = 256.
+template <int C, int MB, typename T, bool PAIR>
 __global__ void __launch_bounds__(448, 1)
 resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA8,
                      const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2,
                      const __grid_constant__ PairGeom g, const __grid_constant__ EpiParams e) {
   constexpr int ROWB = C * 2;             // bytes per activation row = one swizzle span (128 B / 64 B)
-  constexpr int W_TILE = C * ROWB;        // one tap of one conv
+  constexpr int W_TILE = (PAIR ? C / 2 : C) * ROWB;   // one tap of one conv: the output channels THIS CTA holds
   constexpr int W_STAGE = 2 * W_TILE;     // streamed weights: two taps per ring stage
   constexpr int SLOT = MB * C;            // TMEM columns of one accumulator buffer
   constexpr int R = 128 * MB;
@@ -68,24 +70,39 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint8_t* stage_base = tail + kPairBarBytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nt_cta = (g.total_tiles > static_cast<int>(blockIdx.x))
-                         ? (g.total_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+  const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
+  // work units: tiles, or pairs of tiles (2u, 2u + 1); the odd CTA of the last pair may get a tile past the end (a ghost:
+  // its loads are out of range = zero fill, it stores nothing)
+  const int units = PAIR ? (g.total_tiles + 1) / 2 : g.total_tiles;
+  const int u0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int ustep = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int nt_cta = units > u0 ? (units - 1 - u0) / ustep + 1 : 0;
+  auto tile_of = [&](int n) { const int u = u0 + n * ustep; return PAIR ? 2 * u + rank : u; };
+  auto arrive_mma = [](uint64_t* bar) { if constexpr (PAIR) mbar_arrive_leader(bar); else mbar_arrive(bar); };   // barriers the issuer waits on
+  auto expect = [&](uint64_t* bar, uint32_t bytes) { if constexpr (PAIR) { if (rank == 0) mbar_expect_tx(bar, 2 * bytes); } else mbar_expect_tx(bar, bytes); };
+  auto load2 = [](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+    if constexpr (PAIR) tma_load_2d_pair(dst, m, bar, c0, c1); else tma_load_2d(dst, m, bar, c0, c1);
+  };
+  auto load3 = [](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+    if constexpr (PAIR) tma_load_3d_pair(dst, m, bar, c0, c1, c2); else tma_load_3d(dst, m, bar, c0, c1, c2);
+  };
+  const int wrow0 = PAIR ? rank * (C / 2) : 0;   // first output channel of this CTA's weight rows
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmA8); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
     for (int s = 0; s < 4; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < 8; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], 4);
-      mbar_init(&t2_full[s], 1); mbar_init(&t2_empty[s], 4 * EG);
+      mbar_init(&t1_full[s], 1); mbar_init(&t1_empty[s], PAIR ? 8 : 4);
+      mbar_init(&t2_full[s], 1); mbar_init(&t2_empty[s], (PAIR ? 8 : 4) * EG);
     }
-    for (int s = 0; s < 2; ++s) { mbar_init(&mid_full[s], 4); mbar_init(&mid_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&mid_full[s], PAIR ? 8 : 4); mbar_init(&mid_empty[s], 1); }
     mbar_init(wres, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  if (warp == 1) { if constexpr (PAIR) tmem_alloc_pair<512>(tmem_slot); else tmem_alloc<512>(tmem_slot); }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -96,16 +113,16 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     long long pw[2] = {0, 0};
     const long long pt0 = clock64();
     auto load_A = [&](int n) {
-      const int tile = blockIdx.x + n * gridDim.x;
+      const int tile = tile_of(n);
       const int b = tile / g.tiles_per_b, t0 = (tile % g.tiles_per_b) * g.S;
       const int row0 = t0 - p - p * g.dil;
       PW(mbar_wait(&a_empty[as], aph ^ 1), pw[0]);
       if (elect_one()) {
         uint8_t* dst = a_ring + as * g.a_bytes;
-        mbar_expect_tx(&a_full[as], (R + 8 * g.extra) * ROWB);
+        expect(&a_full[as], (R + 8 * g.extra) * ROWB);
 #pragma unroll
-        for (int i = 0; i < MB; ++i) tma_load_3d(dst + i * 128 * ROWB, &tmA, &a_full[as], 0, row0 + 128 * i, b);
-        for (int x = 0; x < g.extra; ++x) tma_load_3d(dst + (R + 8 * x) * ROWB, &tmA8, &a_full[as], 0, row0 + R + 8 * x, b);
+        for (int i = 0; i < MB; ++i) load3(dst + i * 128 * ROWB, &tmA, &a_full[as], 0, row0 + 128 * i, b);
+        for (int x = 0; x < g.extra; ++x) load3(dst + (R + 8 * x) * ROWB, &tmA8, &a_full[as], 0, row0 + R + 8 * x, b);
       }
       __syncwarp();
       if (++as == g.a_stages) { as = 0; aph ^= 1; }
@@ -115,8 +132,8 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const int nt = min(2, K - 2 * st);
         PW(mbar_wait(&w_empty[ws], wph ^ 1), pw[1]);
         if (elect_one()) {
-          mbar_expect_tx(&w_full[ws], nt * W_TILE);
-          for (int j = 0; j < nt; ++j) tma_load_2d(w_base + ws * W_STAGE + j * W_TILE, tm, &w_full[ws], (2 * st + j) * C, 0);
+          expect(&w_full[ws], nt * W_TILE);
+          for (int j = 0; j < nt; ++j) load2(w_base + ws * W_STAGE + j * W_TILE, tm, &w_full[ws], (2 * st + j) * C, wrow0);
         }
         __syncwarp();
         if (++ws == g.w_stages) { ws = 0; wph ^= 1; }
@@ -124,9 +141,9 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     };
     if (g.w_resident) {
       if (elect_one()) {
-        mbar_expect_tx(wres, static_cast<uint32_t>(w_bytes));
-        for (int j = 0; j < K; ++j) tma_load_2d(w_base + j * W_TILE, &tmW1, wres, j * C, 0);
-        for (int j = 0; j < K; ++j) tma_load_2d(w_base + (K + j) * W_TILE, &tmW2, wres, j * C, 0);
+        expect(wres, static_cast<uint32_t>(w_bytes));
+        for (int j = 0; j < K; ++j) load2(w_base + j * W_TILE, &tmW1, wres, j * C, wrow0);
+        for (int j = 0; j < K; ++j) load2(w_base + (K + j) * W_TILE, &tmW2, wres, j * C, wrow0);
       }
       __syncwarp();
       for (int n = 0; n < nt_cta; ++n) load_A(n);
@@ -147,8 +164,13 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       o[11] = clock64() - pt0; o[12] = pw[0]; o[13] = pw[1]; o[14] = nt_cta;
     }
   } else if (warp == 1) {
-    // ================================================================= MMA issuer
-    constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 128, C);
+    // ================================================================= MMA issuer (pair: the leader's only)
+    if (rank == 0) {
+    constexpr uint32_t idesc = umma_idesc_f16(std::is_same<T, __nv_bfloat16>::value ? 1 : 0, PAIR ? 256 : 128, C);
+    auto umma_f16_lohi = [](uint32_t d, uint32_t a, uint32_t b, uint32_t hi, uint32_t id, uint32_t acc) {
+      if constexpr (PAIR) mb::umma_f16_lohi_pair(d, a, b, hi, id, acc); else mb::umma_f16_lohi(d, a, b, hi, id, acc);
+    };
+    auto umma_commit = [](uint64_t* bar) { if constexpr (PAIR) mb::umma_commit_pair(bar); else mb::umma_commit(bar); };
     constexpr uint32_t W16 = W_TILE >> 4, BLK16 = (128 * ROWB) >> 4, ROW16 = ROWB >> 4, WST16 = W_STAGE >> 4;
     const uint32_t desc_hi = static_cast<uint32_t>(umma_smem_desc<ROWB>(0) >> 32);
     const uint32_t a_lo0 = static_cast<uint32_t>(umma_smem_desc<ROWB>(smem_u32(a_ring)));
@@ -227,6 +249,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       o[0] = clock64() - pt0;
       for (int i = 0; i < 5; ++i) o[1 + i] = pw[i];
     }
+    }
   } else if (warp < 6) {
     // ================================================================= E1: accumulator 1 -> mid tile (A operand of c2)
     const int lane_grp = warp & 3;
@@ -235,7 +258,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const long long pt0 = clock64();
     constexpr int ITEMS = MB * (C / 32);
     for (int n = 0; n < nt_cta; ++n) {
-      const int tile = blockIdx.x + n * gridDim.x;
+      const int tile = tile_of(n);
       const int t0 = (tile % g.tiles_per_b) * g.S, m0 = t0 - p;
       const int slot = n & 1;
       const int ms = g.mid_stages == 2 ? slot : 0;
@@ -284,7 +307,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       tc_fence_before();
       fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async-proxy reads
       __syncwarp();
-      if (lane == 0) { mbar_arrive(&t1_empty[slot]); mbar_arrive(&mid_full[ms]); }
+      if (lane == 0) { arrive_mma(&t1_empty[slot]); arrive_mma(&mid_full[ms]); }
     }
     if (g.dbg_out && warp == 2 && lane == 0) {
       long long* o = g.dbg_out + blockIdx.x * 16;
@@ -298,16 +321,20 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     long long pw = 0;
     const long long pt0 = clock64();
     for (int n = 0; n < nt_cta; ++n) {
-      const int tile = blockIdx.x + n * gridDim.x;
+      const int tile = tile_of(n);
       const int b = tile / g.tiles_per_b, t0 = (tile % g.tiles_per_b) * g.S;
       const int slot = n & 1;
       const int t_lim = min(g.T, t0 + g.S);     // rows past S belong to the next tile
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16) + (2 + slot) * SLOT;
-      epilogue_tile3<C, MB, EG, T, kFC_VOC>(e, b, t0, t_lim, 0, 0, taddr, stg, nullptr, lane, lane_grp, grp, &t2_full[slot],
-                                   (n >> 1) & 1, g.dbg_out ? &pw : nullptr);
+      if (PAIR && tile >= g.total_tiles) {
+        mbar_wait(&t2_full[slot], (n >> 1) & 1);   // ghost tile: consume the phase, store nothing
+      } else {
+        epilogue_tile3<C, MB, EG, T, kFC_VOC>(e, b, t0, t_lim, 0, 0, taddr, stg, nullptr, lane, lane_grp, grp, &t2_full[slot],
+                                     (n >> 1) & 1, g.dbg_out ? &pw : nullptr);
+      }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&t2_empty[slot]);
+      if (lane == 0) arrive_mma(&t2_empty[slot]);
     }
     if (g.dbg_out && warp == 6 && lane == 0) {
       long long* o = g.dbg_out + blockIdx.x * 16;
@@ -315,27 +342,36 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<512>(tmem_base);
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
+  if (warp == 1) { if constexpr (PAIR) tmem_dealloc_pair<512>(tmem_base); else tmem_dealloc<512>(tmem_base); }
 }
 
-template <int C, int MB, typename T>
+template <int C, int MB, typename T, bool PAIR>
 static cudaError_t launch_pair_inst(const PairLaunch& L, cudaStream_t st) {
-  auto kern = resblock_pair_kernel<C, MB, T>;
+  auto kern = resblock_pair_kernel<C, MB, T, PAIR>;
   static PerDeviceOnce configured;
   if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (err != cudaSuccess) return err;
     configured.mark();
   }
-  kern<<<L.grid, 448, L.smem_bytes, st>>>(L.tmA, L.tmA8, L.tmW1, L.tmW2, L.g, L.e);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(L.grid);
+  cfg.blockDim = dim3(448);
+  cfg.dynamicSmemBytes = L.smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = PAIR ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, L.tmA, L.tmA8, L.tmW1, L.tmW2, L.g, L.e);
 }
 
 template <typename T>
 cudaError_t launch_resblock_pair(const PairLaunch& L, cudaStream_t st) {
-  if (L.C == 64 && L.mb == 2) return launch_pair_inst<64, 2, T>(L, st);
-  if (L.C == 32 && L.mb == 4) return launch_pair_inst<32, 4, T>(L, st);
+  if (L.C == 64 && L.mb == 2) return L.cta_pair ? launch_pair_inst<64, 2, T, true>(L, st) : launch_pair_inst<64, 2, T, false>(L, st);
+  if (L.C == 32 && L.mb == 4) return L.cta_pair ? launch_pair_inst<32, 4, T, true>(L, st) : launch_pair_inst<32, 4, T, false>(L, st);
   return cudaErrorInvalidConfiguration;
 }
 template cudaError_t launch_resblock_pair<__nv_bfloat16>(const PairLaunch&, cudaStream_t);
