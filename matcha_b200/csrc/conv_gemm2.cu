@@ -103,11 +103,19 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     // ================================================================= TMA producer (converged warp, elected issue)
     if (g.w_resident) {
       if (elect_one()) {
-        mbar_expect_tx(wres, static_cast<uint32_t>(w_bytes));
-        for (int pn = 0; pn < np; ++pn)   // pn = phase * n_tiles + n_tile
-          for (int kk = 0; kk < kchunks; ++kk)
-            tma_load_2d(w_base + static_cast<size_t>(pn * kchunks + kk) * W_TILE, &tmW, wres, kk * KC,
-                        (pn / g.n_tiles) * g.N + (pn % g.n_tiles) * NTILE);
+        if constexpr (PAIR) {   // this CTA's half of every weight tile; the leader's barrier counts both halves
+          if (rank == 0) mbar_expect_tx(wres, 2u * static_cast<uint32_t>(w_bytes));
+          for (int pn = 0; pn < np; ++pn)
+            for (int kk = 0; kk < kchunks; ++kk)
+              tma_load_2d_pair(w_base + static_cast<size_t>(pn * kchunks + kk) * W_TILE, &tmW, wres, kk * KC,
+                               (pn / g.n_tiles) * g.N + (pn % g.n_tiles) * NTILE + rank * (NTILE / 2));
+        } else {
+          mbar_expect_tx(wres, static_cast<uint32_t>(w_bytes));
+          for (int pn = 0; pn < np; ++pn)   // pn = phase * n_tiles + n_tile
+            for (int kk = 0; kk < kchunks; ++kk)
+              tma_load_2d(w_base + static_cast<size_t>(pn * kchunks + kk) * W_TILE, &tmW, wres, kk * KC,
+                          (pn / g.n_tiles) * g.N + (pn % g.n_tiles) * NTILE);
+        }
       }
       __syncwarp();
     }

@@ -47,6 +47,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_FP32")) fp32_split = std::strcmp(v, "simt") != 0;
   if (const char* v = std::getenv("MB200_FF_PAIR")) ff_pair = std::atoi(v) != 0;
   if (const char* v = std::getenv("MB200_RES_PAIR")) res_pair = std::atoi(v) != 0;
+  if (const char* v = std::getenv("MB200_PAIR_RESIDENT")) pair_resident = std::atoi(v) != 0;
   if (const char* v = std::getenv("MB200_PAIR")) use_pair = std::atoi(v);   // 0 off, 1 N = 256 layers only, 2 (default) also the N = 128 layers
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
 }
@@ -339,7 +340,7 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
     // rows (conv_gemm2.cu).  Needs one N tile and one phase (both CTAs of a pair then always want the same weights).
     const long w_total_bytes = static_cast<long>(W.n_phases) * W.N * Kw * 2;
     const bool pair = use_pair && kernel_version >= 2 && (ntile == 256 || (ntile == 128 && T_out >= 2048 && use_pair > 1)) && W.N == ntile && W.n_phases == 1 && W.kc == 64 &&
-                      (split || w_total_bytes > 100 * 1024) && static_cast<long>(B) * ((T_out + 127) / 128) >= 2;
+                      (split || w_total_bytes > 100 * 1024 || (pair_resident && T_out >= 2048)) && static_cast<long>(B) * ((T_out + 127) / 128) >= 2;
     const int wbox = pair ? ntile / 2 : ntile;
     if (split) L.tmW = (ntile == W.ntile && !pair) ? W.tm3 : tmap_w(W.w3, Kw, W.n_phases * W.N, W.kc, wbox, MB200_BF16);
     else L.tmW = (ntile == W.ntile && !pair) ? W.tm : tmap_w(W.w, W.K_total, W.n_phases * W.N, W.kc, wbox);
@@ -400,12 +401,14 @@ Launch Plan::conv_op(const PackedW& W, Src s0, const Src* s1, int B, int T_out, 
       const int tail_bytes = 1024 + 512 + 4 * eg * 4608 + 8192, budget = 227 * 1024 - tail_bytes;
       g2.eg = eg;
       // (split mode streams: the resident loader walks a weight row front to back, the three products revisit its hi half)
-      if (!split && !pair && w_total <= 100 * 1024 && (budget - w_total) / a_bytes >= 2) {
+      // pair: each CTA keeps half of the resident weights, which buys a third activation stage for the HBM-bound K = 3 convs
+      const long w_res = pair ? w_total / 2 : w_total;
+      if (!split && w_total <= 100 * 1024 && (budget - w_res) / a_bytes >= 2) {
         g2.w_resident = 1;
         g2.wt = 1;
-        g2.a_stages = std::min<long>(8, (budget - w_total) / a_bytes);
+        g2.a_stages = std::min<long>(8, (budget - w_res) / a_bytes);
         g2.w_stages = 0;
-        L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_total) + tail_bytes;
+        L.smem_bytes = static_cast<int>(g2.a_stages * a_bytes + w_res) + tail_bytes;
         return true;
       }
       g2.w_resident = 0;
