@@ -152,6 +152,7 @@ struct EpiParams {
   float2* stats_part;
   int* stats_cnt;
   int stats_slots;
+  int stats_nofinish;      // the consumer (gn_mish_kernel) adds the slots itself: no counter, no ordered sum at the end of this launch
   // Euler update fused into final_proj (flow_matching.py:79): x += dt * v ; second output = x * mask
   float* x_state;  int x_ld;  float dt;
   void* out0;  int out0_ld;  int out0_f32;  float out0_slope;   // main store; slope != 1 applies LeakyReLU

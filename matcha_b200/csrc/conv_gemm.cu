@@ -144,7 +144,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_con
   __syncthreads();
   __shared__ int stats_last;
   if (e.stats_out && (threadIdx.x & 31) == 0) gn_stats_publish();
-  if (e.stats_out) gn_stats_finish(e, g.B, gridDim.x * gridDim.y * gridDim.z, &stats_last);   // ordered GroupNorm sums by the last CTA
+  if (e.stats_out && !e.stats_nofinish) gn_stats_finish(e, g.B, gridDim.x * gridDim.y * gridDim.z, &stats_last);   // ordered GroupNorm sums by the last CTA
   if (warp == 1) tmem_dealloc<(NTILE < 32 ? 32 : NTILE)>(tmem_base);
 }
 
@@ -246,7 +246,7 @@ conv_gemm_simt_kernel(const T* __restrict__ a0, const T* __restrict__ a1, const 
   if (n0 < g.N) epilogue_chunk<T>(e, b, t, phase, n0, t < g.T_out, true, acc);  // n0 is warp-uniform
   __shared__ int stats_last;
   if (e.stats_out && (threadIdx.x & 31) == 0) gn_stats_publish();
-  if (e.stats_out) gn_stats_finish(e, g.B, gridDim.x * gridDim.y * gridDim.z, &stats_last);   // ordered GroupNorm sums by the last CTA
+  if (e.stats_out && !e.stats_nofinish) gn_stats_finish(e, g.B, gridDim.x * gridDim.y * gridDim.z, &stats_last);   // ordered GroupNorm sums by the last CTA
 }
 
 template <typename T>

@@ -318,7 +318,7 @@ conv_gemm_umma2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
   tc_fence_before();
   if constexpr (PAIR) cluster_sync_all(); else __syncthreads();   // pair: nothing of the peer's may still be in flight towards this CTA
   if constexpr ((F & kF_STATS) != 0) {
-    if (e.stats_out) gn_stats_finish(e, g.B, gridDim.x, reinterpret_cast<int*>(tmem_slot + 1));   // ordered GroupNorm sums by the last CTA to get here
+    if (e.stats_out && !e.stats_nofinish) gn_stats_finish(e, g.B, gridDim.x, reinterpret_cast<int*>(tmem_slot + 1));   // ordered GroupNorm sums by the last CTA to get here
   }
 #ifdef MB200_PROBE
   if (threadIdx.x == 0 && g.dbg_out) { g.dbg_out[blockIdx.x * 16 + 8] = clock64() - probe_k0; g.dbg_out[blockIdx.x * 16 + 9] = probe_k1 - probe_k0; }

@@ -20,60 +20,84 @@ template <> __device__ __forceinline__ float mish_sel<__half>(float x) {
 }
 template <> __device__ __forceinline__ float mish_sel<__nv_bfloat16>(float x) { return mish_sel<__half>(x); }
 
+// GroupNorm statistics arrive either finished ([B][8] (sum, sum of squares): part == nullptr) or as the producing conv's
+// per-32-row partial sums ([B][8][slots] float2): the CTA then adds the slots of the (utterance, group) pairs its rows need
+// in index order - a fixed order, so results stay bit-identical run to run - and the conv launch carries no ordered-sum
+// tail (gn_stats_finish: +5.7 us per launch).  A CTA handles kGnRows rows (<= kGnRows utterances, <= 8 * kGnRows pairs).
+constexpr int kGnRows = 32;
 template <typename T>
 __global__ void __launch_bounds__(256)
-gn_mish_kernel(const T* __restrict__ raw, const float* __restrict__ stats, const float* __restrict__ gamma,
-               const float* __restrict__ beta, const float* __restrict__ tadd, int tadd_bstride,
-               const float* __restrict__ mask, T* __restrict__ out, int Tn, long total_vec, float inv_count) {
-  const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;  // one 8-channel vector of a 256-ch row
-  if (i >= total_vec) return;
-  const int row = static_cast<int>(i >> 5);
-  const int c0 = static_cast<int>(i & 31) * 8;
-  const int b = row / Tn;
-  const float m = __ldg(mask + row);
-  float o[8];
-  if (m == 0.f) {  // exact: anything times a zero mask is zero (inputs are finite)
-#pragma unroll
-    for (int k = 0; k < 8; ++k) o[k] = 0.f;
-  } else {
-    float r[8];
-    Elem<T>::ld8(raw + static_cast<long>(row) * 256 + c0, r);
-    const float2 st = __ldg(reinterpret_cast<const float2*>(stats + (b * 8 + (c0 >> 5)) * 2));
-    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c0)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c0 + 4));
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c0)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c0 + 4));
-    float4 t0 = make_float4(0.f, 0.f, 0.f, 0.f), t1 = t0;
-    if (tadd) {
-      const float* tp = tadd + static_cast<long>(b) * tadd_bstride + c0;
-      t0 = __ldg(reinterpret_cast<const float4*>(tp));
-      t1 = __ldg(reinterpret_cast<const float4*>(tp + 4));
+gn_mish_kernel(const T* __restrict__ raw, const float* __restrict__ stats, const float2* __restrict__ part, int slots,
+               const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ tadd, int tadd_bstride,
+               const float* __restrict__ mask, T* __restrict__ out, int Tn, long total_rows, float inv_count) {
+  __shared__ float2 st_s[8 * kGnRows];
+  const long row_first = static_cast<long>(blockIdx.x) * kGnRows;
+  const long row_last = min(row_first + kGnRows, total_rows) - 1;
+  const int b_first = static_cast<int>(row_first / Tn), b_last = static_cast<int>(row_last / Tn);
+  const int pairs = (b_last - b_first + 1) * 8;
+  for (int j = threadIdx.x; j < pairs; j += 256) {
+    const int bg = b_first * 8 + j;
+    float2 acc = make_float2(0.f, 0.f);
+    if (part) {
+      const float2* pp = part + static_cast<long>(bg) * slots;
+      for (int i = 0; i < slots; ++i) { const float2 v = __ldcg(pp + i); acc.x += v.x; acc.y += v.y; }
+    } else {
+      acc = __ldg(reinterpret_cast<const float2*>(stats) + bg);
     }
-    const float mean = st.x * inv_count;
-    const float rstd = rsqrtf(fmaxf(st.y * inv_count - mean * mean, 0.f) + 1e-5f);
-    const float ga[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-    const float be[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-    const float ta[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float y = (r[k] - mean) * rstd * ga[k] + be[k];
-      o[k] = (mish_sel<T>(y) + ta[k]) * m;
-    }
+    st_s[j] = acc;
   }
-  Elem<T>::st8(out + static_cast<long>(row) * 256 + c0, o);
+  __syncthreads();
+  const int c0 = (threadIdx.x & 31) * 8;                    // this thread's 8 channels of a 256-channel row
+  const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c0)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c0 + 4));
+  const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c0)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c0 + 4));
+  const float ga[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+  const float be[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+  for (int it = 0; it < kGnRows / 8; ++it) {
+    const long row = row_first + it * 8 + (threadIdx.x >> 5);
+    if (row >= total_rows) break;
+    const int b = static_cast<int>(row / Tn);
+    const float m = __ldg(mask + row);
+    float o[8];
+    if (m == 0.f) {  // exact: anything times a zero mask is zero (inputs are finite)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+    } else {
+      float r[8];
+      Elem<T>::ld8(raw + row * 256 + c0, r);
+      const float2 st = st_s[(b - b_first) * 8 + (c0 >> 5)];
+      float4 t0 = make_float4(0.f, 0.f, 0.f, 0.f), t1 = t0;
+      if (tadd) {
+        const float* tp = tadd + static_cast<long>(b) * tadd_bstride + c0;
+        t0 = __ldg(reinterpret_cast<const float4*>(tp));
+        t1 = __ldg(reinterpret_cast<const float4*>(tp + 4));
+      }
+      const float mean = st.x * inv_count;
+      const float rstd = rsqrtf(fmaxf(st.y * inv_count - mean * mean, 0.f) + 1e-5f);
+      const float ta[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float y = (r[k] - mean) * rstd * ga[k] + be[k];
+        o[k] = (mish_sel<T>(y) + ta[k]) * m;
+      }
+    }
+    Elem<T>::st8(out + row * 256 + c0, o);
+  }
 }
 
 template <typename T>
-cudaError_t launch_gn_mish(const T* raw, const float* stats, const float* gamma, const float* beta, const float* tadd,
-                           int tadd_bstride, const float* mask, T* out, int B, int Tn, cudaStream_t st) {
-  const long total = static_cast<long>(B) * Tn * 32;
-  gn_mish_kernel<T><<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
-      raw, stats, gamma, beta, tadd, tadd_bstride, mask, out, Tn, total, 1.f / (32.f * Tn));
+cudaError_t launch_gn_mish(const T* raw, const float* stats, const float2* part, int slots, const float* gamma, const float* beta,
+                           const float* tadd, int tadd_bstride, const float* mask, T* out, int B, int Tn, cudaStream_t st) {
+  const long rows = static_cast<long>(B) * Tn;
+  gn_mish_kernel<T><<<static_cast<unsigned>((rows + kGnRows - 1) / kGnRows), 256, 0, st>>>(
+      raw, stats, part, slots, gamma, beta, tadd, tadd_bstride, mask, out, Tn, rows, 1.f / (32.f * Tn));
   return cudaGetLastError();
 }
-template cudaError_t launch_gn_mish<float>(const float*, const float*, const float*, const float*, const float*, int,
+template cudaError_t launch_gn_mish<float>(const float*, const float*, const float2*, int, const float*, const float*, const float*, int,
                                            const float*, float*, int, int, cudaStream_t);
-template cudaError_t launch_gn_mish<__nv_bfloat16>(const __nv_bfloat16*, const float*, const float*, const float*,
+template cudaError_t launch_gn_mish<__nv_bfloat16>(const __nv_bfloat16*, const float*, const float2*, int, const float*, const float*,
                                                    const float*, int, const float*, __nv_bfloat16*, int, int, cudaStream_t);
-template cudaError_t launch_gn_mish<__half>(const __half*, const float*, const float*, const float*, const float*, int,
+template cudaError_t launch_gn_mish<__half>(const __half*, const float*, const float2*, int, const float*, const float*, const float*, int,
                                             const float*, __half*, int, int, cudaStream_t);
 
 // ---------------------------------------------------------------- LayerNorm(256), one warp per row, two-pass variance

@@ -140,6 +140,9 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   auto add = [&](Launch l) { ops.push_back(std::move(l)); prog.kernels++; };
   // statistics of the next Block1D conv over Tn rows: fills the epilogue's fields, returns the [B][8][2] sums the
   // consumer reads.  Sums are written (not accumulated) in a fixed order, so nothing has to be cleared between calls.
+  // Statistics whose consumer is gn_mish_kernel are left as per-slot partial sums (the consumer adds them): the producing conv
+  // then has no ordered-sum tail.  Only with the tensor-core kernels: the FFMA kernel keeps its own finish (MB200_GN_FINISH=1 too).
+  const int stats_by_consumer = (tc || split_mode()) && !std::getenv("MB200_GN_FINISH") ? 1 : 0;
   auto next_stats = [&](EpiParams& e, int Tn) {
     const int k = stat_slot++;
     e.stats_out = stats_base + static_cast<size_t>(k) * B * 16;
@@ -149,12 +152,17 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     return e.stats_out;
   };
 
-  auto gn_mish = [&](const void* raw, const float* st, const float* g, const float* bta, const float* tadd, int tbs,
+  // e: the EpiParams of the conv that produced `raw` (its statistics are consumed here as per-slot partial sums when the
+  // conv ran without its ordered-sum tail, see use_partials below)
+  auto gn_mish = [&](const void* raw, const EpiParams& pe, const float* g, const float* bta, const float* tadd, int tbs,
                      const float* mask, void* out, int Tn) {
+    const float* st = pe.stats_out;
+    const float2* part = pe.stats_nofinish ? pe.stats_part : nullptr;
+    const int slots = pe.stats_slots;
     add([=](cudaStream_t s) -> cudaError_t {
-      if (dtype == MB200_F32) return launch_gn_mish<float>((const float*)raw, st, g, bta, tadd, tbs, mask, (float*)out, B, Tn, s);
-      if (dtype == MB200_BF16) return launch_gn_mish<__nv_bfloat16>((const __nv_bfloat16*)raw, st, g, bta, tadd, tbs, mask, (__nv_bfloat16*)out, B, Tn, s);
-      return launch_gn_mish<__half>((const __half*)raw, st, g, bta, tadd, tbs, mask, (__half*)out, B, Tn, s);
+      if (dtype == MB200_F32) return launch_gn_mish<float>((const float*)raw, st, part, slots, g, bta, tadd, tbs, mask, (float*)out, B, Tn, s);
+      if (dtype == MB200_BF16) return launch_gn_mish<__nv_bfloat16>((const __nv_bfloat16*)raw, st, part, slots, g, bta, tadd, tbs, mask, (__nv_bfloat16*)out, B, Tn, s);
+      return launch_gn_mish<__half>((const __half*)raw, st, part, slots, g, bta, tadd, tbs, mask, (__half*)out, B, Tn, s);
     });
   };
   auto layernorm = [&](const void* in, const float* g, const float* bta, void* out, long rows) {
@@ -171,9 +179,10 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     const ResnetW& R = est_.res[r];
     EpiParams e = epi();
     e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
-    const float* st1 = next_stats(e, Tn);
+    next_stats(e, Tn);
+    e.stats_nofinish = stats_by_consumer;
     add(conv_op(R.conv1, s0, s1, B, Tn, e));
-    gn_mish(buf(RAW), st1, R.gn1_g, R.gn1_b, tproj + r * 256, tproj_bstride, mask, buf(H1), Tn);
+    gn_mish(buf(RAW), e, R.gn1_g, R.gn1_b, tproj + r * 256, tproj_bstride, mask, buf(H1), Tn);
     e = epi();
     e.out0 = buf(RAW2); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
     const float* st2 = next_stats(e, Tn);
@@ -262,9 +271,10 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   {
     EpiParams e = epi();
     e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
-    const float* stf = next_stats(e, T);
+    next_stats(e, T);
+    e.stats_nofinish = stats_by_consumer;
     add(conv_op(est_.final_conv, Src{buf(YB), 256, 256, T}, nullptr, B, T, e));
-    gn_mish(buf(RAW), stf, est_.fgn_g, est_.fgn_b, nullptr, 0, maskT, buf(H1), T);
+    gn_mish(buf(RAW), e, est_.fgn_g, est_.fgn_b, nullptr, 0, maskT, buf(H1), T);
     e = epi();
     e.mask = maskT; e.mask_out = 1;
     if (euler) {

@@ -67,8 +67,8 @@ template <typename T> cudaError_t launch_conv_umma2(const ConvLaunch& L, cudaStr
 
 // ---- elementwise / small kernels (elementwise.cu)
 template <typename T>
-cudaError_t launch_gn_mish(const T* raw, const float* stats, const float* gamma, const float* beta, const float* tadd,
-                           int tadd_bstride, const float* mask, T* out, int B, int Tn, cudaStream_t st);
+cudaError_t launch_gn_mish(const T* raw, const float* stats, const float2* part, int slots, const float* gamma, const float* beta,
+                           const float* tadd, int tadd_bstride, const float* mask, T* out, int B, int Tn, cudaStream_t st);
 template <typename T>
 cudaError_t launch_layernorm(const T* in, const float* g, const float* b, T* out, long rows, cudaStream_t st);
 cudaError_t launch_split_bf16x2(const float* s0, int ld0, int c0, const float* s1, int ld1, int c1, long rows, void* hi, void* lo,
