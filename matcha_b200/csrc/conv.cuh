@@ -115,6 +115,8 @@ struct RQGeom {
   const float* bias;             // res_conv bias [256]
   const void* gn_raw;            // block2 conv output [rows][256], operand dtype
   const float* gn_stats;         // [B][8][2] sum, sum of squares
+  const float2* gn_part;         // or, when not null: the producing conv's per-32-row partial sums [B][8][gn_slots], added here
+  int gn_slots;
   const float* gn_gamma;         // [256]
   const float* gn_beta;
   float gn_inv_count;            // 1 / (32 L)

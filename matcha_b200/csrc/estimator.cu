@@ -186,9 +186,11 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     e = epi();
     e.out0 = buf(RAW2); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
     const float* st2 = next_stats(e, Tn);
+    // the fused consumer adds the partial sums itself when that is cheap (one load per slot and group: up to 16 slots = 512 frames)
+    e.stats_nofinish = (stats_by_consumer && rq_supported() && e.stats_slots <= 16) ? 1 : 0;
     add(conv_op(R.conv2, Src{buf(H1), 256, 256, Tn}, nullptr, B, Tn, e));
     if (rq_supported()) {   // res_conv + GroupNorm/Mish + LayerNorm1 + QKV projection: one kernel (RES and QKV written)
-      add(resqkv_op(R.res, X.qkv, s0, s1, buf(RAW2), st2, R.gn2_g, R.gn2_b, mask, buf(RES), X.ln1_g, X.ln1_b, buf(QKV), B, Tn));
+      add(resqkv_op(R.res, X.qkv, s0, s1, buf(RAW2), e, R.gn2_g, R.gn2_b, mask, buf(RES), X.ln1_g, X.ln1_b, buf(QKV), B, Tn));
       return;
     }
     e = epi();

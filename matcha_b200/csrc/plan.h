@@ -231,7 +231,7 @@ class Plan {
                const void* res_in = nullptr, const float* ln_g = nullptr, const float* ln_b = nullptr);
   // res = x Wres^T + b + mish(GN(raw2)) * mask ; qkv = LayerNorm1(res) Wqkv^T as one kernel (resqkv_fused.cu);
   // sources are dense [B][L][ld] buffers tiled over the flat B*L rows
-  Launch resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const Src* s1, const void* gn_raw, const float* gn_stats,
+  Launch resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const Src* s1, const void* gn_raw, const EpiParams& gn_producer,
                    const float* gn_gamma, const float* gn_beta, const float* mask, void* res_out, const float* ln_g,
                    const float* ln_b, void* qkv_out, int B, int L);
   // softmax(q k^T + mask) v on [B][L][384] qkv -> [B][L][128] (operand dtype; fp32 mode: SIMT kernel)

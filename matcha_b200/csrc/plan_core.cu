@@ -633,7 +633,7 @@ Launch Plan::ff_op(const PackedW& W1, const PackedW& W2, const float* snake_a, c
 }
 
 Launch Plan::resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const Src* s1, const void* gn_raw,
-                       const float* gn_stats, const float* gn_gamma, const float* gn_beta, const float* mask, void* res_out,
+                       const EpiParams& gn_producer, const float* gn_gamma, const float* gn_beta, const float* mask, void* res_out,
                        const float* ln_g, const float* ln_b, void* qkv_out, int B, int L) {
   if (!rq_supported()) throw Error("resqkv_op: unsupported configuration");
   const int kres = s0.ch + (s1 ? s1->ch : 0);
@@ -646,7 +646,9 @@ Launch Plan::resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const S
   g.rows = static_cast<long>(B) * L; g.L = L;
   g.total_tiles = static_cast<int>((g.rows + 127) / 128);
   g.nk0 = s0.ch / 64; g.nk1 = s1 ? s1->ch / 64 : 0;
-  g.bias = Wres.bias; g.gn_raw = gn_raw; g.gn_stats = gn_stats; g.gn_gamma = gn_gamma; g.gn_beta = gn_beta;
+  g.bias = Wres.bias; g.gn_raw = gn_raw; g.gn_stats = gn_producer.stats_out; g.gn_gamma = gn_gamma; g.gn_beta = gn_beta;
+  g.gn_part = gn_producer.stats_nofinish ? gn_producer.stats_part : nullptr;   // the conv left its partial sums un-added
+  g.gn_slots = gn_producer.stats_slots;
   g.gn_inv_count = 1.f / (32.f * L);
   g.mask = mask; g.res_out = res_out; g.ln_g = ln_g; g.ln_b = ln_b; g.qkv_out = qkv_out;
   g.dbg_out = nullptr;

@@ -49,7 +49,14 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
       const int n0 = half * 128 + cb * 32;
       float acc[32];
       tmem_ld_32x32(tlane + n0, acc);
-      const float gsum = __ldg(st + 2 * cb), gsq = __ldg(st + 2 * cb + 1);
+      float gsum, gsq;
+      if (g.gn_part) {   // fixed-order sum of the producing conv's partial sums (it ran without its ordered-sum tail)
+        const float2* pp = g.gn_part + static_cast<long>(b * 8 + half * 4 + cb) * g.gn_slots;
+        gsum = 0.f; gsq = 0.f;
+        for (int i = 0; i < g.gn_slots; ++i) { const float2 v = __ldcg(pp + i); gsum += v.x; gsq += v.y; }
+      } else {
+        gsum = __ldg(st + 2 * cb); gsq = __ldg(st + 2 * cb + 1);
+      }
       const float gmean = gsum * g.gn_inv_count;
       const float grstd = rsqrtf(fmaxf(gsq * g.gn_inv_count - gmean * gmean, 0.f) + 1e-5f);
       uint4* xp[4];
