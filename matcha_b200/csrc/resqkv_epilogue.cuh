@@ -38,6 +38,21 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
     const float m = ok ? __ldg(g.mask + row) : 0.f;
     const int b = ok ? static_cast<int>(row / g.L) : 0;
     const float* st = g.gn_stats + (b * 8 + half * 4) * 2;
+    // this row's four GroupNorm groups: finished sums, or the fixed-order sum of the producing conv's per-32-row partial
+    // sums (it then ran without its ordered-sum tail).  Fetched here so the loads fly while the accumulator is awaited.
+    float gs[4], gq[4];
+    if (g.gn_part) {
+      const float2* pp = g.gn_part + static_cast<long>(b * 8 + half * 4) * g.gn_slots;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { gs[c] = 0.f; gq[c] = 0.f; }
+      for (int i = 0; i < g.gn_slots; ++i) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { const float2 v = __ldcg(pp + c * g.gn_slots + i); gs[c] += v.x; gq[c] += v.y; }
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { gs[c] = __ldg(st + 2 * c); gq[c] = __ldg(st + 2 * c + 1); }
+    }
     __syncwarp();
     if (probe && n == 0) po[0] = clock64() - pt0;
     mbar_wait(t0_full, n & 1);
@@ -49,14 +64,8 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
       const int n0 = half * 128 + cb * 32;
       float acc[32];
       tmem_ld_32x32(tlane + n0, acc);
-      float gsum, gsq;
-      if (g.gn_part) {   // fixed-order sum of the producing conv's partial sums (it ran without its ordered-sum tail)
-        const float2* pp = g.gn_part + static_cast<long>(b * 8 + half * 4 + cb) * g.gn_slots;
-        gsum = 0.f; gsq = 0.f;
-        for (int i = 0; i < g.gn_slots; ++i) { const float2 v = __ldcg(pp + i); gsum += v.x; gsq += v.y; }
-      } else {
-        gsum = __ldg(st + 2 * cb); gsq = __ldg(st + 2 * cb + 1);
-      }
+      const float gsum = cb == 0 ? gs[0] : cb == 1 ? gs[1] : cb == 2 ? gs[2] : gs[3];   // (rolled loop: no dynamic register index)
+      const float gsq = cb == 0 ? gq[0] : cb == 1 ? gq[1] : cb == 2 ? gq[2] : gq[3];
       const float gmean = gsum * g.gn_inv_count;
       const float grstd = rsqrtf(fmaxf(gsq * g.gn_inv_count - gmean * gmean, 0.f) + 1e-5f);
       uint4* xp[4];
