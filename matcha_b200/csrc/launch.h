@@ -55,6 +55,7 @@ struct RQLaunch {
   CUtensorMap tmA0, tmA1, tmWres, tmWqkv;
   RQGeom g;
   int smem_bytes, grid;
+  int pair;                            // CTA pairs (cta_group::2)
 };
 int resqkv_fused_smem_bytes();
 template <typename T> cudaError_t launch_resqkv_fused(const RQLaunch& L, cudaStream_t st);

@@ -186,6 +186,7 @@ class Plan {
   bool fp32_split = true;
   bool ff_pair = true;      // CTA pairs in the fused post-attention kernel (MB200_FF_PAIR=0 turns them off)
   bool res_pair = true;     // CTA pairs in the fused ResBlock kernel (MB200_RES_PAIR=0 turns them off)
+  bool rq_pair = false;     // CTA pairs in the fused res_conv + GroupNorm + LayerNorm + QKV kernel (MB200_RQ_PAIR=1)
   bool pair_resident = false;   // CTA pairs also for long layers with resident weights (MB200_PAIR_RESIDENT=1)
   int use_pair = 2;         // CTA pairs (cta_group::2) in the persistent conv-GEMM: 1 = N = 256 layers, 2 = also N = 128 (HiFi-GAN stage 2); MB200_PAIR=0 turns them off
   int kernel_version = 2;   // 2 = persistent conv_gemm2.cu (default), 1 = first non-persistent kernel (MB200_KERNEL=1)

@@ -47,6 +47,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
   if (const char* v = std::getenv("MB200_FP32")) fp32_split = std::strcmp(v, "simt") != 0;
   if (const char* v = std::getenv("MB200_FF_PAIR")) ff_pair = std::atoi(v) != 0;
   if (const char* v = std::getenv("MB200_RES_PAIR")) res_pair = std::atoi(v) != 0;
+  if (const char* v = std::getenv("MB200_RQ_PAIR")) rq_pair = std::atoi(v) != 0;
   if (const char* v = std::getenv("MB200_PAIR_RESIDENT")) pair_resident = std::atoi(v) != 0;
   if (const char* v = std::getenv("MB200_PAIR")) use_pair = std::atoi(v);   // 0 off, 1 N = 256 layers only, 2 (default) also the N = 128 layers
   if (major != 10) throw Error("matcha_b200 kernels are built for sm_100a only; device compute capability major = " + std::to_string(major));
@@ -662,10 +663,11 @@ Launch Plan::resqkv_op(const PackedW& Wres, const PackedW& Wqkv, Src s0, const S
   }
   Lq.tmA0 = tmap_act(s0.p, s0.ld, static_cast<int>(g.rows), 1, 64);
   Lq.tmA1 = s1 ? tmap_act(s1->p, s1->ld, static_cast<int>(g.rows), 1, 64) : Lq.tmA0;
-  Lq.tmWres = Wres.tm;
-  Lq.tmWqkv = tmap_w(Wqkv.w, 256, 384, 64, 128);
+  Lq.pair = (rq_pair && g.total_tiles >= 2) ? 1 : 0;   // CTA pairs: every weight box split between the two CTAs of a cluster
+  Lq.tmWres = Lq.pair ? tmap_w(Wres.w, Wres.K_total, 256, 64, 128) : Wres.tm;
+  Lq.tmWqkv = tmap_w(Wqkv.w, 256, 384, 64, Lq.pair ? 64 : 128);
   Lq.smem_bytes = resqkv_fused_smem_bytes();
-  Lq.grid = std::min(g.total_tiles, num_sms);
+  Lq.grid = Lq.pair ? 2 * std::min((g.total_tiles + 1) / 2, num_sms / 2) : std::min(g.total_tiles, num_sms);
   const int dtype = cfg.dtype;
   Launch op([Lq, dtype](cudaStream_t st) -> cudaError_t {
     return dtype == MB200_BF16 ? launch_resqkv_fused<__nv_bfloat16>(Lq, st) : launch_resqkv_fused<__half>(Lq, st);

@@ -8,10 +8,13 @@
 
 namespace mb {
 
-template <typename T>
+// PAIR (CTA pairs, see resqkv_fused.cu): tiles are numbered 2 u + rank and the barriers the issuer waits on (x_full, t_free)
+// live in the pair's leader CTA.
+template <typename T, bool PAIR>
 __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, uint8_t* x_tile, float2* xch, uint64_t* t0_full,
                                             uint64_t* x_full, uint64_t* t1_full, uint64_t* t_free, uint32_t tmem_base,
-                                            int warp, int lane, int nt_cta) {
+                                            int warp, int lane, int nt_cta, int u0, int ustep, int rank) {
+  auto arrive_mma = [](uint64_t* bar) { if constexpr (PAIR) mbar_arrive_leader(bar); else mbar_arrive(bar); };
   const int lane_grp = warp & 3, half = (warp - 2) >> 2;
   const int r = lane_grp * 32 + lane;                      // row of the tile held by this lane
   const uint32_t tlane = tmem_base + (static_cast<uint32_t>(lane_grp * 32) << 16);
@@ -23,7 +26,7 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
   const bool probe = g.dbg_out && warp == 2 && lane == 0;
   long long* po = g.dbg_out ? g.dbg_out + blockIdx.x * 16 : nullptr;
   for (int n = 0; n < nt_cta; ++n) {
-    const int tile = blockIdx.x + n * gridDim.x;
+    const int tile = PAIR ? 2 * (u0 + n * ustep) + rank : u0 + n * ustep;   // a pair's odd tile may lie past the end: all padding
     const long row = static_cast<long>(tile) * 128 + r;
     const bool ok = row < g.rows;
     // ---- E0.  The loops below are deliberately ROLLED: fully unrolled, this epilogue was 4 600 straight-line instructions
@@ -123,7 +126,7 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
     tc_fence_before();
     fence_proxy_async();          // generic-proxy stores -> visible to the tensor core's async-proxy reads
     __syncwarp();
-    if (lane == 0) mbar_arrive(x_full);
+    if (lane == 0) arrive_mma(x_full);
     if (probe && n == 0) po[3] = clock64() - pt0;
     // ---- E1: q | k | v columns [192 half, +192) of this lane's row
     // q | k | v columns [192 half, +192) of this warp's 32 rows, in two rounds of 96 columns staged through a warp-private
@@ -154,7 +157,7 @@ __device__ __forceinline__ void rq_epilogue(const RQGeom& g, const float* par, u
     }
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(t_free);
+    if (lane == 0) arrive_mma(t_free);
     if (n + 1 < nt_cta) named_bar_sync(5, 256);   // every warp's staging slice is drained before the next tile's rows land in the x tile
     if (probe && n == 0) po[5] = clock64() - pt0;
   }

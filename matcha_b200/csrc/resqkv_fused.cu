@@ -37,7 +37,9 @@ int resqkv_fused_smem_bytes() {
   return 1024 + kRQAStages * kRQAStage + kRQWStages * kRQWStage + kRQXBytes + kRQXchBytes + kRQBarBytes + kRQParBytes;
 }
 
-template <typename T>
+// PAIR: two CTAs of a cluster as one tcgen05 cta_group::2 unit (conv_gemm2.cu): each CTA runs its own 128-row tile and holds
+// half of every weight box (res_conv: 128 of 256 output channels, QKV: 64 of a block's 128), the even CTA issues the MMAs.
+template <typename T, bool PAIR>
 __global__ void __launch_bounds__(320, 1)
 resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                     const __grid_constant__ CUtensorMap tmWres, const __grid_constant__ CUtensorMap tmWqkv,
@@ -61,14 +63,25 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
   float* par = reinterpret_cast<float*>(x_tile + kRQXBytes + kRQXchBytes + kRQBarBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nt_cta = (g.total_tiles > static_cast<int>(blockIdx.x))
-                         ? (g.total_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+  const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
+  const int units = PAIR ? (g.total_tiles + 1) / 2 : g.total_tiles;   // tiles, or pairs of tiles (2 u, 2 u + 1)
+  const int u0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int ustep = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int nt_cta = units > u0 ? (units - 1 - u0) / ustep + 1 : 0;
   const int nk = g.nk0 + g.nk1;
+  constexpr int WSTAGE = PAIR ? kRQWStage / 2 : kRQWStage;            // this CTA's share of a weight ring stage
+  auto expect = [&](uint64_t* bar, uint32_t bytes) { if constexpr (PAIR) { if (rank == 0) mbar_expect_tx(bar, 2 * bytes); } else mbar_expect_tx(bar, bytes); };
+  auto load2 = [](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+    if constexpr (PAIR) tma_load_2d_pair(dst, m, bar, c0, c1); else tma_load_2d(dst, m, bar, c0, c1);
+  };
+  auto load3 = [](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+    if constexpr (PAIR) tma_load_3d_pair(dst, m, bar, c0, c1, c2); else tma_load_3d(dst, m, bar, c0, c1, c2);
+  };
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmA1); tma_prefetch_desc(&tmWres); tma_prefetch_desc(&tmWqkv);
     for (int s = 0; s < 3; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    mbar_init(t0_full, 1); mbar_init(x_full, 8); mbar_init(t1_full, 1); mbar_init(t_free, 8);
+    mbar_init(t0_full, 1); mbar_init(x_full, PAIR ? 16 : 8); mbar_init(t1_full, 1); mbar_init(t_free, PAIR ? 16 : 8);
     fence_barrier_init();
   }
   // per-channel parameters -> shared memory once per CTA: with 217 KB of the SM's 256 KB carved out as shared memory the
@@ -78,9 +91,9 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
     const float* src = i < 256 ? g.bias : (i < 512 ? g.gn_gamma : (i < 768 ? g.gn_beta : (i < 1024 ? g.ln_g : g.ln_b)));
     par[i] = __ldg(src + (i & 255));
   }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  if (warp == 1) { if constexpr (PAIR) tmem_alloc_pair<512>(tmem_slot); else tmem_alloc<512>(tmem_slot); }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -89,16 +102,16 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0;
     for (int n = 0; n < nt_cta; ++n) {
-      const int tile = blockIdx.x + n * gridDim.x;
+      const int tile = PAIR ? 2 * (u0 + n * ustep) + rank : u0 + n * ustep;
       for (int c = 0; c < nk; ++c) {
         const bool second = c >= g.nk0;
         mbar_wait(&a_empty[as], aph ^ 1);
         mbar_wait(&w_empty[ws], wph ^ 1);
         if (elect_one()) {
-          mbar_expect_tx(&a_full[as], kRQAStage);
-          tma_load_3d(a_ring + as * kRQAStage, second ? &tmA1 : &tmA0, &a_full[as], (second ? c - g.nk0 : c) * 64, tile * 128, 0);
-          mbar_expect_tx(&w_full[ws], kRQWStage);
-          tma_load_2d(w_ring + ws * kRQWStage, &tmWres, &w_full[ws], c * 64, 0);
+          expect(&a_full[as], kRQAStage);
+          load3(a_ring + as * kRQAStage, second ? &tmA1 : &tmA0, &a_full[as], (second ? c - g.nk0 : c) * 64, tile * 128, 0);
+          expect(&w_full[ws], WSTAGE);
+          load2(w_ring + ws * WSTAGE, &tmWres, &w_full[ws], c * 64, PAIR ? rank * 128 : 0);
         }
         __syncwarp();
         if (++as == kRQAStages) { as = 0; aph ^= 1; }
@@ -108,18 +121,25 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
         for (int s = 0; s < 2; ++s) {
           mbar_wait(&w_empty[ws], wph ^ 1);
           if (elect_one()) {
-            mbar_expect_tx(&w_full[ws], kRQWStage);
-            tma_load_2d(w_ring + ws * kRQWStage, &tmWqkv, &w_full[ws], (2 * s) * 64, nb * 128);
-            tma_load_2d(w_ring + ws * kRQWStage + 16384, &tmWqkv, &w_full[ws], (2 * s + 1) * 64, nb * 128);
+            expect(&w_full[ws], WSTAGE);
+            const int n0 = nb * 128 + (PAIR ? rank * 64 : 0);
+            load2(w_ring + ws * WSTAGE, &tmWqkv, &w_full[ws], (2 * s) * 64, n0);
+            load2(w_ring + ws * WSTAGE + WSTAGE / 2, &tmWqkv, &w_full[ws], (2 * s + 1) * 64, n0);
           }
           __syncwarp();
           if (++ws == kRQWStages) { ws = 0; wph ^= 1; }
         }
     }
   } else if (warp == 1) {
-    // ================================================================= MMA issuer
+    // ================================================================= MMA issuer (pair: the leader's only)
+    if (rank == 0) {
     constexpr int fmt = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
-    constexpr uint32_t idesc128 = umma_idesc_f16(fmt, 128, 128), idesc256 = umma_idesc_f16(fmt, 128, 256);
+    constexpr int MM = PAIR ? 256 : 128;
+    constexpr uint32_t idesc128 = umma_idesc_f16(fmt, MM, 128), idesc256 = umma_idesc_f16(fmt, MM, 256);
+    auto umma_f16_lohi = [](uint32_t d, uint32_t a, uint32_t b, uint32_t hi, uint32_t id, uint32_t acc) {
+      if constexpr (PAIR) mb::umma_f16_lohi_pair(d, a, b, hi, id, acc); else mb::umma_f16_lohi(d, a, b, hi, id, acc);
+    };
+    auto umma_commit = [](uint64_t* bar) { if constexpr (PAIR) mb::umma_commit_pair(bar); else mb::umma_commit(bar); };
     const uint32_t desc_hi = static_cast<uint32_t>(umma_smem_desc<128>(0) >> 32);
     const uint32_t a_lo0 = static_cast<uint32_t>(umma_smem_desc<128>(smem_u32(a_ring)));
     const uint32_t x_lo = static_cast<uint32_t>(umma_smem_desc<128>(smem_u32(x_tile)));
@@ -134,7 +154,7 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
         mbar_wait(&w_full[ws], wph);
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t a = a_lo0 + as * (kRQAStage >> 4), w = w_lo0 + ws * (kRQWStage >> 4);
+          const uint32_t a = a_lo0 + as * (kRQAStage >> 4), w = w_lo0 + ws * (WSTAGE >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_f16_lohi(tmem_base, a + 2 * k, w + 2 * k, desc_hi, idesc256, (c | k) != 0 ? 1u : 0u);
           umma_commit(&a_empty[as]);
@@ -152,10 +172,10 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
           mbar_wait(&w_full[ws], wph);
           tc_fence_after();
           if (elect_one()) {
-            const uint32_t w = w_lo0 + ws * (kRQWStage >> 4);
+            const uint32_t w = w_lo0 + ws * (WSTAGE >> 4);
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
-              const uint32_t a = x_lo + (2 * s + c) * 1024u, wc = w + c * 1024u;
+              const uint32_t a = x_lo + (2 * s + c) * 1024u, wc = w + c * ((WSTAGE / 2) >> 4);
 #pragma unroll
               for (int k = 0; k < 4; ++k) umma_f16_lohi(tmem_base + nb * 128, a + 2 * k, wc + 2 * k, desc_hi, idesc128, (s | c | k) != 0 ? 1u : 0u);
             }
@@ -166,25 +186,40 @@ resqkv_fused_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
           if (++ws == kRQWStages) { ws = 0; wph ^= 1; }
         }
     }
+    }
   } else {
-    rq_epilogue<T>(g, par, x_tile, xch, t0_full, x_full, t1_full, t_free, tmem_base, warp, lane, nt_cta);
+    rq_epilogue<T, PAIR>(g, par, x_tile, xch, t0_full, x_full, t1_full, t_free, tmem_base, warp, lane, nt_cta, u0, ustep, rank);
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<512>(tmem_base);
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
+  if (warp == 1) { if constexpr (PAIR) tmem_dealloc_pair<512>(tmem_base); else tmem_dealloc<512>(tmem_base); }
 }
 
-template <typename T>
-cudaError_t launch_resqkv_fused(const RQLaunch& L, cudaStream_t st) {
-  auto kern = resqkv_fused_kernel<T>;
+template <typename T, bool PAIR>
+static cudaError_t launch_resqkv_inst(const RQLaunch& L, cudaStream_t st) {
+  auto kern = resqkv_fused_kernel<T, PAIR>;
   static PerDeviceOnce configured;
   if (configured.needed()) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (err != cudaSuccess) return err;
     configured.mark();
   }
-  kern<<<L.grid, 320, L.smem_bytes, st>>>(L.tmA0, L.tmA1, L.tmWres, L.tmWqkv, L.g);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(L.grid);
+  cfg.blockDim = dim3(320);
+  cfg.dynamicSmemBytes = L.smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = PAIR ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, L.tmA0, L.tmA1, L.tmWres, L.tmWqkv, L.g);
+}
+
+template <typename T>
+cudaError_t launch_resqkv_fused(const RQLaunch& L, cudaStream_t st) {
+  return L.pair ? launch_resqkv_inst<T, true>(L, st) : launch_resqkv_inst<T, false>(L, st);
 }
 template cudaError_t launch_resqkv_fused<__nv_bfloat16>(const RQLaunch&, cudaStream_t);
 template cudaError_t launch_resqkv_fused<__half>(const RQLaunch&, cudaStream_t);

@@ -12,6 +12,7 @@ from matcha_b200 import synthetic as weights
 pytestmark = pytest.mark.gpu
 
 PAIR_VARS = ("MB200_PAIR", "MB200_RES_PAIR", "MB200_FF_PAIR")
+OPTIONAL_PAIR_VARS = ("MB200_RQ_PAIR", "MB200_PAIR_RESIDENT")   # built, measured neutral, off by default: covered here
 
 
 def _plan(prec):
@@ -33,6 +34,8 @@ def test_estimator_with_cta_pairs_equals_single_cta_kernels(monkeypatch, prec, b
                 monkeypatch.setenv(v, "0")
             else:
                 monkeypatch.delenv(v, raising=False)
+        for v in OPTIONAL_PAIR_VARS:
+            monkeypatch.setenv(v, "1" if pairs == "on" else "0")
         plan = _plan(prec)
         plan.load_estimator(sd)
         out[pairs] = plan.estimator_forward(x, mask, mu, torch.tensor(0.4)).cpu()
@@ -52,6 +55,8 @@ def test_vocoder_with_cta_pairs_equals_single_cta_kernels(monkeypatch, prec, B, 
                 monkeypatch.setenv(v, "0")
             else:
                 monkeypatch.delenv(v, raising=False)
+        for v in OPTIONAL_PAIR_VARS:
+            monkeypatch.setenv(v, "1" if pairs == "on" else "0")
         plan = _plan(prec)
         plan.load_generator(sd)
         out[pairs] = plan.hifigan_forward(mel).cpu()
