@@ -143,6 +143,10 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
   // Statistics whose consumer is gn_mish_kernel are left as per-slot partial sums (the consumer adds them): the producing conv
   // then has no ordered-sum tail.  Only with the tensor-core kernels: the FFMA kernel keeps its own finish (MB200_GN_FINISH=1 too).
   const int stats_by_consumer = (tc || split_mode()) && !std::getenv("MB200_GN_FINISH") ? 1 : 0;
+  // ... for sequences of at most 16 slots (512 frames): every consumer CTA / thread re-adds the slots it needs, which at cfg4's
+  // 94 slots made the GroupNorm + Mish pass 3.6 x slower (measured: 56.0 against 52.6 ms per step); longer sequences keep the finish
+  // in the conv.
+  constexpr int kConsumerSumSlots = 16;
   auto next_stats = [&](EpiParams& e, int Tn) {
     const int k = stat_slot++;
     e.stats_out = stats_base + static_cast<size_t>(k) * B * 16;
@@ -180,14 +184,14 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     EpiParams e = epi();
     e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
     next_stats(e, Tn);
-    e.stats_nofinish = stats_by_consumer;
+    e.stats_nofinish = stats_by_consumer && e.stats_slots <= kConsumerSumSlots;
     add(conv_op(R.conv1, s0, s1, B, Tn, e));
     gn_mish(buf(RAW), e, R.gn1_g, R.gn1_b, tproj + r * 256, tproj_bstride, mask, buf(H1), Tn);
     e = epi();
     e.out0 = buf(RAW2); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
     const float* st2 = next_stats(e, Tn);
     // the fused consumer adds the partial sums itself when that is cheap (one load per slot and group: up to 16 slots = 512 frames)
-    e.stats_nofinish = (stats_by_consumer && rq_supported() && e.stats_slots <= 16) ? 1 : 0;
+    e.stats_nofinish = (stats_by_consumer && rq_supported() && e.stats_slots <= kConsumerSumSlots) ? 1 : 0;
     add(conv_op(R.conv2, Src{buf(H1), 256, 256, Tn}, nullptr, B, Tn, e));
     if (rq_supported()) {   // res_conv + GroupNorm/Mish + LayerNorm1 + QKV projection: one kernel (RES and QKV written)
       add(resqkv_op(R.res, X.qkv, s0, s1, buf(RAW2), e, R.gn2_g, R.gn2_b, mask, buf(RES), X.ln1_g, X.ln1_b, buf(QKV), B, Tn));
@@ -274,7 +278,7 @@ void Plan::build_estimator_step(Program& prog, int B, int T, const float* tproj,
     EpiParams e = epi();
     e.out0 = buf(RAW); e.out0_ld = 256; e.out0_f32 = dtype == MB200_F32;
     next_stats(e, T);
-    e.stats_nofinish = stats_by_consumer;
+    e.stats_nofinish = stats_by_consumer && e.stats_slots <= kConsumerSumSlots;
     add(conv_op(est_.final_conv, Src{buf(YB), 256, 256, T}, nullptr, B, T, e));
     gn_mish(buf(RAW), e, est_.fgn_g, est_.fgn_b, nullptr, 0, maskT, buf(H1), T);
     e = epi();
