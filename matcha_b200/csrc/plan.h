@@ -252,7 +252,7 @@ class Plan {
       cache.erase(victim);
     }
   }
-  size_t cached_programs() const { return decode_cache_.size() + vocoder_cache_.size(); }
+  size_t cached_programs() const { return decode_cache_.size() + vocoder_cache_.size() + encoder_cache_.size(); }
 
  private:
   std::vector<void*> owned_;
@@ -262,7 +262,7 @@ class Plan {
   EstimatorW est_;
   GeneratorW gen_;
   TextEncW enc_;
-  DevBuf ws_enc_[11];
+  DevBuf ws_enc_[16];
   // workspaces
   DevBuf ws_est_[28];
   DevBuf ws_voc_[8];
@@ -287,6 +287,7 @@ class Plan {
   float* host_wav_dst_ = nullptr;        // set only while synthesise_host runs the vocoder
   std::map<std::tuple<int, int, int, int, long long>, std::unique_ptr<Program>> decode_cache_;   // (B,T,steps,spk,ptr-key)
   std::map<std::tuple<int, int>, std::unique_ptr<Program>> vocoder_cache_;
+  std::map<std::tuple<int, int>, std::unique_ptr<Program>> encoder_cache_;   // text encoder programs by (B, Lx)
 
   void build_estimator_step(Program& prog, int B, int T, const float* tproj, int tproj_bstride, bool euler, float dt,
                             float* v_out_ntc);

@@ -56,6 +56,7 @@ Plan::Plan(const mb200_cfg& c) : cfg(c) {
 Plan::~Plan() {
   for (auto& kv : decode_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
   for (auto& kv : vocoder_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
+  for (auto& kv : encoder_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
   for (void* p : owned_) cudaFree(p);
   if (train_arena_) cudaFree(train_arena_);
   for (auto* arr : {ws_est_, ws_voc_, ws_io_}) (void)arr;
@@ -102,8 +103,10 @@ void* Plan::ensure(DevBuf& b, size_t bytes) {
   // workspaces are referenced by cached programs: growing one invalidates them
   for (auto& kv : decode_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
   for (auto& kv : vocoder_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
+  for (auto& kv : encoder_cache_) if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
   decode_cache_.clear();
   vocoder_cache_.clear();
+  encoder_cache_.clear();
   if (b.p) { MB_CUDA(cudaDeviceSynchronize()); cudaFree(b.p); bytes_allocated -= static_cast<long long>(b.bytes); }
   bytes = (bytes + 1023) & ~size_t(1023);
   MB_CUDA(cudaMalloc(&b.p, bytes));

@@ -341,17 +341,17 @@ void Plan::load_text_encoder(const StateDict& sd, int n_heads) {
   E.loaded = true;
 }
 
-void Plan::text_encoder_forward(const long long* ids, const long long* lengths, const float* spks, int B, int Lx, float* mu_x,
+void Plan::text_encoder_forward(const long long* ids_in, const long long* lengths_in, const float* spks_in, int B, int Lx, float* mu_x,
                                 float* logw, float* x_mask, cudaStream_t st) {
   std::lock_guard<std::recursive_mutex> lk(mu_);
   const TextEncW& E = enc_;
   if (!E.loaded) throw Error("text encoder weights are not loaded");
   if (B < 1 || Lx < 1) throw Error("text encoder: empty batch");
-  if ((E.spk_dim > 0) != (spks != nullptr)) throw Error("spks must be given exactly when the encoder has speaker channels");
+  if ((E.spk_dim > 0) != (spks_in != nullptr)) throw Error("spks must be given exactly when the encoder has speaker channels");
   const long rows = static_cast<long>(B) * Lx;
   const int C = E.C, C0 = E.C0;
   const int wide = std::max(E.filt, 3 * C);
-  enum { X0, H0, H1, X, Y, Z, A, M, P, D1, APART };
+  enum { X0, H0, H1, X, Y, Z, A, M, P, D1, APART, IDS, LENS, SPK, MUX, LOGW };
   reserve_split(rows * static_cast<size_t>(std::max(std::max(wide, C0), 2 * E.filt_dp)));
   float* x0 = static_cast<float*>(ensure(ws_enc_[X0], rows * C0 * 4));
   float* h0 = static_cast<float*>(ensure(ws_enc_[H0], rows * C0 * 4));
@@ -368,23 +368,38 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
   const int att_ctas = ((Lx + 63) / 64) * E.H * B;
   int att_ks = std::min(8, (2 * num_sms + att_ctas - 1) / att_ctas);
   att_ks = std::max(1, std::min(att_ks, ((Lx + 31) / 32) / 4));
+  // The launch sequence is built once per (B, Lx), captured into a CUDA graph (run()) and replayed: at B = 1 the ~90 launches
+  // are otherwise bound by the host's launch rate.  Inputs and outputs go through plan-owned buffers so that the recorded
+  // pointers stay valid whatever the caller passes next time.
+  long long* ids_s = static_cast<long long*>(ensure(ws_enc_[IDS], rows * 8));
+  long long* lens_s = static_cast<long long*>(ensure(ws_enc_[LENS], static_cast<size_t>(B) * 8));
+  float* spk_s = E.spk_dim > 0 ? static_cast<float*>(ensure(ws_enc_[SPK], static_cast<size_t>(B) * E.spk_dim * 4)) : nullptr;
+  float* mux_s = static_cast<float*>(ensure(ws_enc_[MUX], rows * 80 * 4));
+  float* logw_s = static_cast<float*>(ensure(ws_enc_[LOGW], rows * 4));
   float* att_part = att_ks > 1 ? static_cast<float*>(ensure(ws_enc_[APART], rows * E.H * att_ks * (E.Dh + 2) * 4)) : nullptr;
   const unsigned row_blocks = static_cast<unsigned>((rows + 7) / 8);
   auto grid1 = [](long n) { return static_cast<unsigned>((n + 255) / 256); };
+  auto key = std::make_tuple(B, Lx);
+  auto it = encoder_cache_.find(key);
+  if (it == encoder_cache_.end()) {
+  auto prog = std::make_unique<Program>();
+  auto emit = [&](std::function<cudaError_t(cudaStream_t)> fn) { prog->ops.emplace_back(std::move(fn)); prog->kernels++; };
   auto conv = [&](const PackedW& W, const float* in, int in_ch, EpiParams e) {
-    MB_CUDA(conv_op(W, Src{in, in_ch, in_ch, Lx}, nullptr, B, Lx, e)(st));
-    launches += 1;
+    prog->ops.push_back(conv_op(W, Src{in, in_ch, in_ch, Lx}, nullptr, B, Lx, e));
+    prog->kernels++;
   };
   auto ln = [&](const float* in, const float* g, const float* b, const float* mask, int ch, int pre_relu, int post_relu, float* out) {
-    channel_ln_kernel<<<row_blocks, 256, 0, st>>>(in, g, b, mask, ch, pre_relu, post_relu, rows, out);
-    MB_CUDA(cudaGetLastError());
-    launches += 1;
+    emit([=](cudaStream_t s) { channel_ln_kernel<<<row_blocks, 256, 0, s>>>(in, g, b, mask, ch, pre_relu, post_relu, rows, out); return cudaGetLastError(); });
   };
+  const long long* ids = ids_s;
+  const long long* lengths = lens_s;
+  const float* spks = spk_s;
 
   // ---- emb(x) * sqrt(C0) * x_mask  (text_encoder.py:395-397)
-  embed_kernel<<<row_blocks, 256, 0, st>>>(ids, lengths, E.emb, E.n_vocab, C0, std::sqrt(static_cast<float>(C0)), Lx, rows, x0, m);
-  MB_CUDA(cudaGetLastError());
-  launches += 1;
+  {
+    const float* emb = E.emb; const int n_vocab = E.n_vocab; const float esc = std::sqrt(static_cast<float>(C0));
+    emit([=](cudaStream_t s) { embed_kernel<<<row_blocks, 256, 0, s>>>(ids, lengths, emb, n_vocab, C0, esc, Lx, rows, x0, m); return cudaGetLastError(); });
+  }
   // ---- prenet (:36-67): x = x_org; 3 x [conv k5 (x * mask) -> LayerNorm -> ReLU]; (x_org + proj(x)) * mask
   const float* h = x0;
   for (int i = 0; i < 3; ++i) {
@@ -402,9 +417,8 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
     conv(E.pre_proj, h1, C0, e);
   }
   if (E.spk_dim > 0) {                   // :401-402, times the mask the encoder applies first thing (:313)
-    fill_spk_kernel<<<grid1(rows * E.spk_dim), 256, 0, st>>>(spks, m, E.spk_dim, C0, C, Lx, rows, x);
-    MB_CUDA(cudaGetLastError());
-    launches += 1;
+    const int sd = E.spk_dim; const unsigned gsp = grid1(rows * E.spk_dim);
+    emit([=](cudaStream_t s) { fill_spk_kernel<<<gsp, 256, 0, s>>>(spks, m, sd, C0, C, Lx, rows, x); return cudaGetLastError(); });
   }
   // ---- encoder (:276-325)
   const float q_scale = 1.0f / std::sqrt(static_cast<float>(E.Dh));
@@ -413,22 +427,25 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
     EpiParams e = epi_f32();
     e.out0 = z; e.out0_ld = 3 * C;
     conv(Ly.qkv, x, C, e);
-    rope_kernel<<<grid1(rows * 2 * E.H * (E.Dh / 4)), 256, 0, st>>>(z, E.theta, C, E.H, E.Dh, Lx, rows, q_scale);
-    MB_CUDA(cudaGetLastError());
-    scale_q_tail_kernel<<<grid1(rows * E.H * (E.Dh / 2)), 256, 0, st>>>(z, C, E.H, E.Dh, rows, q_scale);
-    MB_CUDA(cudaGetLastError());
-    dim3 ag(((Lx + 63) / 64) * att_ks, E.H, B);
-    if (E.Dh == 96) text_attention_kernel<96><<<ag, 64, 0, st>>>(z, m, a, Lx, C, att_ks, att_part);
-    else text_attention_kernel<128><<<ag, 64, 0, st>>>(z, m, a, Lx, C, att_ks, att_part);
-    MB_CUDA(cudaGetLastError());
+    const float* theta = E.theta; const int H = E.H, Dh = E.Dh;
+    const unsigned g_rope = grid1(rows * 2 * E.H * (E.Dh / 4)), g_tail = grid1(rows * E.H * (E.Dh / 2));
+    emit([=](cudaStream_t s) { rope_kernel<<<g_rope, 256, 0, s>>>(z, theta, C, H, Dh, Lx, rows, q_scale); return cudaGetLastError(); });
+    emit([=](cudaStream_t s) { scale_q_tail_kernel<<<g_tail, 256, 0, s>>>(z, C, H, Dh, rows, q_scale); return cudaGetLastError(); });
+    const dim3 ag(((Lx + 63) / 64) * att_ks, E.H, B);
+    emit([=](cudaStream_t s) {
+      if (Dh == 96) text_attention_kernel<96><<<ag, 64, 0, s>>>(z, m, a, Lx, C, att_ks, att_part);
+      else text_attention_kernel<128><<<ag, 64, 0, s>>>(z, m, a, Lx, C, att_ks, att_part);
+      return cudaGetLastError();
+    });
     if (att_ks > 1) {
       const long total = rows * E.H * E.Dh;
-      if (E.Dh == 96) text_attention_merge_kernel<96><<<grid1(total), 256, 0, st>>>(att_part, a, Lx, C, E.H, att_ks, total);
-      else text_attention_merge_kernel<128><<<grid1(total), 256, 0, st>>>(att_part, a, Lx, C, E.H, att_ks, total);
-      MB_CUDA(cudaGetLastError());
-      launches += 1;
+      const unsigned gm = grid1(total);
+      emit([=](cudaStream_t s) {
+        if (Dh == 96) text_attention_merge_kernel<96><<<gm, 256, 0, s>>>(att_part, a, Lx, C, H, att_ks, total);
+        else text_attention_merge_kernel<128><<<gm, 256, 0, s>>>(att_part, a, Lx, C, H, att_ks, total);
+        return cudaGetLastError();
+      });
     }
-    launches += 3;
     e = epi_f32();                       // x = LayerNorm(x + conv_o(attn))
     e.resid = x; e.resid_ld = C; e.resid_f32 = 1;
     e.out0 = y; e.out0_ld = C;
@@ -450,8 +467,7 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
     e.mask = m; e.mask_out = 1;
     e.out0 = p; e.out0_ld = 80;
     conv(E.proj_m, x, C, e);
-    MB_CUDA(launch_btc_to_bct(p, mu_x, B, 80, Lx, st));
-    launches += 1;
+    emit([=](cudaStream_t s) { return launch_btc_to_bct(p, mux_s, B, 80, Lx, s); });
   }
   // ---- logw = proj_w(x.detach(), mask)  (:70-94, :409): conv -> ReLU -> LayerNorm, twice; 1x1 proj; mask
   {
@@ -466,10 +482,18 @@ void Plan::text_encoder_forward(const long long* ids, const long long* lengths, 
     e = epi_f32();
     e.out0 = d1; e.out0_ld = 8;          // one real output channel; the epilogue stores groups of eight
     conv(E.dp_proj, d2, E.filt_dp, e);
-    take_col0_kernel<<<grid1(rows), 256, 0, st>>>(d1, 8, m, rows, logw);
-    MB_CUDA(cudaGetLastError());
-    launches += 1;
+    const unsigned g0 = grid1(rows);
+    emit([=](cudaStream_t s) { take_col0_kernel<<<g0, 256, 0, s>>>(d1, 8, m, rows, logw_s); return cudaGetLastError(); });
   }
+  make_room(encoder_cache_);
+  it = encoder_cache_.emplace(key, std::move(prog)).first;
+  }
+  MB_CUDA(cudaMemcpyAsync(ids_s, ids_in, rows * 8, cudaMemcpyDeviceToDevice, st));
+  MB_CUDA(cudaMemcpyAsync(lens_s, lengths_in, static_cast<size_t>(B) * 8, cudaMemcpyDeviceToDevice, st));
+  if (spk_s) MB_CUDA(cudaMemcpyAsync(spk_s, spks_in, static_cast<size_t>(B) * E.spk_dim * 4, cudaMemcpyDeviceToDevice, st));
+  run(*it->second, st);
+  MB_CUDA(cudaMemcpyAsync(mu_x, mux_s, rows * 80 * 4, cudaMemcpyDeviceToDevice, st));
+  MB_CUDA(cudaMemcpyAsync(logw, logw_s, rows * 4, cudaMemcpyDeviceToDevice, st));
   MB_CUDA(cudaMemcpyAsync(x_mask, m, rows * 4, cudaMemcpyDeviceToDevice, st));
   mark_busy(st);
 }
