@@ -6,14 +6,16 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 
-from bench import B, make_inputs  # noqa: E402
 from matcha_b200 import synthetic  # noqa: E402
 from matcha_b200._lib import Plan  # noqa: E402
 
 os.environ.setdefault("MB200_RQ_DBG", "1")
 plan = Plan("fp16", 160, use_graph=False)
 plan.load_estimator(synthetic.estimator_state_dict(160, seed=1234))
-mu, mask, z = (t.cuda() for t in make_inputs(B))
+B, T_PAD = 64, 452
+g = torch.Generator().manual_seed(0)
+mu, z = torch.randn(B, 80, T_PAD, generator=g).cuda(), torch.randn(B, 80, T_PAD, generator=g).cuda()
+mask = torch.ones(B, 1, T_PAD).cuda()
 for _ in range(3):
     plan.estimator_forward(z, mask, mu, torch.tensor(0.3))
 torch.cuda.synchronize()

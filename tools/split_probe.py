@@ -7,12 +7,17 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 
-from bench import B, MEL_MEAN, MEL_STD, N_STEPS, T_VALID, make_inputs  # noqa: E402
+from bench import CONFIGS  # noqa: E402
 from matcha_b200 import synthetic  # noqa: E402
 from matcha_b200._lib import Plan  # noqa: E402
 
 est, gen = synthetic.estimator_state_dict(160, seed=1234), synthetic.generator_state_dict(1234)
-mu, mask, z = (t.cuda() for t in make_inputs(B))
+B, T_VALID, N_STEPS = CONFIGS["cfg2"]["batch"], CONFIGS["cfg2"]["t_valid"], CONFIGS["cfg2"]["n_steps"]
+MEL_MEAN, MEL_STD = CONFIGS["cfg2"]["stats"]
+T_PAD = (T_VALID + 3) // 4 * 4
+g = torch.Generator().manual_seed(0)
+mu, z = torch.randn(B, 80, T_PAD, generator=g).cuda(), torch.randn(B, 80, T_PAD, generator=g).cuda()
+mask = torch.ones(B, 1, T_PAD).cuda()
 
 
 def mk():
